@@ -1,0 +1,167 @@
+/*
+ * tfp_store.h -- C ABI of libtfpstore.so, the B200 (sm_100a) implementation of
+ * LocalAI's `local-store` vector store.
+ *
+ * This is the drop-in boundary: a Go host (go/local-store/store_gpu.go) binds
+ * these entry points through cgo and keeps the reference's gRPC surface
+ * (backend/backend.proto:24-27) unchanged.  Every entry point names the
+ * reference interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions (the reference's own cgo shims use the same ones,
+ * backend/go/bark/gobark.h:1-7): every function returns int, 0 = ok;
+ *   > 0  a validation error the reference would also report -- the text from
+ *        tfp_last_error() is byte-identical to store.go's fmt.Errorf text;
+ *   < 0  a CUDA / driver failure (text from tfp_last_error()).
+ * There is no CPU fallback anywhere behind this header.
+ *
+ * Keys are fp32, row-major, `dim` floats per key.  Ids are int64 handles the
+ * library assigns at insertion; the host keeps id -> value bytes (values never
+ * cross this boundary, store.go:23).
+ *
+ * Threading: calls on one store may come from any thread; mutations are
+ * serialised internally, finds on different find-contexts may overlap.
+ */
+#ifndef TFP_STORE_H
+#define TFP_STORE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tfp_store tfp_store;
+typedef struct tfp_find_ctx tfp_find_ctx;
+
+typedef struct {
+    int      device;         /* CUDA device ordinal this store (shard) lives on            */
+    int64_t  capacity_rows;  /* initial HBM reservation in rows; 0 = default, grows on use */
+    uint32_t flags;          /* TFP_FLAG_*                                                  */
+    uint32_t reserved;
+} tfp_cfg;
+
+#define TFP_FLAG_NONE 0u
+
+/* Largest top-k served by the fused in-kernel selection; larger k takes the
+ * score-spill + radix-sort path (same results, more HBM traffic). */
+#define TFP_FUSED_TOPK_MAX 1024
+
+/* Which arithmetic a find used (store.go:496-510 dispatch). */
+#define TFP_PATH_NORMALIZED 1   /* store.go:327-339, fp32 sequential dot          */
+#define TFP_PATH_FALLBACK   0   /* store.go:414-428, fp64-accumulated cosine      */
+
+/* ---- lifecycle -------------------------------------------------------------
+ * replaces NewStore() (backend/go/stores/store.go:39-46) and Load() (:101-103). */
+int  tfp_store_open(const tfp_cfg* cfg, tfp_store** out);
+void tfp_store_close(tfp_store* s);
+
+/* Text of the calling thread's most recent non-zero return. */
+const char* tfp_last_error(void);
+
+/* ---- StoresSet: replaces Store.StoresSet (store.go:106-198) ------------------
+ * keys: n x dim floats in host memory, copied before return (the Go host may
+ * not lend Go pointers past the call, cgo rules).  n_values is len(opts.Values)
+ * and is only checked against n (store.go:111-113).
+ * out_ids[i]: id now holding key i; out_was_new[i]: 1 = appended, 0 = an equal
+ * stored key was replaced (store.go:183-187; equality is Go's cmp.Compare:
+ * -0 == +0, NaN == NaN).  Duplicates inside one call are both stored, as in the
+ * reference (each stored key is replaced at most once per call). */
+int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_t n_values,
+                  int64_t* out_ids, uint8_t* out_was_new);
+
+/* Same, with the keys already in this device's HBM (bulk load / ingest from an
+ * embedding model's output).  No reference counterpart below the API: the
+ * reference has no device.  Same semantics as tfp_store_set. */
+int tfp_store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim,
+                         int64_t* out_ids, uint8_t* out_was_new);
+
+/* ---- StoresDelete: replaces Store.StoresDelete (store.go:200-264) ------------
+ * out_ids[i] = id removed for key i, or -1 when the key was not stored
+ * (missing keys are ignored, as in the reference). */
+int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids);
+
+/* ---- StoresGet: replaces Store.StoresGet (store.go:266-311) ------------------
+ * out_ids[i] = id for request key i or -1.  out_order[0..*out_n_found) lists
+ * the request indices of the found keys in sorted-key order, the order the
+ * reference returns them in (store.go:269,285-301).
+ * Deviation, documented: n == 0 returns an error; the reference panics
+ * (store.go:276 indexes opts.Keys[0]). */
+int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim,
+                  int64_t* out_ids, int64_t* out_order, int64_t* out_n_found);
+
+/* ---- StoresFind: replaces Store.StoresFind / StoresFindNormalized /
+ * StoresFindFallback (store.go:477-511, 373-412, 430-475) -----------------------
+ * q: dim floats, host memory.  Results in descending similarity:
+ * out_ids/out_sims hold *out_n = min(topk, rows) entries (caller provides topk
+ * slots); out_keys, when not NULL, receives the matching key rows (topk x dim),
+ * which StoresFindResult.Keys needs.  out_path, when not NULL, gets TFP_PATH_*.
+ * Scores are the reference's arithmetic bit for bit (amd64, no FMA); among
+ * exactly equal scores the lower slot (older row) ranks first. */
+int tfp_store_find(tfp_store* s, const float* q, int dim, int topk,
+                   int* out_n, int64_t* out_ids, float* out_sims, float* out_keys, int* out_path);
+
+/* nq independent finds that share one pass over the keys per group of up to 8
+ * queries.  Same per-query results as nq calls of tfp_store_find.  Replaces nq
+ * sequential Store.StoresFind calls (the reference has no batch RPC; SURVEY
+ * §8f.2).  out_n[nq]; out_ids/out_sims [nq x topk]; out_keys [nq x topk x dim] or NULL. */
+int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk,
+                         int* out_n, int64_t* out_ids, float* out_sims, float* out_keys);
+
+/* ---- introspection: feeds Status / memory breakdown (pkg/grpc/base/base.go:77-81) */
+typedef struct {
+    int64_t rows;
+    int64_t capacity_rows;
+    int64_t hbm_bytes;
+    int     dim;                  /* -1 until latched (store.go:29,44)              */
+    int     keys_are_normalized;  /* sticky flag, store.go:27,43,126-127            */
+    int     device;
+    int     reserved;
+} tfp_stats;
+int tfp_store_stats(tfp_store* s, tfp_stats* out);
+
+/* ---- find contexts: the asynchronous, device-resident face of StoresFind ------
+ * A context owns a CUDA stream, staged queries in HBM, scratch for the
+ * per-CTA candidate lists and device-resident results.  It exists so that
+ * (a) several finds can be in flight, (b) a multi-GPU host can all-gather the
+ * per-shard candidates without a host round trip, and (c) the
+ * scan can be timed with inputs already in HBM.  No reference counterpart:
+ * the reference is synchronous and single-threaded (store.go:18).        */
+int  tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out);
+void tfp_find_ctx_destroy(tfp_find_ctx* c);
+/* Stage nq host queries into HBM (async on the context's stream); computes each
+ * query's path and |q| on the host exactly as store.go:313-324,435-439. */
+int  tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int dim);
+/* Enqueue the scan + top-k for staged queries [first, first+count).  Results
+ * stay in HBM.  Returns without waiting. */
+int  tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int topk);
+/* Wait, then copy results of the last launch to the host (same layout as
+ * tfp_store_find_batch for `count` queries). */
+int  tfp_find_ctx_download(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys);
+int  tfp_find_ctx_sync(tfp_find_ctx* c);
+/* The context's cudaStream_t, for event timing and for ordering collectives. */
+void* tfp_find_ctx_stream(tfp_find_ctx* c);
+/* Device pointers of the last launch's results: cand[count x topk] packed
+ * (score-order word << 32 | ~slot), ids[count x topk], sims[count x topk], n[count]. */
+int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids,
+                                 float** d_sims, int** d_n);
+/* Number of kernels the context has launched so far (for bench accounting). */
+int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c);
+
+/* ---- cross-shard merge (no reference counterpart) ------------------
+ * After an all-gather of every shard's (sims, ids, n) for one launch, pick the
+ * global top-k per query on the device.  gathered_*: [n_shards x nq x topk]
+ * (n: [n_shards x nq]) in HBM; outputs [nq x topk] / [nq] in HBM; also reports
+ * the winning shard and the index inside that shard's list.  Ties: lower shard,
+ * then that shard's own order.  stream is a cudaStream_t (NULL = default). */
+int tfp_merge_candidates(const float* d_gathered_sims, const int64_t* d_gathered_ids,
+                         const int* d_gathered_n, int n_shards, int nq, int topk,
+                         float* d_out_sims, int64_t* d_out_ids, int* d_out_shard,
+                         int* d_out_index, int* d_out_n, void* stream);
+
+/* Build/version string (contains the SM target the kernels were built for). */
+const char* tfp_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFP_STORE_H */

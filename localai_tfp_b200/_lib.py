@@ -1,0 +1,72 @@
+"""ctypes binding of libtfpstore.so -- one prototype per entry point of include/tfp_store.h."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libtfpstore.so")
+
+
+class TfpCfg(C.Structure):
+    _fields_ = [("device", C.c_int), ("capacity_rows", C.c_int64), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class TfpStats(C.Structure):
+    _fields_ = [("rows", C.c_int64), ("capacity_rows", C.c_int64), ("hbm_bytes", C.c_int64), ("dim", C.c_int),
+                ("keys_are_normalized", C.c_int), ("device", C.c_int), ("reserved", C.c_int)]
+
+
+fp = C.POINTER(C.c_float)
+i64p = C.POINTER(C.c_int64)
+i32p = C.POINTER(C.c_int)
+u8p = C.POINTER(C.c_uint8)
+vp = C.c_void_p
+
+# name -> (restype, argtypes); kept in the order of include/tfp_store.h
+PROTOTYPES = {
+    "tfp_store_open": (C.c_int, [C.POINTER(TfpCfg), C.POINTER(vp)]),
+    "tfp_store_close": (None, [vp]),
+    "tfp_last_error": (C.c_char_p, []),
+    "tfp_store_set": (C.c_int, [vp, fp, C.c_int64, C.c_int, C.c_int64, i64p, u8p]),
+    "tfp_store_set_device": (C.c_int, [vp, vp, C.c_int64, C.c_int, i64p, u8p]),
+    "tfp_store_delete": (C.c_int, [vp, fp, C.c_int64, C.c_int, i64p]),
+    "tfp_store_get": (C.c_int, [vp, fp, C.c_int64, C.c_int, i64p, i64p, i64p]),
+    "tfp_store_find": (C.c_int, [vp, fp, C.c_int, C.c_int, i32p, i64p, fp, fp, i32p]),
+    "tfp_store_find_batch": (C.c_int, [vp, fp, C.c_int, C.c_int, C.c_int, i32p, i64p, fp, fp]),
+    "tfp_store_stats": (C.c_int, [vp, C.POINTER(TfpStats)]),
+    "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),
+    "tfp_find_ctx_destroy": (None, [vp]),
+    "tfp_find_ctx_upload": (C.c_int, [vp, fp, C.c_int, C.c_int]),
+    "tfp_find_ctx_launch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
+    "tfp_find_ctx_download": (C.c_int, [vp, i32p, i64p, fp, fp]),
+    "tfp_find_ctx_sync": (C.c_int, [vp]),
+    "tfp_find_ctx_stream": (vp, [vp]),
+    "tfp_find_ctx_device_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+    "tfp_find_ctx_launch_count": (C.c_int64, [vp]),
+    "tfp_merge_candidates": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
+    "tfp_version": (C.c_char_p, []),
+}
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _LIB
+
+
+def load():
+    """dlopen libtfpstore.so.  Raises if it has not been built: there is nothing to fall back to."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            raise RuntimeError(
+                f"{_LIB} is missing: build it with `python -m localai_tfp_b200.build` "
+                "(or __graft_entry__.build()); the store has no CPU fallback")
+        L = C.CDLL(_LIB)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)  # AttributeError here == the library does not match the header
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib

@@ -1,0 +1,435 @@
+// scan.cuh -- the StoresFind hot loop on sm_100a.
+//
+// Replaces `for i, k := range s.keys { sim := ...; heap.Push ...}` of
+// StoresFindNormalized / StoresFindFallback
+// (backend/go/stores/store.go:378-389, :441-452) and the two similarity
+// functions (store.go:327-339 fp32 sequential dot; :414-428 fp64-accumulated
+// cosine of fp32-rounded products).
+//
+// Design:
+//   * persistent grid, one CTA per SM; tile = 128 consecutive rows;
+//   * a producer warp streams each tile as [128 rows x 32 floats] TMA boxes
+//     (128-byte swizzle) through a ring of shared-memory stages guarded by
+//     full/empty mbarriers -- the key matrix is read from HBM exactly once;
+//   * 128 consumer threads, ONE THREAD PER ROW: each thread walks its row in
+//     index order with separately rounded multiply and add, i.e. exactly the
+//     reference's arithmetic, so scores are bit-identical to the Go code.  The
+//     swizzle makes the per-thread 16-byte shared loads bank-conflict free;
+//   * NQ (1..8) queries share one pass over the keys;
+//   * the top-k selection is fused (select.cuh); per-CTA survivors go to a small
+//     scratch area in HBM and the last CTA to finish merges them.
+#pragma once
+#include "select.cuh"
+
+namespace tfp {
+
+constexpr int kBoxCols = 32;                               // floats per row per TMA box (128 B)
+constexpr int kStageBytes = kRowsPerTile * kBoxCols * 4;   // 16 KiB
+constexpr int kScanThreads = kRowsPerTile + 32;            // consumers + producer warp
+constexpr int kMaxStages = 12;
+constexpr int kMaxNQ = 8;
+
+struct QInfo {        // per staged query, filled on the host (exact reference arithmetic)
+    double mag1;      // store.go:435-439
+    int normalized;   // store.go:313-324 && store flag
+    int pad;
+};
+
+struct ScanParams {
+    const float* keys;        // [capacity x dim] row-major
+    const int64_t* ids;       // [capacity]
+    const double* knorm;      // [capacity] sqrt(sum float64(float32(k*k))), store.go:420,423
+    uint32_t n_rows;
+    int dim;
+    int n_chunks;             // ceil(dim / 32)
+    int n_stages;
+    int topk;                 // <= TFP_FUSED_TOPK_MAX on the fused path
+    int cap;                  // selection buffer entries per query (power of two)
+    int evict_first;          // stream keys through L2 with evict-first
+    const float* q;           // [nq_total x dim] staged queries
+    const QInfo* qinfo;       // [nq_total]
+    int q_first;              // first staged query of this launch group
+    int out_first;            // first output slot of this launch group
+    // scratch (per find-context)
+    uint64_t* part;           // [grid x kMaxNQ x topk] per-CTA survivors
+    int* part_cnt;            // [grid x kMaxNQ]
+    unsigned long long* gtau; // [kMaxNQ] grid-wide admission bounds
+    unsigned int* ticket;     // [1]
+    uint64_t* all_cand;       // big-k path: [kMaxNQ? no: 1 x n_rows] every row's candidate word
+    // outputs, indexed by out_first + query
+    uint64_t* out_cand;       // [* x topk]
+    int64_t* out_ids;         // [* x topk]
+    float* out_sims;          // [* x topk]
+    uint32_t* out_slots;      // [* x topk]
+    int* out_n;               // [*]
+};
+
+// ---- per-row arithmetic ----------------------------------------------------
+template <bool F64> struct Acc;
+template <> struct Acc<false> {
+    float v;
+    __device__ __forceinline__ void zero() { v = 0.0f; }
+    // dot += k1[i] * k2[i]   (store.go:332) -- product and sum rounded separately
+    __device__ __forceinline__ void add(float q, float k) { v = __fadd_rn(v, __fmul_rn(q, k)); }
+};
+template <> struct Acc<true> {
+    double v;
+    __device__ __forceinline__ void zero() { v = 0.0; }
+    // dot += float64(k1[i] * k2[i])   (store.go:419)
+    __device__ __forceinline__ void add(float q, float k) { v = __dadd_rn(v, (double)__fmul_rn(q, k)); }
+};
+
+template <bool F64>
+__device__ __forceinline__ float finish_score(const Acc<F64>& a, double mag1, double knorm) {
+    if constexpr (F64) {
+        // sim := float32(dot / (mag1 * math.Sqrt(mag2)))   (store.go:423)
+        return __double2float_rn(__ddiv_rn(a.v, __dmul_rn(mag1, knorm)));
+    } else {
+        return a.v;
+    }
+}
+
+// ---- shared-memory carve-up --------------------------------------------------
+struct ScanSmem {
+    uint8_t* stages;             // n_stages x kStageBytes, 1024-aligned
+    float* q;                    // NQ x dpad
+    uint64_t* sel;               // NQ x cap
+    uint64_t* full;              // n_stages
+    uint64_t* empty;             // n_stages
+    uint64_t* qbar;              // 1
+    unsigned long long* tau;     // NQ
+    int* cnt;                    // NQ
+    int* flag;                   // 1
+};
+__host__ __device__ inline size_t scan_smem_bytes(int n_stages, int nq, int dpad, int cap) {
+    size_t b = (size_t)n_stages * kStageBytes;
+    b += (size_t)nq * dpad * 4;
+    b = (b + 15) & ~(size_t)15;
+    b += (size_t)nq * cap * 8;
+    b += (size_t)(2 * n_stages + 1) * 8;
+    b += (size_t)nq * 8 + (size_t)nq * 4 + 16;
+    return b + 1024;  // slack for the 1024-byte alignment of the stage ring
+}
+__device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int nq, int dpad, int cap) {
+    ScanSmem s;
+    // pointer arithmetic only (no integer round trip), so the compiler keeps the
+    // shared address space and emits LDS/STS rather than generic LD/ST
+    uint8_t* p = raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
+    s.stages = p; p += (size_t)n_stages * kStageBytes;
+    s.q = (float*)p; p += ((size_t)nq * dpad * 4 + 15) & ~(size_t)15;
+    s.sel = (uint64_t*)p; p += (size_t)nq * cap * 8;
+    s.full = (uint64_t*)p; p += (size_t)n_stages * 8;
+    s.empty = (uint64_t*)p; p += (size_t)n_stages * 8;
+    s.qbar = (uint64_t*)p; p += 8;
+    s.tau = (unsigned long long*)p; p += (size_t)nq * 8;
+    s.cnt = (int*)p; p += (size_t)nq * 4;
+    s.flag = (int*)p;
+    return s;
+}
+
+// ---- epilogue shared by the TMA and the generic kernel -----------------------
+// Called by the kSelThreads consumer threads after the CTA's last tile.
+template <int NQ>
+__device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int tid) {
+    const int k = p.topk;
+    // 1. final local prune, then publish this CTA's survivors
+    for (int q = 0; q < NQ; q++) {
+        sel_prune(sel[q], p.gtau + q, tid);
+        int m = *sel[q].cnt;
+        unsigned long long bound = *sel[q].tau;   // includes the grid-wide bound seen so far
+        uint64_t* dst = p.part + ((size_t)blockIdx.x * kMaxNQ + q) * k;
+        // survivors are sorted descending, so those >= bound form a prefix
+        int keep = 0;
+        for (int i = tid; i < m; i += kSelThreads) {
+            uint64_t c = sel[q].buf[i];
+            if (c >= bound) dst[i] = c;
+        }
+        if (tid == 0) {
+            int lo = 0, hi = m;   // first index with buf[i] < bound
+            while (lo < hi) { int mid = (lo + hi) >> 1; if (sel[q].buf[mid] >= bound) lo = mid + 1; else hi = mid; }
+            keep = lo;
+            p.part_cnt[blockIdx.x * kMaxNQ + q] = keep;
+        }
+    }
+    __threadfence();
+    named_bar_sync(kSelBarrier, kSelThreads);
+    if (tid == 0) {
+        unsigned int t = atomicAdd(p.ticket, 1u);
+        *flag = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    named_bar_sync(kSelBarrier, kSelThreads);
+    if (*flag == 0) return;
+    __threadfence();
+
+    // 2. last CTA: merge every CTA's survivors (own list is already in sel[q].buf).
+    // tau may BE another CTA's k-th best (it travelled through gtau), and that row is
+    // part of the answer: admit words >= tau here, i.e. > tau - 1.  No word is offered
+    // twice (own rows are not re-offered), so equality can only be that one row.
+    if (tid < NQ) { unsigned long long t = *sel[tid].tau; *sel[tid].tau = t ? t - 1 : 0ull; }
+    named_bar_sync(kSelBarrier, kSelThreads);
+    for (int q = 0; q < NQ; q++) {
+        for (unsigned b = 0; b < gridDim.x; b++) {
+            if (b == blockIdx.x) continue;
+            int m = ((volatile int*)p.part_cnt)[b * kMaxNQ + q];
+            const uint64_t* src = p.part + ((size_t)b * kMaxNQ + q) * k;
+            for (int i = tid; i < m; i += kSelThreads) sel_offer(sel[q], __ldcg(src + i));
+            named_bar_sync(kSelBarrier, kSelThreads);
+            sel_maybe_prune(sel[q], nullptr, tid);
+        }
+        sel_prune(sel[q], nullptr, tid);
+        int m = *sel[q].cnt;
+        const int o = p.out_first + q;
+        for (int i = tid; i < k; i += kSelThreads) {
+            size_t at = (size_t)o * k + i;
+            if (i < m) {
+                uint64_t c = sel[q].buf[i];
+                uint32_t slot = cand_slot(c);
+                p.out_cand[at] = c;
+                p.out_sims[at] = cand_score(c);
+                p.out_slots[at] = slot;
+                p.out_ids[at] = p.ids[slot];
+            } else {
+                p.out_cand[at] = 0ull;
+                p.out_sims[at] = 0.0f;
+                p.out_slots[at] = 0xFFFFFFFFu;
+                p.out_ids[at] = -1;
+            }
+        }
+        if (tid == 0) {
+            p.out_n[o] = m;
+            p.gtau[q] = 0ull;   // leave the scratch clean for the next launch on this context
+        }
+    }
+    if (tid == 0) *p.ticket = 0u;
+}
+
+template <int NQ>
+__device__ __forceinline__ void sel_setup(const ScanParams& p, const ScanSmem& sm, SelState* sel, int tid) {
+    for (int q = 0; q < NQ; q++) {
+        sel[q].buf = sm.sel + (size_t)q * p.cap;
+        sel[q].cnt = sm.cnt + q;
+        sel[q].tau = sm.tau + q;
+        sel[q].cap = p.cap;
+        sel[q].k = p.topk;
+        sel[q].room = p.topk > kRowsPerTile ? p.topk : kRowsPerTile;
+    }
+    if (tid < NQ) { sm.cnt[tid] = 0; sm.tau[tid] = 0ull; }
+}
+
+// Offer one finished tile's scores and keep the buffers within capacity.
+template <int NQ, bool SPILL>
+__device__ __forceinline__ void tile_offer(const ScanParams& p, SelState* sel, const float* score, uint32_t row,
+                                           bool valid, int tid, unsigned long long g_seen) {
+    if constexpr (SPILL) {
+        // big-k path: every row's candidate word goes to HBM, selection happens in a later pass
+        if (valid) {
+#pragma unroll
+            for (int q = 0; q < NQ; q++) p.all_cand[(size_t)q * p.n_rows + row] = pack_cand(score[q], row);
+        }
+    } else {
+        if (valid) {
+#pragma unroll
+            for (int q = 0; q < NQ; q++) sel_offer(sel[q], pack_cand(score[q], row));
+        }
+        named_bar_sync(kSelBarrier, kSelThreads);
+        if (tid < NQ) {  // fold in the grid-wide bound read at the start of this tile
+            if (g_seen > *sel[tid].tau) *sel[tid].tau = g_seen;
+        }
+#pragma unroll
+        for (int q = 0; q < NQ; q++) sel_maybe_prune(sel[q], p.gtau + q, tid);
+    }
+}
+
+// ---- the TMA kernel -----------------------------------------------------------
+template <int NQ, bool F64, bool SPILL>
+__global__ void __launch_bounds__(kScanThreads, 1)
+scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const int dpad = p.n_chunks * kBoxCols;
+    ScanSmem sm = scan_carve(smem_raw, p.n_stages, NQ, dpad, p.cap);
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5;
+    const uint32_t n_tiles = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+
+    if (tid == 0) {
+        for (int s = 0; s < p.n_stages; s++) {
+            mbar_init(sm.full + s, 1);                     // producer's arrive.expect_tx
+            mbar_init(sm.empty + s, kRowsPerTile / 32);    // one arrive per consumer warp
+        }
+        mbar_init(sm.qbar, 1);
+        fence_mbar_init();
+    }
+    // zero the padded query tail (columns >= dim) before the bulk copies land
+    for (int i = tid; i < NQ * dpad; i += kScanThreads) {
+        int c = i % dpad;
+        if (c >= p.dim) sm.q[i] = 0.0f;
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    if (warp == kRowsPerTile / 32) {
+        // ===================== producer warp (one elected lane) =====================
+        if ((tid & 31) == 0) {
+            tma_prefetch_desc(&tmap);
+            // TMA-stage the queries: one 1-D bulk copy per query
+            mbar_arrive_expect_tx(sm.qbar, (uint32_t)(NQ * p.dim * 4));
+            for (int q = 0; q < NQ; q++)
+                bulk_load_1d(sm.q + (size_t)q * dpad, p.q + (size_t)(p.q_first + q) * p.dim, (uint32_t)(p.dim * 4),
+                             sm.qbar);
+            const uint64_t policy = p.evict_first ? l2_policy_evict_first() : l2_policy_evict_normal();
+            int stage = 0;
+            uint32_t phase = 0;
+            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int c = 0; c < p.n_chunks; c++) {
+                    mbar_wait(sm.empty + stage, phase ^ 1u);
+                    mbar_arrive_expect_tx(sm.full + stage, kStageBytes);
+                    tma_load_2d(sm.stages + (size_t)stage * kStageBytes, &tmap, sm.full + stage, c * kBoxCols,
+                                (int)(tile * kRowsPerTile), policy);
+                    if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        return;
+    }
+
+    // ========================= consumer threads: one row each =========================
+    SelState sel[NQ];
+    sel_setup<NQ>(p, sm, sel, tid);
+    named_bar_sync(kSelBarrier, kSelThreads);
+
+    double mag1[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+
+    mbar_wait(sm.qbar, 0);
+    const uint32_t swz = (uint32_t)(tid & 7);
+    const uint32_t row_off = (uint32_t)tid * 128u;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        Acc<F64> acc[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; q++) acc[q].zero();
+        const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
+        const bool valid = row < p.n_rows;
+        // issued now, consumed at the end of the tile: their latency hides behind the row walk
+        const double kn = (F64 && valid) ? __ldg(p.knorm + row) : 1.0;
+        unsigned long long g_seen = 0ull;
+        if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
+        for (int c = 0; c < p.n_chunks; c++) {
+            mbar_wait(sm.full + stage, phase);
+            const uint8_t* srow = sm.stages + (size_t)stage * kStageBytes + row_off;
+            const float* qc = sm.q + c * kBoxCols;
+            const int nvalid = p.dim - c * kBoxCols;  // >= 32 except in a ragged last chunk
+            if (nvalid >= kBoxCols) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float4 kv = *reinterpret_cast<const float4*>(srow + (((uint32_t)j ^ swz) << 4));
+#pragma unroll
+                    for (int q = 0; q < NQ; q++) {
+                        const float4 qv = *reinterpret_cast<const float4*>(qc + (size_t)q * dpad + j * 4);
+                        acc[q].add(qv.x, kv.x);
+                        acc[q].add(qv.y, kv.y);
+                        acc[q].add(qv.z, kv.z);
+                        acc[q].add(qv.w, kv.w);
+                    }
+                }
+            } else {
+                for (int j = 0; j * 4 < nvalid; j++) {  // dim % 4 == 0 on this path
+                    const float4 kv = *reinterpret_cast<const float4*>(srow + (((uint32_t)j ^ swz) << 4));
+#pragma unroll
+                    for (int q = 0; q < NQ; q++) {
+                        const float4 qv = *reinterpret_cast<const float4*>(qc + (size_t)q * dpad + j * 4);
+                        acc[q].add(qv.x, kv.x);
+                        acc[q].add(qv.y, kv.y);
+                        acc[q].add(qv.z, kv.z);
+                        acc[q].add(qv.w, kv.w);
+                    }
+                }
+            }
+            __syncwarp();
+            if ((tid & 31) == 0) mbar_arrive(sm.empty + stage);
+            if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
+        }
+        float score[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
+        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
+    }
+    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, tid);
+}
+
+// ---- the generic kernel: any dim (dim % 4 != 0, dim < 32, or a query too long
+// for shared memory).  Same arithmetic and selection; rows are read straight
+// from global memory, one thread per row, so it is correct but not tuned. -------
+template <int NQ, bool F64, bool SPILL>
+__global__ void __launch_bounds__(kSelThreads, 4)
+scan_generic_kernel(const ScanParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    ScanSmem sm;  // no stages, no staged query: only the selection state
+    uint8_t* base = smem_raw + ((16u - (smem_u32(smem_raw) & 15u)) & 15u);
+    sm.sel = (uint64_t*)base;
+    sm.tau = (unsigned long long*)(base + (size_t)NQ * p.cap * 8);
+    sm.cnt = (int*)(sm.tau + NQ);
+    sm.flag = sm.cnt + NQ;
+    const int tid = threadIdx.x;
+    SelState sel[NQ];
+    sel_setup<NQ>(p, sm, sel, tid);
+    named_bar_sync(kSelBarrier, kSelThreads);
+    double mag1[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    const uint32_t n_tiles = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
+        const bool valid = row < p.n_rows;
+        Acc<F64> acc[NQ];
+#pragma unroll
+        for (int q = 0; q < NQ; q++) acc[q].zero();
+        unsigned long long g_seen = 0ull;
+        if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
+        if (valid) {
+            const float* kr = p.keys + (size_t)row * p.dim;
+            for (int i = 0; i < p.dim; i++) {
+                const float kv = kr[i];
+#pragma unroll
+                for (int q = 0; q < NQ; q++) acc[q].add(__ldg(p.q + (size_t)(p.q_first + q) * p.dim + i), kv);
+            }
+        }
+        float score[NQ];
+        const double kn = (F64 && valid) ? p.knorm[row] : 1.0;
+#pragma unroll
+        for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
+        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
+    }
+    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, tid);
+}
+__host__ inline size_t scan_generic_smem_bytes(int nq, int cap) {
+    return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + 32;
+}
+
+// ---- big-k path, pass 2: decode the first k of the (already sorted) spill -------
+__global__ void decode_sorted_kernel(const uint64_t* sorted, uint32_t n_rows, int k, const int64_t* ids, int o,
+                                     uint64_t* out_cand, int64_t* out_ids, float* out_sims, uint32_t* out_slots,
+                                     int* out_n) {
+    const int m = (uint32_t)k < n_rows ? k : (int)n_rows;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < k; i += gridDim.x * blockDim.x) {
+        size_t at = (size_t)o * k + i;
+        if (i < m) {
+            uint64_t c = sorted[i];
+            uint32_t slot = cand_slot(c);
+            out_cand[at] = c;
+            out_sims[at] = cand_score(c);
+            out_slots[at] = slot;
+            out_ids[at] = ids[slot];
+        } else {
+            out_cand[at] = 0ull;
+            out_sims[at] = 0.0f;
+            out_slots[at] = 0xFFFFFFFFu;
+            out_ids[at] = -1;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) out_n[o] = m;
+}
+
+}  // namespace tfp

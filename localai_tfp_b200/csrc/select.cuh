@@ -1,0 +1,94 @@
+// select.cuh -- fused top-k selection that lives inside the scan kernel.
+//
+// Replaces the reference's container/heap priority queue
+// (backend/go/stores/store.go:341-371, push/pop per key at :380-388) with a
+// threshold-filtered candidate buffer in shared memory:
+//   * every row's score becomes one 64-bit candidate word (common.cuh);
+//   * a row is appended only if it beats the current k-th best (`tau`);
+//   * when the buffer is nearly full the CTA sorts it (bitonic, descending),
+//     keeps the best k and raises tau;
+//   * tau is also raised from a grid-wide bound (`gtau`, atomicMax in HBM): the
+//     k-th best of ANY CTA is a lower bound of the global k-th best, so rows
+//     below it can never be in the answer.  This only drops non-winners, so the
+//     result is deterministic.
+// The selection costs nothing in HBM traffic: the key stream is read once.
+#pragma once
+#include "common.cuh"
+
+namespace tfp {
+
+constexpr int kRowsPerTile = 128;           // rows per tile == consumer threads per CTA
+constexpr int kSelThreads = kRowsPerTile;   // threads that run the selection
+constexpr int kSelBarrier = 1;              // named barrier id used by the consumer warps
+
+struct SelState {
+    uint64_t* buf;           // [cap] candidate words (shared)
+    int* cnt;                // entries in buf (shared)
+    unsigned long long* tau; // current admission threshold (shared)
+    int cap;                 // power of two
+    int k;
+    int room;                // pushes that may happen between two capacity checks
+};
+
+// Bitonic sort, descending, of buf[0..P) with P a power of two, by kSelThreads threads.
+__device__ __forceinline__ void sel_sort_desc(uint64_t* buf, int P, int tid) {
+    for (int k2 = 2; k2 <= P; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < (P >> 1); i += kSelThreads) {
+                int lo = ((i / j) * (j << 1)) + (i % j);
+                int hi = lo + j;
+                uint64_t x = buf[lo], y = buf[hi];
+                bool desc = ((lo & k2) == 0);
+                if ((x < y) == desc && x != y) {
+                    buf[lo] = y;
+                    buf[hi] = x;
+                }
+            }
+            named_bar_sync(kSelBarrier, kSelThreads);
+        }
+    }
+}
+
+// Keep the best k of buf[0..cnt); raise tau; fold in / publish the grid-wide bound.
+// Must be called by all kSelThreads threads with a uniform view of *cnt.
+__device__ __forceinline__ void sel_prune(const SelState& s, unsigned long long* gtau, int tid) {
+    int n = *s.cnt;
+    int P = 2;
+    while (P < n) P <<= 1;
+    for (int i = n + tid; i < P; i += kSelThreads) s.buf[i] = 0ull;
+    named_bar_sync(kSelBarrier, kSelThreads);
+    sel_sort_desc(s.buf, P, tid);
+    if (tid == 0) {
+        int m = n < s.k ? n : s.k;
+        unsigned long long t = *s.tau;
+        if (m == s.k) {
+            unsigned long long kth = s.buf[s.k - 1];
+            if (kth > t) t = kth;
+        }
+        if (gtau) {
+            unsigned long long g = (m == s.k) ? atomicMax(gtau, t) : *((volatile unsigned long long*)gtau);
+            if (g > t) t = g;
+        }
+        *s.tau = t;
+        *s.cnt = m;
+    }
+    named_bar_sync(kSelBarrier, kSelThreads);
+}
+
+// One thread offers one candidate.  Capacity is guaranteed by sel_maybe_prune.
+__device__ __forceinline__ void sel_offer(const SelState& s, uint64_t cand) {
+    if (cand > *((volatile unsigned long long*)s.tau)) {
+        int pos = atomicAdd(s.cnt, 1);
+        s.buf[pos] = cand;
+    }
+}
+
+// Call after a round of offers, with a barrier already between the offers and
+// this call.  Uniform across the consumer threads.
+__device__ __forceinline__ void sel_maybe_prune(const SelState& s, unsigned long long* gtau, int tid) {
+    int n = *((volatile int*)s.cnt);
+    named_bar_sync(kSelBarrier, kSelThreads);  // everyone has read cnt before anyone changes it
+    if (n > s.cap - s.room) sel_prune(s, gtau, tid);
+}
+
+}  // namespace tfp

@@ -1,0 +1,895 @@
+// tfp_store.cu -- host side of libtfpstore.so and the C ABI of include/tfp_store.h.
+//
+// Mirrors the reference's Store (backend/go/stores/store.go:17-30): the sticky
+// normalised flag, the latched key length, the error texts, the set / delete /
+// get / find semantics -- with the keys resident in B200 HBM and every loop over
+// keys running as a CUDA kernel (scan.cuh, select.cuh, ingest.cuh).
+// There is no CPU fallback: if CUDA is unusable every entry point fails.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <shared_mutex>
+#include <string>
+#include <unordered_set>
+#include <vector>
+
+#include "../../include/tfp_store.h"
+#include "host_index.hpp"
+#include "ingest.cuh"
+#include "scan.cuh"
+
+using namespace tfp;
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CU_OK(expr)                                                                                       \
+    do {                                                                                                  \
+        cudaError_t e__ = (expr);                                                                         \
+        if (e__ != cudaSuccess)                                                                           \
+            return fail(-1, "CUDA error %s at %s:%d: %s", cudaGetErrorName(e__), __FILE__, __LINE__, #expr); \
+    } while (0)
+
+extern "C" const char* tfp_last_error(void) { return g_err.c_str(); }
+extern "C" const char* tfp_version(void) { return "libtfpstore 0.1 (sm_100a; TMA scan, fused top-k)"; }
+
+// ---------------------------------------------------------------------------
+// small RAII-less buffers (explicit release; the store owns them)
+// ---------------------------------------------------------------------------
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t want) {
+        if (want <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        size_t cap = std::max<size_t>(want, 256);
+        CU_OK(cudaMalloc(&p, cap));
+        bytes = cap;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <class T> T* as() const { return (T*)p; }
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t want) {
+        if (want <= bytes) return 0;
+        if (p) cudaFreeHost(p);
+        p = nullptr; bytes = 0;
+        size_t cap = std::max<size_t>(want, 4096);
+        CU_OK(cudaMallocHost(&p, cap));
+        bytes = cap;
+        return 0;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+    template <class T> T* as() const { return (T*)p; }
+};
+
+// ---------------------------------------------------------------------------
+// TMA descriptor encoding through the driver entry point (no -lcuda link, so
+// the library still loads on a machine without a driver; it just cannot run)
+// ---------------------------------------------------------------------------
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_tmapEncodeTiled g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static int get_encoder() {
+    std::call_once(g_encode_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            g_encode = (PFN_tmapEncodeTiled)fn;
+    });
+    return g_encode ? 0 : fail(-2, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+}
+
+// ---------------------------------------------------------------------------
+// the store
+// ---------------------------------------------------------------------------
+struct tfp_find_ctx;
+
+struct tfp_store {
+    int device = 0;
+    std::shared_mutex rw;      // finds: shared while enqueueing; mutations: exclusive
+    int dim = -1;              // store.go:29,44 keyLen
+    bool normalized = true;    // store.go:27,43 keysAreNormalized (sticky)
+    int64_t n = 0, cap = 0, cap_hint = 0;
+    int64_t next_id = 0;
+    float* d_keys = nullptr;
+    int64_t* d_ids = nullptr;
+    double* d_knorm = nullptr;
+    CUtensorMap tmap;
+    bool tmap_ok = false;
+    FlatIndex index;
+    std::vector<uint64_t> slot_hash;   // host mirror: slot -> row hash
+    std::vector<int64_t> slot_id;      // host mirror: slot -> id
+    cudaStream_t s_mut = nullptr;      // side stream for ingest / compaction
+    DevBuf st_rows, st_hash, st_knorm, st_isnorm, st_pair_row, st_pair_slot, st_pair_eq, st_src, st_dst, st_ids;
+    std::vector<tfp_find_ctx*> ctxs;
+    tfp_find_ctx* default_ctx = nullptr;
+    int sm_count = 148;
+    int max_smem = 0;
+};
+
+struct tfp_find_ctx {
+    tfp_store* st = nullptr;
+    cudaStream_t stream = nullptr;
+    int nq = 0, dim = 0;
+    std::vector<QInfo> qinfo;
+    DevBuf d_q, d_qinfo;
+    PinBuf h_in, h_out;
+    DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket
+    DevBuf all_cand, sorted_cand, cub_tmp;
+    DevBuf out_cand, out_ids, out_sims, out_slots, out_n, out_keys;
+    int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
+    int64_t launches = 0;
+};
+
+static int set_device(const tfp_store* s) {
+    CU_OK(cudaSetDevice(s->device));
+    return 0;
+}
+
+static bool tma_eligible(const tfp_store* s) { return s->dim >= kBoxCols && (s->dim % 4) == 0; }
+
+static int encode_tmap(tfp_store* s) {
+    s->tmap_ok = false;
+    if (!tma_eligible(s) || s->cap < kRowsPerTile) return 0;
+    if (get_encoder()) return -2;
+    cuuint64_t gdim[2] = {(cuuint64_t)s->dim, (cuuint64_t)s->cap};
+    cuuint64_t gstride[1] = {(cuuint64_t)s->dim * 4};
+    cuuint32_t box[2] = {(cuuint32_t)kBoxCols, (cuuint32_t)kRowsPerTile};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(&s->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_keys, gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    s->tmap_ok = true;
+    return 0;
+}
+
+// Grow the HBM arrays to hold `rows` rows (dim must be latched).
+static int ensure_capacity(tfp_store* s, int64_t rows) {
+    if (rows <= s->cap) return 0;
+    int64_t ncap = std::max<int64_t>({rows, s->cap * 2, s->cap_hint, (int64_t)1024});
+    if (ncap > 0xFFFFFFF0ll) return fail(-3, "store shard would exceed 2^32 rows");
+    float* nk = nullptr; int64_t* ni = nullptr; double* nn = nullptr;
+    CU_OK(cudaMalloc(&nk, (size_t)ncap * s->dim * 4 + 256));
+    CU_OK(cudaMalloc(&ni, (size_t)ncap * 8));
+    CU_OK(cudaMalloc(&nn, (size_t)ncap * 8));
+    if (s->n > 0) {
+        CU_OK(cudaMemcpyAsync(nk, s->d_keys, (size_t)s->n * s->dim * 4, cudaMemcpyDeviceToDevice, s->s_mut));
+        CU_OK(cudaMemcpyAsync(ni, s->d_ids, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
+        CU_OK(cudaMemcpyAsync(nn, s->d_knorm, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
+        CU_OK(cudaStreamSynchronize(s->s_mut));
+    }
+    if (s->d_keys) cudaFree(s->d_keys);
+    if (s->d_ids) cudaFree(s->d_ids);
+    if (s->d_knorm) cudaFree(s->d_knorm);
+    s->d_keys = nk; s->d_ids = ni; s->d_knorm = nn; s->cap = ncap;
+    return encode_tmap(s);
+}
+
+// ---------------------------------------------------------------------------
+// kernel attribute setup (dynamic shared memory opt-in), once per process+device
+// ---------------------------------------------------------------------------
+template <int NQ, bool F64, bool SPILL> static cudaError_t optin_tma(int bytes) {
+    return cudaFuncSetAttribute(scan_tma_kernel<NQ, F64, SPILL>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+template <int NQ, bool F64, bool SPILL> static cudaError_t optin_gen(int bytes) {
+    return cudaFuncSetAttribute(scan_generic_kernel<NQ, F64, SPILL>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+static int optin_all(int bytes) {
+    CU_OK((optin_tma<1, false, false>(bytes))); CU_OK((optin_tma<1, true, false>(bytes)));
+    CU_OK((optin_tma<2, false, false>(bytes))); CU_OK((optin_tma<2, true, false>(bytes)));
+    CU_OK((optin_tma<4, false, false>(bytes))); CU_OK((optin_tma<4, true, false>(bytes)));
+    CU_OK((optin_tma<8, false, false>(bytes))); CU_OK((optin_tma<8, true, false>(bytes)));
+    CU_OK((optin_tma<1, false, true>(bytes)));  CU_OK((optin_tma<1, true, true>(bytes)));
+    CU_OK((optin_gen<1, false, false>(bytes))); CU_OK((optin_gen<1, true, false>(bytes)));
+    CU_OK((optin_gen<2, false, false>(bytes))); CU_OK((optin_gen<2, true, false>(bytes)));
+    CU_OK((optin_gen<4, false, false>(bytes))); CU_OK((optin_gen<4, true, false>(bytes)));
+    CU_OK((optin_gen<8, false, false>(bytes))); CU_OK((optin_gen<8, true, false>(bytes)));
+    CU_OK((optin_gen<1, false, true>(bytes)));  CU_OK((optin_gen<1, true, true>(bytes)));
+    CU_OK(cudaFuncSetAttribute(merge_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// lifecycle
+// ---------------------------------------------------------------------------
+static int ctx_create(tfp_store* s, tfp_find_ctx** out);
+static void ctx_destroy(tfp_find_ctx* c);
+
+extern "C" int tfp_store_open(const tfp_cfg* cfg, tfp_store** out) {
+    if (!out) return fail(2, "tfp_store_open: out is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(-1, "no usable CUDA device (%s); libtfpstore has no CPU fallback",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    tfp_store* s = new tfp_store();
+    s->device = cfg ? cfg->device : 0;
+    s->cap_hint = cfg ? cfg->capacity_rows : 0;
+    if (s->device < 0 || s->device >= ndev) { delete s; return fail(2, "device %d out of range (have %d)", cfg->device, ndev); }
+    if (set_device(s)) { delete s; return -1; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, s->device) != cudaSuccess) { delete s; return fail(-1, "cudaGetDeviceProperties failed"); }
+    if (prop.major != 10) {
+        int maj = prop.major, min = prop.minor;
+        delete s;
+        return fail(-1, "device %d is sm_%d%d; libtfpstore is built for sm_100a (B200) only", cfg ? cfg->device : 0, maj, min);
+    }
+    s->sm_count = prop.multiProcessorCount;
+    s->max_smem = (int)prop.sharedMemPerBlockOptin;
+    if (optin_all(s->max_smem)) { delete s; return -1; }
+    if (cudaStreamCreateWithFlags(&s->s_mut, cudaStreamNonBlocking) != cudaSuccess) { delete s; return fail(-1, "cudaStreamCreate failed"); }
+    if (ctx_create(s, &s->default_ctx)) { cudaStreamDestroy(s->s_mut); delete s; return -1; }
+    *out = s;
+    return 0;
+}
+
+extern "C" void tfp_store_close(tfp_store* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    cudaDeviceSynchronize();
+    std::vector<tfp_find_ctx*> ctxs = s->ctxs;
+    for (tfp_find_ctx* c : ctxs) ctx_destroy(c);
+    if (s->d_keys) cudaFree(s->d_keys);
+    if (s->d_ids) cudaFree(s->d_ids);
+    if (s->d_knorm) cudaFree(s->d_knorm);
+    DevBuf* bufs[] = {&s->st_rows, &s->st_hash, &s->st_knorm, &s->st_isnorm, &s->st_pair_row,
+                      &s->st_pair_slot, &s->st_pair_eq, &s->st_src, &s->st_dst, &s->st_ids};
+    for (DevBuf* b : bufs) b->release();
+    if (s->s_mut) cudaStreamDestroy(s->s_mut);
+    delete s;
+}
+
+extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
+    if (!s || !out) return fail(2, "tfp_store_stats: NULL argument");
+    std::shared_lock<std::shared_mutex> lk(s->rw);
+    out->rows = s->n;
+    out->capacity_rows = s->cap;
+    out->hbm_bytes = s->cap * ((int64_t)(s->dim > 0 ? s->dim : 0) * 4 + 16);
+    out->dim = s->dim;
+    out->keys_are_normalized = s->normalized ? 1 : 0;
+    out->device = s->device;
+    out->reserved = 0;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// mutation plumbing
+// ---------------------------------------------------------------------------
+static int quiesce_finds(tfp_store* s) {
+    for (tfp_find_ctx* c : s->ctxs) CU_OK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// Go's cmp.Compare on float32 (NaN lowest, NaN == NaN, -0 == +0), used to put a
+// request's keys in the reference's sorted order (store.go:86-99).
+static inline int go_cmp(float x, float y) {
+    bool xn = x != x, yn = y != y;
+    if (xn) return yn ? 0 : -1;
+    if (yn) return 1;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+static int cmp_rows(const float* a, const float* b, int d) {
+    for (int i = 0; i < d; i++) { int c = go_cmp(a[i], b[i]); if (c) return c; }
+    return 0;
+}
+
+struct Lookup {
+    std::vector<uint64_t> hash;     // per staged row
+    std::vector<uint8_t> is_norm;
+    std::vector<int64_t> match;     // stored slot confirmed equal and not yet consumed, or -1
+};
+
+// Hash the staged rows on the device, probe the host index, confirm candidates on
+// the device.  `order` gives the sequence in which rows claim stored slots (each
+// stored slot is claimed at most once per call, like the reference's walks over
+// a sorted batch: store.go:154-189, :225-238, :285-301).
+static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::vector<int64_t>& order, Lookup& L) {
+    const int dim = s->dim;
+    if (s->st_hash.reserve((size_t)n * 8) || s->st_knorm.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
+    int threads = 128;
+    int64_t blocks = (n + threads - 1) / threads;
+    row_stats_kernel<<<(unsigned)blocks, threads, 0, s->s_mut>>>(d_rows, n, dim, s->st_hash.as<uint64_t>(),
+                                                               s->st_knorm.as<double>(), s->st_isnorm.as<uint8_t>());
+    CU_OK(cudaGetLastError());
+    L.hash.resize((size_t)n);
+    L.is_norm.resize((size_t)n);
+    CU_OK(cudaMemcpyAsync(L.hash.data(), s->st_hash.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
+    CU_OK(cudaMemcpyAsync(L.is_norm.data(), s->st_isnorm.p, (size_t)n, cudaMemcpyDeviceToHost, s->s_mut));
+    CU_OK(cudaStreamSynchronize(s->s_mut));
+
+    // candidate pairs (row, slot)
+    std::vector<uint32_t> pr, ps;
+    std::vector<size_t> first((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; i++) {
+        first[(size_t)i] = pr.size();
+        s->index.for_each(L.hash[(size_t)i], [&](uint32_t slot) { pr.push_back((uint32_t)i); ps.push_back(slot); });
+    }
+    first[(size_t)n] = pr.size();
+    std::vector<uint8_t> eq(pr.size(), 0);
+    if (!pr.empty()) {
+        size_t m = pr.size();
+        if (s->st_pair_row.reserve(m * 4) || s->st_pair_slot.reserve(m * 4) || s->st_pair_eq.reserve(m)) return -1;
+        CU_OK(cudaMemcpyAsync(s->st_pair_row.p, pr.data(), m * 4, cudaMemcpyHostToDevice, s->s_mut));
+        CU_OK(cudaMemcpyAsync(s->st_pair_slot.p, ps.data(), m * 4, cudaMemcpyHostToDevice, s->s_mut));
+        int64_t vthreads = (int64_t)m * 32;
+        verify_pairs_kernel<<<(unsigned)((vthreads + 255) / 256), 256, 0, s->s_mut>>>(
+            s->d_keys, dim, d_rows, s->st_pair_row.as<uint32_t>(), s->st_pair_slot.as<uint32_t>(), (int64_t)m,
+            s->st_pair_eq.as<uint8_t>());
+        CU_OK(cudaGetLastError());
+        CU_OK(cudaMemcpyAsync(eq.data(), s->st_pair_eq.p, m, cudaMemcpyDeviceToHost, s->s_mut));
+        CU_OK(cudaStreamSynchronize(s->s_mut));
+    }
+    L.match.assign((size_t)n, -1);
+    std::unordered_set<uint32_t> claimed;
+    for (int64_t oi = 0; oi < n; oi++) {
+        int64_t i = order.empty() ? oi : order[(size_t)oi];
+        for (size_t j = first[(size_t)i]; j < first[(size_t)i + 1]; j++) {
+            if (eq[j] && !claimed.count(ps[j])) {
+                claimed.insert(ps[j]);
+                L.match[(size_t)i] = ps[j];
+                break;
+            }
+        }
+    }
+    return 0;
+}
+
+// Stage host rows in HBM on the mutation stream.
+static int stage_rows(tfp_store* s, const float* keys, int64_t n, int dim, const float** d_rows) {
+    size_t bytes = (size_t)n * dim * 4;
+    if (s->st_rows.reserve(bytes)) return -1;
+    CU_OK(cudaMemcpyAsync(s->st_rows.p, keys, bytes, cudaMemcpyHostToDevice, s->s_mut));
+    *d_rows = s->st_rows.as<float>();
+    return 0;
+}
+
+static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_ids, uint8_t* out_was_new) {
+    const int dim = s->dim;
+    Lookup L;
+    std::vector<int64_t> order;
+    if (lookup_rows(s, d_rows, n, order, L)) return -1;
+    // sticky flag (store.go:125-135)
+    for (int64_t i = 0; i < n; i++) if (!L.is_norm[(size_t)i]) { s->normalized = false; break; }
+
+    std::vector<uint32_t> src((size_t)n), dst((size_t)n);
+    std::vector<int64_t> ids((size_t)n);
+    int64_t n_new = 0;
+    for (int64_t i = 0; i < n; i++) {
+        src[(size_t)i] = (uint32_t)i;
+        if (L.match[(size_t)i] >= 0) {   // equal stored key: the new pair replaces it (store.go:183-187)
+            dst[(size_t)i] = (uint32_t)L.match[(size_t)i];
+            ids[(size_t)i] = s->slot_id[(size_t)L.match[(size_t)i]];
+            if (out_was_new) out_was_new[i] = 0;
+        } else {
+            dst[(size_t)i] = (uint32_t)(s->n + n_new);
+            ids[(size_t)i] = s->next_id + n_new;
+            n_new++;
+            if (out_was_new) out_was_new[i] = 1;
+        }
+        if (out_ids) out_ids[i] = ids[(size_t)i];
+    }
+    if (ensure_capacity(s, s->n + n_new)) return -1;
+    if (s->st_src.reserve((size_t)n * 4) || s->st_dst.reserve((size_t)n * 4) || s->st_ids.reserve((size_t)n * 8)) return -1;
+    CU_OK(cudaMemcpyAsync(s->st_src.p, src.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
+    CU_OK(cudaMemcpyAsync(s->st_dst.p, dst.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
+    CU_OK(cudaMemcpyAsync(s->st_ids.p, ids.data(), (size_t)n * 8, cudaMemcpyHostToDevice, s->s_mut));
+    int threads = dim >= 256 ? 256 : (dim >= 64 ? 64 : 32);
+    scatter_rows_kernel<<<(unsigned)n, threads, 0, s->s_mut>>>(d_rows, s->st_knorm.as<double>(), s->st_src.as<uint32_t>(),
+                                                             s->st_dst.as<uint32_t>(), s->st_ids.as<int64_t>(), n, dim,
+                                                             s->d_keys, s->d_ids, s->d_knorm);
+    CU_OK(cudaGetLastError());
+    // host mirrors and index
+    s->slot_hash.resize((size_t)(s->n + n_new));
+    s->slot_id.resize((size_t)(s->n + n_new));
+    s->index.reserve((size_t)(s->n + n_new));
+    for (int64_t i = 0; i < n; i++) {
+        if (L.match[(size_t)i] < 0) {
+            uint32_t slot = dst[(size_t)i];
+            s->slot_hash[slot] = L.hash[(size_t)i];
+            s->slot_id[slot] = ids[(size_t)i];
+            s->index.insert(L.hash[(size_t)i], slot);
+        }
+    }
+    s->n += n_new;
+    s->next_id += n_new;
+    CU_OK(cudaStreamSynchronize(s->s_mut));
+    return 0;
+}
+
+static int check_scatter_grid(int64_t n) {
+    if (n > 0x7FFFFFFFll) return fail(2, "too many keys in one call (%lld)", (long long)n);
+    return 0;
+}
+
+extern "C" int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_t n_values, int64_t* out_ids,
+                             uint8_t* out_was_new) {
+    if (!s) return fail(2, "tfp_store_set: store is NULL");
+    if (n == 0) return fail(1, "no keys to add");                                     // store.go:107-109
+    if (n != n_values) return fail(1, "len(keys) = %lld, len(values) = %lld", (long long)n, (long long)n_values);  // :111-113
+    if (!keys || dim <= 0) return fail(2, "tfp_store_set: keys is NULL or dim <= 0");
+    if (check_scatter_grid(n)) return 2;
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (s->dim == -1) s->dim = dim;                                                  // :115-116
+    else if (dim != s->dim)
+        return fail(1, "Try to add key with length %d when existing length is %d", dim, s->dim);  // :118-120
+    if (set_device(s) || quiesce_finds(s)) return -1;
+    const float* d_rows = nullptr;
+    if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
+    return set_impl(s, d_rows, n, out_ids, out_was_new);
+}
+
+extern "C" int tfp_store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim, int64_t* out_ids,
+                                    uint8_t* out_was_new) {
+    if (!s) return fail(2, "tfp_store_set_device: store is NULL");
+    if (n == 0) return fail(1, "no keys to add");
+    if (!d_keys || dim <= 0) return fail(2, "tfp_store_set_device: d_keys is NULL or dim <= 0");
+    if (check_scatter_grid(n)) return 2;
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (s->dim == -1) s->dim = dim;
+    else if (dim != s->dim) return fail(1, "Try to add key with length %d when existing length is %d", dim, s->dim);
+    if (set_device(s) || quiesce_finds(s)) return -1;
+    CU_OK(cudaDeviceSynchronize());   // the caller's producer stream is unknown: order after all of it
+    return set_impl(s, d_keys, n, out_ids, out_was_new);
+}
+
+// Request keys in the reference's sorted order (store.go:86-99); ties keep request order.
+static void sorted_order(const float* keys, int64_t n, int dim, std::vector<int64_t>& order) {
+    order.resize((size_t)n);
+    for (int64_t i = 0; i < n; i++) order[(size_t)i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) {
+        return cmp_rows(keys + (size_t)a * dim, keys + (size_t)b * dim, dim) < 0;
+    });
+}
+
+extern "C" int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids, int64_t* out_order,
+                             int64_t* out_n_found) {
+    if (!s) return fail(2, "tfp_store_get: store is NULL");
+    if (out_n_found) *out_n_found = 0;
+    if (n == 0) return fail(1, "no keys to get");   // reference panics here (store.go:276); documented deviation
+    if (!keys || dim <= 0 || !out_ids) return fail(2, "tfp_store_get: NULL argument or dim <= 0");
+    std::unique_lock<std::shared_mutex> lk(s->rw);   // uses the mutation staging buffers
+    if (s->dim == -1) s->dim = dim;                                                  // :275-276
+    else if (dim != s->dim)
+        return fail(1, "Try to get a key with length %d when existing length is %d", dim, s->dim);  // :278-280
+    if (set_device(s)) return -1;
+    std::vector<int64_t> order;
+    sorted_order(keys, n, dim, order);
+    for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
+    int64_t found = 0;
+    if (s->n > 0) {
+        const float* d_rows = nullptr;
+        if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
+        Lookup L;
+        if (lookup_rows(s, d_rows, n, order, L)) return -1;
+        for (int64_t oi = 0; oi < n; oi++) {
+            int64_t i = order[(size_t)oi];
+            if (L.match[(size_t)i] >= 0) {
+                out_ids[i] = s->slot_id[(size_t)L.match[(size_t)i]];
+                if (out_order) out_order[found] = i;
+                found++;
+            }
+        }
+    }
+    if (out_n_found) *out_n_found = found;
+    return 0;
+}
+
+extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids) {
+    if (!s) return fail(2, "tfp_store_delete: store is NULL");
+    if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203
+    if (!keys || dim <= 0) return fail(2, "tfp_store_delete: keys is NULL or dim <= 0");
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (s->dim == -1) s->dim = dim;                                                  // :209-210
+    else if (dim != s->dim)
+        return fail(1, "Trying to delete key with length %d when existing length is %d", dim, s->dim);  // :212-214
+    if (out_ids) for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
+    if (s->n == 0) return 0;
+    if (set_device(s) || quiesce_finds(s)) return -1;
+    std::vector<int64_t> order;
+    sorted_order(keys, n, dim, order);
+    const float* d_rows = nullptr;
+    if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
+    Lookup L;
+    if (lookup_rows(s, d_rows, n, order, L)) return -1;
+    std::vector<uint32_t> holes;
+    for (int64_t i = 0; i < n; i++) {
+        if (L.match[(size_t)i] >= 0) {
+            uint32_t slot = (uint32_t)L.match[(size_t)i];
+            holes.push_back(slot);
+            if (out_ids) out_ids[i] = s->slot_id[slot];
+        }
+    }
+    if (holes.empty()) return 0;
+    const int64_t new_n = s->n - (int64_t)holes.size();
+    std::vector<uint8_t> dead((size_t)(s->n - new_n), 0);   // marks deleted slots in the tail [new_n, n)
+    for (uint32_t h : holes) {
+        s->index.erase(s->slot_hash[h], h);
+        if ((int64_t)h >= new_n) dead[(size_t)(h - new_n)] = 1;
+    }
+    // survivors in the tail fill the holes below new_n
+    std::vector<uint32_t> src, dst;
+    int64_t t = new_n;
+    for (uint32_t h : holes) {
+        if ((int64_t)h >= new_n) continue;
+        while (dead[(size_t)(t - new_n)]) t++;
+        src.push_back((uint32_t)t);
+        dst.push_back(h);
+        s->index.relocate(s->slot_hash[(size_t)t], (uint32_t)t, h);
+        s->slot_hash[h] = s->slot_hash[(size_t)t];
+        s->slot_id[h] = s->slot_id[(size_t)t];
+        t++;
+    }
+    if (!src.empty()) {
+        size_t m = src.size();
+        if (s->st_src.reserve(m * 4) || s->st_dst.reserve(m * 4)) return -1;
+        CU_OK(cudaMemcpyAsync(s->st_src.p, src.data(), m * 4, cudaMemcpyHostToDevice, s->s_mut));
+        CU_OK(cudaMemcpyAsync(s->st_dst.p, dst.data(), m * 4, cudaMemcpyHostToDevice, s->s_mut));
+        int threads = s->dim >= 256 ? 256 : (s->dim >= 64 ? 64 : 32);
+        move_rows_kernel<<<(unsigned)m, threads, 0, s->s_mut>>>(s->d_keys, s->d_ids, s->d_knorm, s->st_src.as<uint32_t>(),
+                                                              s->st_dst.as<uint32_t>(), (int64_t)m, s->dim);
+        CU_OK(cudaGetLastError());
+        CU_OK(cudaStreamSynchronize(s->s_mut));
+    }
+    s->slot_hash.resize((size_t)new_n);
+    s->slot_id.resize((size_t)new_n);
+    s->n = new_n;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// find contexts
+// ---------------------------------------------------------------------------
+static int ctx_create(tfp_store* s, tfp_find_ctx** out) {
+    tfp_find_ctx* c = new tfp_find_ctx();
+    c->st = s;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(-1, "cudaStreamCreate failed"); }
+    if (c->sync_words.reserve((kMaxNQ + 1) * 8)) { cudaStreamDestroy(c->stream); delete c; return -1; }
+    if (cudaMemset(c->sync_words.p, 0, (kMaxNQ + 1) * 8) != cudaSuccess) { ctx_destroy(c); return fail(-1, "cudaMemset failed"); }
+    s->ctxs.push_back(c);
+    *out = c;
+    return 0;
+}
+static void ctx_destroy(tfp_find_ctx* c) {
+    if (!c) return;
+    tfp_store* s = c->st;
+    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    DevBuf* bufs[] = {&c->d_q, &c->d_qinfo, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
+                      &c->cub_tmp, &c->out_cand, &c->out_ids, &c->out_sims, &c->out_slots, &c->out_n, &c->out_keys};
+    for (DevBuf* b : bufs) b->release();
+    c->h_in.release();
+    c->h_out.release();
+    if (s) s->ctxs.erase(std::remove(s->ctxs.begin(), s->ctxs.end(), c), s->ctxs.end());
+    delete c;
+}
+
+extern "C" int tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out) {
+    if (!s || !out) return fail(2, "tfp_find_ctx_create: NULL argument");
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (set_device(s)) return -1;
+    return ctx_create(s, out);
+}
+extern "C" void tfp_find_ctx_destroy(tfp_find_ctx* c) {
+    if (!c) return;
+    tfp_store* s = c->st;
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    cudaSetDevice(s->device);
+    if (c == s->default_ctx) return;   // owned by the store
+    ctx_destroy(c);
+}
+
+// store.go:313-324
+static bool host_is_normalized(const float* k, int d) {
+    double sum = 0.0;
+    for (int i = 0; i < d; i++) { double v = (double)k[i]; sum += v * v; }
+    double s = std::sqrt(sum);
+    return s >= 0.99 && s <= 1.01;
+}
+// store.go:435-439
+static double host_query_mag(const float* q, int d) {
+    double m = 0.0;
+    for (int i = 0; i < d; i++) { volatile float p = q[i] * q[i]; m += (double)p; }
+    return std::sqrt(m);
+}
+
+static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim) {
+    tfp_store* s = c->st;
+    size_t qbytes = (size_t)nq * dim * 4, ibytes = (size_t)nq * sizeof(QInfo);
+    if (c->h_in.reserve(qbytes + ibytes) || c->d_q.reserve(qbytes + 256) || c->d_qinfo.reserve(ibytes)) return -1;
+    c->qinfo.resize((size_t)nq);
+    for (int i = 0; i < nq; i++) {
+        const float* qi = q + (size_t)i * dim;
+        QInfo& info = c->qinfo[(size_t)i];
+        info.normalized = host_is_normalized(qi, dim) ? 1 : 0;   // the store flag is folded in at launch
+        info.mag1 = host_query_mag(qi, dim);
+        info.pad = 0;
+    }
+    memcpy(c->h_in.p, q, qbytes);
+    memcpy((uint8_t*)c->h_in.p + qbytes, c->qinfo.data(), ibytes);
+    CU_OK(cudaMemcpyAsync(c->d_q.p, c->h_in.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+    CU_OK(cudaMemcpyAsync(c->d_qinfo.p, (uint8_t*)c->h_in.p + qbytes, ibytes, cudaMemcpyHostToDevice, c->stream));
+    c->nq = nq;
+    c->dim = dim;
+    (void)s;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int dim) {
+    if (!c || !q || nq <= 0 || dim <= 0) return fail(2, "tfp_find_ctx_upload: bad argument");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    CU_OK(cudaStreamSynchronize(c->stream));   // the pinned staging buffer is reused
+    return ctx_upload_locked(c, q, nq, dim);
+}
+
+static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+template <int NQ, bool F64, bool SPILL>
+static int launch_scan(tfp_find_ctx* c, const ScanParams& p, bool use_tma, int grid, size_t smem) {
+    tfp_store* s = c->st;
+    if (use_tma) scan_tma_kernel<NQ, F64, SPILL><<<grid, kScanThreads, smem, c->stream>>>(s->tmap, p);
+    else scan_generic_kernel<NQ, F64, SPILL><<<grid, kSelThreads, smem, c->stream>>>(p);
+    CU_OK(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+template <bool F64, bool SPILL>
+static int launch_scan_nq(tfp_find_ctx* c, int nq, const ScanParams& p, bool use_tma, int grid, size_t smem) {
+    if constexpr (SPILL) { (void)nq; return launch_scan<1, F64, true>(c, p, use_tma, grid, smem); }
+    else {
+        switch (nq) {
+            case 1: return launch_scan<1, F64, false>(c, p, use_tma, grid, smem);
+            case 2: return launch_scan<2, F64, false>(c, p, use_tma, grid, smem);
+            case 4: return launch_scan<4, F64, false>(c, p, use_tma, grid, smem);
+            case 8: return launch_scan<8, F64, false>(c, p, use_tma, grid, smem);
+        }
+        return fail(-4, "internal: bad query group size %d", nq);
+    }
+}
+
+// Enqueue the scan(s) for staged queries [first, first+count).  Caller holds the shared lock.
+static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
+    tfp_store* s = c->st;
+    if (c->dim != s->dim)                                                            // store.go:480-482
+        return fail(1, "Try to find key with length %d when existing length is %d", c->dim, s->dim);
+    if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
+    if (first < 0 || count <= 0 || first + count > c->nq) return fail(2, "find: query range [%d,%d) outside the %d staged queries", first, first + count, c->nq);
+    const int64_t n = s->n;
+    const int ksel = (int)std::min<int64_t>((int64_t)topk, std::max<int64_t>(n, 1));
+    c->last_count = count;
+    c->last_topk = topk;
+    c->last_stride = ksel;
+    c->last_path = (s->normalized && c->qinfo[(size_t)first].normalized) ? TFP_PATH_NORMALIZED : TFP_PATH_FALLBACK;
+    size_t slots = (size_t)count * ksel;
+    if (c->out_cand.reserve(slots * 8) || c->out_ids.reserve(slots * 8) || c->out_sims.reserve(slots * 4) ||
+        c->out_slots.reserve(slots * 4) || c->out_n.reserve((size_t)count * 4)) return -1;
+    if (n == 0) {   // written-then-emptied store: empty result
+        CU_OK(cudaMemsetAsync(c->out_n.p, 0, (size_t)count * 4, c->stream));
+        return 0;
+    }
+    const int dim = s->dim;
+    const bool fused = ksel <= TFP_FUSED_TOPK_MAX;
+    const int n_chunks = (dim + kBoxCols - 1) / kBoxCols;
+    const int dpad = n_chunks * kBoxCols;
+    const int cap = fused ? std::max(512, next_pow2(ksel + std::max(ksel, kRowsPerTile))) : 2;
+    const uint32_t n_tiles = (uint32_t)((n + kRowsPerTile - 1) / kRowsPerTile);
+    const int grid = (int)std::min<uint32_t>((uint32_t)s->sm_count, n_tiles);
+
+    ScanParams p;
+    memset(&p, 0, sizeof(p));
+    p.keys = s->d_keys; p.ids = s->d_ids; p.knorm = s->d_knorm;
+    p.n_rows = (uint32_t)n; p.dim = dim; p.n_chunks = n_chunks;
+    p.topk = ksel; p.cap = cap;
+    p.evict_first = ((size_t)n * dim * 4 > ((size_t)96 << 20)) ? 1 : 0;   // larger than L2: stream it
+    p.q = c->d_q.as<float>(); p.qinfo = c->d_qinfo.as<QInfo>();
+    p.gtau = c->sync_words.as<unsigned long long>();
+    p.ticket = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ);
+    p.out_cand = c->out_cand.as<uint64_t>(); p.out_ids = c->out_ids.as<int64_t>();
+    p.out_sims = c->out_sims.as<float>(); p.out_slots = c->out_slots.as<uint32_t>(); p.out_n = c->out_n.as<int>();
+
+    if (fused) {
+        if (c->part.reserve((size_t)grid * kMaxNQ * ksel * 8) || c->part_cnt.reserve((size_t)grid * kMaxNQ * 4)) return -1;
+        p.part = c->part.as<uint64_t>(); p.part_cnt = c->part_cnt.as<int>();
+    } else {
+        if (c->all_cand.reserve((size_t)n * 8) || c->sorted_cand.reserve((size_t)n * 8)) return -1;
+        p.all_cand = c->all_cand.as<uint64_t>();
+    }
+
+    int i = 0;
+    while (i < count) {
+        const bool norm = s->normalized && c->qinfo[(size_t)(first + i)].normalized;   // store.go:496
+        int g = 1;
+        if (fused) {
+            while (i + g < count && g < kMaxNQ &&
+                   (s->normalized && c->qinfo[(size_t)(first + i + g)].normalized) == norm) g++;
+            g = g >= 8 ? 8 : (g >= 4 ? 4 : (g >= 2 ? 2 : 1));
+        }
+        // pick the kernel flavour and the stage count that fits shared memory
+        bool use_tma = s->tmap_ok;
+        int n_stages = 0;
+        size_t smem = 0;
+        for (;;) {
+            if (use_tma) {
+                size_t fixed = scan_smem_bytes(0, g, dpad, cap);
+                int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
+                n_stages = std::min(kMaxStages, room);
+                if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, dpad, cap); break; }
+                if (g > 1) { g >>= 1; continue; }
+                use_tma = false;
+            }
+            smem = scan_generic_smem_bytes(g, cap);
+            if (smem <= (size_t)s->max_smem) break;
+            if (g > 1) { g >>= 1; continue; }
+            return fail(-4, "internal: selection buffers do not fit shared memory (k=%d)", ksel);
+        }
+        p.n_stages = n_stages;
+        p.q_first = first + i;
+        p.out_first = i;
+        int rc;
+        if (fused) rc = norm ? launch_scan_nq<false, false>(c, g, p, use_tma, grid, smem)
+                             : launch_scan_nq<true, false>(c, g, p, use_tma, grid, smem);
+        else       rc = norm ? launch_scan_nq<false, true>(c, 1, p, use_tma, grid, smem)
+                             : launch_scan_nq<true, true>(c, 1, p, use_tma, grid, smem);
+        if (rc) return rc;
+        if (!fused) {
+            // big-k path: sort every row's candidate word (descending), keep the first k
+            size_t tmp = 0;
+            CU_OK(cub::DeviceRadixSort::SortKeysDescending(nullptr, tmp, c->all_cand.as<uint64_t>(),
+                                                           c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
+            if (c->cub_tmp.reserve(tmp)) return -1;
+            CU_OK(cub::DeviceRadixSort::SortKeysDescending(c->cub_tmp.p, tmp, c->all_cand.as<uint64_t>(),
+                                                           c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
+            decode_sorted_kernel<<<std::min(1024, (ksel + 255) / 256), 256, 0, c->stream>>>(
+                c->sorted_cand.as<uint64_t>(), (uint32_t)n, ksel, s->d_ids, i, p.out_cand, p.out_ids, p.out_sims,
+                p.out_slots, p.out_n);
+            CU_OK(cudaGetLastError());
+            c->launches += 2;
+        }
+        i += g;
+    }
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int topk) {
+    if (!c) return fail(2, "tfp_find_ctx_launch: ctx is NULL");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    return ctx_launch_locked(c, first, count, topk);
+}
+
+static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys) {
+    tfp_store* s = c->st;
+    const int count = c->last_count, topk = c->last_topk, ks = c->last_stride, dim = s->dim;
+    if (count <= 0) return fail(2, "find download: nothing was launched on this context");
+    size_t slots = (size_t)count * ks;
+    size_t off_n = 0, off_ids = ((size_t)count * 4 + 15) & ~(size_t)15, off_sims = off_ids + slots * 8;
+    size_t off_keys = (off_sims + slots * 4 + 15) & ~(size_t)15;
+    size_t total = off_keys + (out_keys ? slots * dim * 4 : 0);
+    if (c->h_out.reserve(total)) return -1;
+    uint8_t* h = (uint8_t*)c->h_out.p;
+    CU_OK(cudaMemcpyAsync(h + off_n, c->out_n.p, (size_t)count * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (s->n > 0) {
+        CU_OK(cudaMemcpyAsync(h + off_ids, c->out_ids.p, slots * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU_OK(cudaMemcpyAsync(h + off_sims, c->out_sims.p, slots * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (out_keys) {
+            if (c->out_keys.reserve(slots * dim * 4)) return -1;
+            dim3 grid((unsigned)ks, (unsigned)count);
+            int threads = dim >= 256 ? 256 : (dim >= 64 ? 64 : 32);
+            gather_rows_kernel<<<grid, threads, 0, c->stream>>>(s->d_keys, dim, c->out_slots.as<uint32_t>(),
+                                                               c->out_n.as<int>(), ks, c->out_keys.as<float>());
+            CU_OK(cudaGetLastError());
+            c->launches++;
+            CU_OK(cudaMemcpyAsync(h + off_keys, c->out_keys.p, slots * dim * 4, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    CU_OK(cudaStreamSynchronize(c->stream));
+    const int* hn = (const int*)(h + off_n);
+    for (int q = 0; q < count; q++) {
+        int m = s->n > 0 ? hn[q] : 0;
+        if (out_n) out_n[q] = m;
+        if (out_ids) memcpy(out_ids + (size_t)q * topk, h + off_ids + (size_t)q * ks * 8, (size_t)m * 8);
+        if (out_sims) memcpy(out_sims + (size_t)q * topk, h + off_sims + (size_t)q * ks * 4, (size_t)m * 4);
+        if (out_keys) memcpy(out_keys + (size_t)q * topk * dim, h + off_keys + (size_t)q * ks * dim * 4, (size_t)m * dim * 4);
+    }
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_download(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys) {
+    if (!c) return fail(2, "tfp_find_ctx_download: ctx is NULL");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    return ctx_download_locked(c, out_n, out_ids, out_sims, out_keys);
+}
+extern "C" int tfp_find_ctx_sync(tfp_find_ctx* c) {
+    if (!c) return fail(2, "tfp_find_ctx_sync: ctx is NULL");
+    if (set_device(c->st)) return -1;
+    CU_OK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+extern "C" void* tfp_find_ctx_stream(tfp_find_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c) { return c ? c->launches : 0; }
+extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids, float** d_sims, int** d_n) {
+    if (!c) return fail(2, "tfp_find_ctx_device_results: ctx is NULL");
+    if (d_cand) *d_cand = c->out_cand.as<uint64_t>();
+    if (d_ids) *d_ids = c->out_ids.as<int64_t>();
+    if (d_sims) *d_sims = c->out_sims.as<float>();
+    if (d_n) *d_n = c->out_n.as<int>();
+    return c->last_stride;   // entries per query in the device arrays (min(topk, rows))
+}
+
+// ---------------------------------------------------------------------------
+// synchronous finds (what the Go host calls)
+// ---------------------------------------------------------------------------
+extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
+                                    float* out_sims, float* out_keys) {
+    if (!s) return fail(2, "tfp_store_find: store is NULL");
+    std::shared_lock<std::shared_mutex> lk(s->rw);
+    if (dim != s->dim)                                                               // store.go:480-482 (fires on -1 too)
+        return fail(1, "Try to find key with length %d when existing length is %d", dim, s->dim);
+    if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
+    if (!q || nq <= 0) return fail(2, "tfp_store_find: q is NULL or nq <= 0");
+    if (set_device(s)) return -1;
+    static std::mutex default_ctx_mu;   // the built-in context serves one synchronous find at a time
+    std::lock_guard<std::mutex> g(default_ctx_mu);
+    tfp_find_ctx* c = s->default_ctx;
+    int rc = ctx_upload_locked(c, q, nq, dim);
+    if (rc) return rc;
+    rc = ctx_launch_locked(c, 0, nq, topk);
+    if (rc) return rc;
+    return ctx_download_locked(c, out_n, out_ids, out_sims, out_keys);
+}
+
+extern "C" int tfp_store_find(tfp_store* s, const float* q, int dim, int topk, int* out_n, int64_t* out_ids,
+                              float* out_sims, float* out_keys, int* out_path) {
+    int rc = tfp_store_find_batch(s, q, 1, dim, topk, out_n, out_ids, out_sims, out_keys);
+    if (rc == 0 && out_path) *out_path = s->default_ctx->last_path;
+    return rc;
+}
+
+// ---------------------------------------------------------------------------
+// cross-shard merge
+// ---------------------------------------------------------------------------
+extern "C" int tfp_merge_candidates(const float* d_sims, const int64_t* d_ids, const int* d_n, int n_shards, int nq,
+                                    int topk, float* o_sims, int64_t* o_ids, int* o_shard, int* o_index, int* o_n,
+                                    void* stream) {
+    if (!d_sims || !d_ids || !d_n || !o_sims || !o_ids || !o_shard || !o_index || !o_n)
+        return fail(2, "tfp_merge_candidates: NULL argument");
+    if (n_shards < 1 || nq < 1 || topk < 1) return fail(2, "tfp_merge_candidates: bad sizes");
+    int64_t total = (int64_t)n_shards * topk;
+    if (total > 16384) return fail(2, "tfp_merge_candidates: n_shards x topk = %lld exceeds 16384", (long long)total);
+    int P = next_pow2((int)std::max<int64_t>(total, 2));
+    if ((size_t)P * 8 > 48 * 1024)
+        CU_OK(cudaFuncSetAttribute(merge_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
+    merge_candidates_kernel<<<nq, 256, (size_t)P * 8, (cudaStream_t)stream>>>(d_sims, d_ids, d_n, n_shards, nq, topk, P,
+                                                                              o_sims, o_ids, o_shard, o_index, o_n);
+    CU_OK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,263 @@
+"""Host-side mirror of the reference `Store` (backend/go/stores/store.go) over the C ABI.
+
+This is what the Go host (go/local-store/store_gpu.go) does, written in Python
+because the build image has no Go toolchain: it keeps `id -> value bytes`, calls
+libtfpstore.so for everything that touches keys, and re-raises the library's
+validation errors with the reference's exact texts.
+
+Method names and argument meaning follow store.go:
+    StoresSet(keys, values)           store.go:106-198
+    StoresDelete(keys)                store.go:200-264
+    StoresGet(keys) -> (keys, values) store.go:266-311  (sorted-key order)
+    StoresFind(key, topk) -> (keys, values, similarities)  store.go:477-511
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from ._lib import TfpCfg, TfpStats, fp, i32p, i64p, u8p
+
+
+class StoreError(Exception):
+    """An error the reference would also return (same message text)."""
+
+    def __init__(self, msg: str, code: int = 1):
+        super().__init__(msg)
+        self.code = code
+
+
+def _rows(keys) -> Tuple[np.ndarray, int]:
+    """Pack keys into one contiguous [n, dim] fp32 block (the Go host does the same gather copy).
+
+    Deviation from the reference, documented in DESIGN.md: a ragged batch is rejected here; the
+    reference only checks the first key's length (store.go:115-121) and would corrupt its order."""
+    if isinstance(keys, np.ndarray) and keys.ndim == 2:
+        return np.ascontiguousarray(keys, dtype=np.float32), int(keys.shape[1])
+    keys = [np.asarray(k, dtype=np.float32).reshape(-1) for k in keys]
+    if not keys:
+        return np.zeros((0, 1), np.float32), 0
+    d = len(keys[0])
+    for k in keys:
+        if len(k) != d:
+            raise StoreError(f"Try to add key with length {len(k)} when existing length is {d}")
+    return np.ascontiguousarray(np.stack(keys), dtype=np.float32), d
+
+
+def _p(a: np.ndarray, t):
+    return a.ctypes.data_as(t)
+
+
+class Store:
+    """One store shard resident on one B200."""
+
+    def __init__(self, device: int = 0, capacity_rows: int = 0):
+        self._L = _lib.load()
+        cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0)
+        h = C.c_void_p()
+        rc = self._L.tfp_store_open(C.byref(cfg), C.byref(h))
+        if rc:
+            raise RuntimeError(f"tfp_store_open failed ({rc}): {self._err()}")
+        self._h = h
+        self.device = device
+        self.values = {}  # id -> bytes; values never cross the C ABI (store.go:23)
+        self.last_path = None
+
+    # -- plumbing ----------------------------------------------------------
+    def _err(self) -> str:
+        return self._L.tfp_last_error().decode(errors="replace")
+
+    def _check(self, rc: int):
+        if rc > 0:
+            raise StoreError(self._err(), rc)
+        if rc < 0:
+            raise RuntimeError(f"libtfpstore failure ({rc}): {self._err()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.tfp_store_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stats(self) -> TfpStats:
+        st = TfpStats()
+        self._check(self._L.tfp_store_stats(self._h, C.byref(st)))
+        return st
+
+    def __len__(self):
+        return int(self.stats().rows)
+
+    @property
+    def key_len(self) -> int:
+        return int(self.stats().dim)
+
+    @property
+    def keys_are_normalized(self) -> bool:
+        return bool(self.stats().keys_are_normalized)
+
+    # -- StoresSet -----------------------------------------------------------
+    def StoresSet(self, keys, values: Sequence[bytes]):
+        ks, d = _rows(keys)
+        n = len(ks)
+        ids = np.empty(max(n, 1), np.int64)
+        new = np.empty(max(n, 1), np.uint8)
+        self._check(self._L.tfp_store_set(self._h, _p(ks, fp), n, d, len(values), _p(ids, i64p), _p(new, u8p)))
+        for i in range(n):
+            self.values[int(ids[i])] = bytes(values[i])
+        return ids[:n], new[:n]
+
+    def set_device(self, d_ptr: int, n: int, dim: int, values: Sequence[bytes] | None = None):
+        """Bulk load rows that already sit in this GPU's HBM (d_ptr = device address of [n, dim] fp32)."""
+        ids = np.empty(max(n, 1), np.int64)
+        new = np.empty(max(n, 1), np.uint8)
+        self._check(self._L.tfp_store_set_device(self._h, C.c_void_p(d_ptr), n, dim, _p(ids, i64p), _p(new, u8p)))
+        if values is not None:
+            for i in range(n):
+                self.values[int(ids[i])] = bytes(values[i])
+        return ids[:n], new[:n]
+
+    # -- StoresDelete --------------------------------------------------------
+    def StoresDelete(self, keys):
+        ks, d = _rows(keys)
+        n = len(ks)
+        ids = np.empty(max(n, 1), np.int64)
+        self._check(self._L.tfp_store_delete(self._h, _p(ks, fp), n, d, _p(ids, i64p)))
+        for i in range(n):
+            if ids[i] >= 0:
+                self.values.pop(int(ids[i]), None)
+        return ids[:n]
+
+    # -- StoresGet -----------------------------------------------------------
+    def StoresGet(self, keys) -> Tuple[List[np.ndarray], List[bytes]]:
+        ks, d = _rows(keys)
+        n = len(ks)
+        ids = np.empty(max(n, 1), np.int64)
+        order = np.empty(max(n, 1), np.int64)
+        nf = C.c_int64()
+        self._check(self._L.tfp_store_get(self._h, _p(ks, fp), n, d, _p(ids, i64p), _p(order, i64p), C.byref(nf)))
+        out_k, out_v = [], []
+        for j in range(nf.value):
+            i = int(order[j])
+            out_k.append(ks[i].copy())  # the reference echoes the request's key (store.go:289-291)
+            out_v.append(self.values.get(int(ids[i])))
+        return out_k, out_v
+
+    # -- StoresFind ----------------------------------------------------------
+    def StoresFind(self, key, topk: int):
+        q = np.ascontiguousarray(np.asarray(key, dtype=np.float32).reshape(-1))
+        k = int(topk)
+        kk = max(k, 1)
+        rows = len(self)
+        kk = min(kk, max(rows, 1))  # the result holds min(topk, rows) entries (store.go:386-388)
+        n = C.c_int()
+        path = C.c_int(-1)
+        ids = np.empty(kk, np.int64)
+        sims = np.empty(kk, np.float32)
+        outk = np.empty((kk, max(len(q), 1)), np.float32)
+        self._check(self._L.tfp_store_find(self._h, _p(q, fp), len(q), k if k < 1 else kk, C.byref(n), _p(ids, i64p),
+                                           _p(sims, fp), _p(outk, fp), C.byref(path)))
+        m = n.value
+        self.last_path = "normalized" if path.value == 1 else "fallback"
+        return ([outk[i, :len(q)].copy() for i in range(m)], [self.values.get(int(ids[i])) for i in range(m)],
+                sims[:m].copy())
+
+    def find_ids(self, key, topk: int):
+        """StoresFind without the key echo: (ids, similarities)."""
+        q = np.ascontiguousarray(np.asarray(key, dtype=np.float32).reshape(-1))
+        kk = min(max(int(topk), 1), max(len(self), 1))
+        n = C.c_int()
+        ids = np.empty(kk, np.int64)
+        sims = np.empty(kk, np.float32)
+        self._check(self._L.tfp_store_find(self._h, _p(q, fp), len(q), int(topk) if topk < 1 else kk, C.byref(n),
+                                           _p(ids, i64p), _p(sims, fp), None, None))
+        return ids[:n.value].copy(), sims[:n.value].copy()
+
+    def find_batch(self, queries, topk: int, with_keys: bool = False):
+        qs = np.ascontiguousarray(np.asarray(queries, dtype=np.float32))
+        nq, d = qs.shape
+        kk = min(max(int(topk), 1), max(len(self), 1))
+        n = np.empty(nq, np.int32)
+        ids = np.empty((nq, kk), np.int64)
+        sims = np.empty((nq, kk), np.float32)
+        outk = np.empty((nq, kk, d), np.float32) if with_keys else None
+        self._check(self._L.tfp_store_find_batch(self._h, _p(qs, fp), nq, d, int(topk) if topk < 1 else kk,
+                                                 _p(n, i32p), _p(ids, i64p), _p(sims, fp),
+                                                 _p(outk, fp) if with_keys else None))
+        res = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy()) for i in range(nq)]
+        return (res, outk) if with_keys else res
+
+    def find_context(self) -> "FindContext":
+        return FindContext(self)
+
+
+class FindContext:
+    """Asynchronous, device-resident finds (include/tfp_store.h `tfp_find_ctx_*`)."""
+
+    def __init__(self, store: Store):
+        self.store = store
+        self._L = store._L
+        h = C.c_void_p()
+        store._check(self._L.tfp_find_ctx_create(store._h, C.byref(h)))
+        self._h = h
+        self.dim = 0
+        self.nq = 0
+        self._count = 0
+        self._topk = 0
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.store, "_h", None):
+            self._L.tfp_find_ctx_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, queries):
+        qs = np.ascontiguousarray(np.asarray(queries, dtype=np.float32))
+        if qs.ndim == 1:
+            qs = qs[None, :]
+        self.nq, self.dim = qs.shape
+        self.store._check(self._L.tfp_find_ctx_upload(self._h, _p(qs, fp), self.nq, self.dim))
+
+    def launch(self, first: int, count: int, topk: int):
+        self.store._check(self._L.tfp_find_ctx_launch(self._h, first, count, topk))
+        self._count, self._topk = count, topk
+
+    def download(self, with_keys: bool = False):
+        cnt, k = self._count, self._topk
+        n = np.empty(cnt, np.int32)
+        ids = np.empty((cnt, k), np.int64)
+        sims = np.empty((cnt, k), np.float32)
+        outk = np.empty((cnt, k, self.dim), np.float32) if with_keys else None
+        self.store._check(self._L.tfp_find_ctx_download(self._h, _p(n, i32p), _p(ids, i64p), _p(sims, fp),
+                                                        _p(outk, fp) if with_keys else None))
+        res = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy()) for i in range(cnt)]
+        return (res, outk) if with_keys else res
+
+    def sync(self):
+        self.store._check(self._L.tfp_find_ctx_sync(self._h))
+
+    @property
+    def stream(self) -> int:
+        return int(self._L.tfp_find_ctx_stream(self._h) or 0)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._L.tfp_find_ctx_launch_count(self._h))
+
+    def device_results(self):
+        """(stride, cand_ptr, ids_ptr, sims_ptr, n_ptr): device addresses of the last launch's results."""
+        a, b, c, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        stride = self._L.tfp_find_ctx_device_results(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d))
+        return stride, a.value, b.value, c.value, d.value

@@ -1,0 +1,242 @@
+"""The reference's own store tests (tests/integration/stores_test.go, core/http/app_test.go:904-974)
+replayed against the CUDA store through the C ABI, each also compared call by call with the oracle."""
+import numpy as np
+import pytest
+
+from conftest import normalize_rows
+from test_oracle_kat import triangle_holds
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+@pytest.fixture()
+def pair(tfp, oracle):
+    s = tfp.Store()
+    yield s, oracle.OracleStore()
+    s.close()
+
+
+def both(pair, method, *args):
+    """Run the same call on the CUDA store and on the oracle; compare what they return."""
+    gpu, orc = pair
+    a = getattr(gpu, method)(*args)
+    b = getattr(orc, method)(*args)
+    return a, b
+
+
+def same_find(a, b):
+    (ka, va, sa), (kb, vb, sb) = a, b
+    assert np.array_equal(sa, sb), f"{sa} vs {sb}"
+    assert va == vb
+    assert len(ka) == len(kb) and all(np.array_equal(x, y) for x, y in zip(ka, kb))
+
+
+def same_get(a, b):
+    (ka, va), (kb, vb) = a, b
+    assert va == vb
+    assert len(ka) == len(kb) and all(np.array_equal(x, y) for x, y in zip(ka, kb))
+
+
+def test_set_a_key(pair):  # stores_test.go:86-89
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3]], [b"test"])
+    assert len(pair[0]) == len(pair[1]) == 1
+
+
+def test_set_keys(pair):  # stores_test.go:91-97
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6]], [b"test1", b"test2"])
+    both(pair, "StoresSet", [[0.7, 0.8, 0.9], [0.10, 0.11, 0.12]], [b"test3", b"test4"])
+    assert len(pair[0]) == len(pair[1]) == 4
+
+
+def test_get_a_key(pair):  # stores_test.go:99-106
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3]], [b"test"])
+    a, b = both(pair, "StoresGet", [[0.1, 0.2, 0.3]])
+    same_get(a, b)
+    assert a[1] == [b"test"]
+
+
+def test_get_keys(pair):  # stores_test.go:108-146
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]], [b"test1", b"test2", b"test3"])
+    a, b = both(pair, "StoresGet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]])
+    same_get(a, b)
+    assert len(a[0]) == 3
+    a, b = both(pair, "StoresGet", [[0.7, 0.8, 0.9], [0.1, 0.2, 0.3]])
+    same_get(a, b)
+    assert a[1] == [b"test1", b"test3"]  # sorted-key order
+
+
+def test_delete_a_key(pair):  # stores_test.go:148-157
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3]], [b"test"])
+    both(pair, "StoresDelete", [[0.1, 0.2, 0.3]])
+    a, b = both(pair, "StoresGet", [[0.1, 0.2, 0.3]])
+    same_get(a, b)
+    assert a == ([], [])
+
+
+def test_delete_keys(pair):  # stores_test.go:159-181
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]], [b"test1", b"test2", b"test3"])
+    both(pair, "StoresDelete", [[0.1, 0.2, 0.3], [0.7, 0.8, 0.9]])
+    a, b = both(pair, "StoresGet", [[0.4, 0.5, 0.6]])
+    same_get(a, b)
+    assert a[1] == [b"test2"] and np.array_equal(a[0][0], np.array([0.4, 0.5, 0.6], f32))
+    a, b = both(pair, "StoresGet", [[0.1, 0.2, 0.3], [0.7, 0.8, 0.9]])
+    same_get(a, b)
+    assert a == ([], [])
+
+
+def test_find_similar_keys(pair):  # stores_test.go:183-203
+    both(pair, "StoresSet", [[0.5, 0.5, 0.5], [0.6, 0.6, -0.6], [0.7, -0.7, -0.7]], [b"test1", b"test2", b"test3"])
+    a, b = both(pair, "StoresFind", [0.1, 0.3, 0.5], 2)
+    same_find(a, b)
+    ks, vs, sims = a
+    assert np.array_equal(ks[0], np.array([0.5, 0.5, 0.5], f32)) and vs[0] == b"test1"
+    assert np.array_equal(ks[1], np.array([0.6, 0.6, -0.6], f32))
+    assert pair[0].last_path == pair[1].last_path == "fallback"
+    assert sims[0] == f32(0.8783101) and sims[1] == f32(-0.09759001)
+
+
+def test_find_similar_normalized_keys(pair):  # stores_test.go:205-232
+    keys = normalize_rows([[0.1, 0.3, 0.5], [0.5, 0.5, 0.5], [0.6, 0.6, -0.6], [0.7, -0.7, -0.7]])
+    both(pair, "StoresSet", keys, [b"test0", b"test1", b"test2", b"test3"])
+    a, b = both(pair, "StoresFind", keys[0], 3)
+    same_find(a, b)
+    ks, vs, sims = a
+    assert pair[0].last_path == "normalized"
+    assert np.array_equal(ks[0], keys[0]) and vs[0] == b"test0" and abs(float(sims[0]) - 1) < 1e-4
+    assert np.array_equal(ks[1], keys[1]) and vs[1] == b"test1"
+
+
+def test_orthogonal_and_opposite_unit_vectors_exact(pair):  # stores_test.go:234-244
+    keys = [[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0], [-1.0, 0.0, 0.0]]
+    both(pair, "StoresSet", keys, [b"x", b"y", b"z", b"-z"])
+    (_, _, sims), (_, _, osims) = both(pair, "StoresFind", keys[0], 4)
+    assert np.array_equal(sims, np.array([1.0, 0.0, 0.0, -1.0], f32))
+    assert np.array_equal(sims, osims)
+
+
+def test_orthogonal_and_opposite_vectors(pair):  # stores_test.go:246-259
+    keys = [[1.0, 0.0, 1.0], [0.0, 2.0, 0.0], [0.0, 0.0, -1.0], [-1.0, 0.0, -1.0]]
+    both(pair, "StoresSet", keys, [b"x", b"y", b"z", b"-z"])
+    a, b = both(pair, "StoresFind", keys[0], 4)
+    same_find(a, b)
+    sims = a[2]
+    assert abs(sims[0] - 1) < 0.1 and abs(sims[1]) < 0.1 and abs(sims[2] + 0.7) < 0.1 and abs(sims[3] + 1) < 0.1
+
+
+def test_triangle_inequality_normalized(pair):  # stores_test.go:303-321
+    keys = np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [-1, 0, 0], [0, -1, 0], [0, 0, -1],
+                     [2, 3, 4], [9, 7, 1], [0, -1.2, 2.3]], f32)
+    keys[6:] = normalize_rows(keys[6:])
+    vals = [b"x", b"y", b"z", b"-x", b"-y", b"-z", b"u", b"v", b"w"]
+    both(pair, "StoresSet", keys, vals)
+    assert triangle_holds(pair[0], keys, vals)
+
+
+def test_triangle_inequality_random(pair):  # stores_test.go:323-348
+    rng = np.random.default_rng(151)
+    keys = rng.random((20, 768), dtype=f32)
+    vals = [bytes([ord("a") + i]) for i in range(20)]
+    both(pair, "StoresSet", keys, vals)
+    assert triangle_holds(pair[0], keys, vals)
+    for k in keys[:5]:  # and bit-exact against the oracle
+        a, b = both(pair, "StoresFind", k, 9)
+        assert np.array_equal(a[2], b[2])
+
+
+def test_http_app_sequence(pair):  # core/http/app_test.go:904-974
+    both(pair, "StoresSet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]], [b"test1", b"test2", b"test3"])
+    same_get(*both(pair, "StoresGet", [[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]]))
+    both(pair, "StoresDelete", [[0.1, 0.2, 0.3]])
+    a, b = both(pair, "StoresFind", [0.1, 0.3, 0.7], 10)
+    same_find(a, b)
+    assert len(a[0]) == 2 and a[1] == [b"test2", b"test3"]
+    assert a[2][0] == f32(0.90502065) and a[2][1] == f32(0.8786198)
+
+
+def test_error_texts_match_the_reference(tfp, oracle):
+    s, o = tfp.Store(), oracle.OracleStore()
+
+    def same_error(method, *args):
+        with pytest.raises(tfp.StoreError) as eg:
+            getattr(s, method)(*args)
+        with pytest.raises(oracle.OracleError) as eo:
+            getattr(o, method)(*args)
+        assert str(eg.value) == str(eo.value)
+        return str(eg.value)
+
+    assert "existing length is -1" in same_error("StoresFind", [1, 0, 0], 1)   # store.go:480-482
+    same_error("StoresSet", [], [])                                             # :107-109
+    same_error("StoresSet", [[1, 0, 0]], [b"a", b"b"])                          # :111-113
+    s.StoresSet([[1, 0, 0]], [b"a"]); o.StoresSet([[1, 0, 0]], [b"a"])
+    same_error("StoresSet", [[1, 0]], [b"a"])                                   # :118-120
+    same_error("StoresDelete", [])                                              # :201-203
+    same_error("StoresDelete", [[1, 0]])                                        # :212-214
+    same_error("StoresGet", [[1, 0]])                                           # :278-280
+    same_error("StoresFind", [1, 0], 1)                                         # :480-482
+    same_error("StoresFind", [1, 0, 0], 0)                                      # :484-486
+    same_error("StoresFind", [1, 0, 0], -5)
+    with pytest.raises(tfp.StoreError):   # documented deviation: the reference panics (store.go:276)
+        s.StoresGet([])
+    s.close()
+
+
+def test_sticky_flag_overwrite_duplicates(pair):
+    gpu, orc = pair
+    both(pair, "StoresSet", [[1, 0, 0]], [b"a"])
+    assert gpu.keys_are_normalized and orc.keys_are_normalized
+    both(pair, "StoresSet", [[2, 0, 0]], [b"b"])
+    assert not gpu.keys_are_normalized and not orc.keys_are_normalized
+    both(pair, "StoresDelete", [[2, 0, 0]])
+    assert not gpu.keys_are_normalized                     # never flips back (store.go:126-127)
+    both(pair, "StoresSet", [[1, 0, 0]], [b"c"])            # overwrite (store.go:183-187)
+    assert len(gpu) == len(orc) == 1
+    same_get(*both(pair, "StoresGet", [[1, 0, 0]]))
+    both(pair, "StoresSet", [[0, 1, 0], [0, 1, 0]], [b"d", b"d"])   # duplicates inside a batch are both kept
+    assert len(gpu) == len(orc) == 3
+    both(pair, "StoresSet", [[-0.0, 1, 0]], [b"d"])         # -0 == +0: replaces one of the two
+    assert len(gpu) == len(orc) == 3
+    a, b = both(pair, "StoresFind", [0, 1, 0], 10)          # TopK > N returns N
+    assert len(a[0]) == len(b[0]) == 3 and np.array_equal(a[2], b[2])
+    both(pair, "StoresDelete", [[0, 1, 0], [0, 1, 0], [0, 1, 0]])   # each stored row is consumed once
+    assert len(gpu) == len(orc) == 1
+
+
+def test_nan_keys_are_one_key(pair):  # cmp.Compare: NaN == NaN
+    nan = float("nan")
+    both(pair, "StoresSet", [[nan, 1, 0]], [b"a"])
+    both(pair, "StoresSet", [[nan, 1, 0]], [b"b"])
+    assert len(pair[0]) == len(pair[1]) == 1
+    same_get(*both(pair, "StoresGet", [[nan, 1, 0]]))
+
+
+def test_delete_latches_key_len_and_emptied_store_finds_nothing(pair):
+    gpu, orc = pair
+    both(pair, "StoresDelete", [[1, 2, 3]])                 # store.go:209-210
+    assert gpu.key_len == orc.key_len == 3
+    both(pair, "StoresSet", [[1, 0, 0]], [b"a"])
+    both(pair, "StoresDelete", [[1, 0, 0]])
+    a, b = both(pair, "StoresFind", [1, 0, 0], 3)
+    assert a[0] == [] and b[0] == [] and len(a[2]) == 0
+
+
+def test_random_mutation_stream_matches_oracle(pair):
+    """Interleaved set / overwrite / delete / get / find on a small key universe."""
+    gpu, orc = pair
+    rng = np.random.default_rng(7)
+    universe = normalize_rows(rng.standard_normal((60, 36)).astype(f32))
+    for step in range(40):
+        op = rng.integers(0, 4)
+        pick = rng.choice(60, size=int(rng.integers(1, 9)), replace=False)
+        ks = universe[pick]
+        if op == 0 or len(gpu) == 0:
+            vals = [b"v%d_%d" % (step, i) for i in pick]
+            both(pair, "StoresSet", ks, vals)
+        elif op == 1:
+            both(pair, "StoresDelete", ks)
+        elif op == 2:
+            same_get(*both(pair, "StoresGet", ks))
+        else:
+            a, b = both(pair, "StoresFind", ks[0], int(rng.integers(1, 12)))
+            same_find(a, b)
+        assert len(gpu) == len(orc)
