@@ -38,6 +38,8 @@ typedef struct {
     int64_t  capacity_rows;  /* initial HBM reservation in rows; 0 = default, grows on use */
     uint32_t flags;          /* TFP_FLAG_*                                                  */
     uint32_t reserved;
+    int64_t  id_base;        /* first id this store hands out (shards of one logical store
+                                use disjoint ranges, e.g. rank << 40)                      */
 } tfp_cfg;
 
 #define TFP_FLAG_NONE 0u
@@ -119,6 +121,11 @@ typedef struct {
 } tfp_stats;
 int tfp_store_stats(tfp_store* s, tfp_stats* out);
 
+/* A shard of a logical multi-GPU store is told that another shard has seen a key that
+ * is not unit length: the sticky flag (store.go:27,126-127) is a property of the whole
+ * store, so every shard must leave the normalised path together. */
+int tfp_store_mark_not_normalized(tfp_store* s);
+
 /* ---- find contexts: the asynchronous, device-resident face of StoresFind ------
  * A context owns a CUDA stream, staged queries in HBM, scratch for the
  * per-CTA candidate lists and device-resident results.  It exists so that
@@ -144,19 +151,30 @@ void* tfp_find_ctx_stream(tfp_find_ctx* c);
  * (score-order word << 32 | ~slot), ids[count x topk], sims[count x topk], n[count]. */
 int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids,
                                  float** d_sims, int** d_n);
+/* Enqueue the gather of the last launch's winning key rows and return their device
+ * address: [count x stride x dim] floats, stride as returned by
+ * tfp_find_ctx_device_results (what StoresFindResult.Keys is built from). */
+int  tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys);
 /* Number of kernels the context has launched so far (for bench accounting). */
 int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c);
 
 /* ---- cross-shard merge (no reference counterpart) ------------------
- * After an all-gather of every shard's (sims, ids, n) for one launch, pick the
- * global top-k per query on the device.  gathered_*: [n_shards x nq x topk]
- * (n: [n_shards x nq]) in HBM; outputs [nq x topk] / [nq] in HBM; also reports
- * the winning shard and the index inside that shard's list.  Ties: lower shard,
- * then that shard's own order.  stream is a cudaStream_t (NULL = default). */
-int tfp_merge_candidates(const float* d_gathered_sims, const int64_t* d_gathered_ids,
-                         const int* d_gathered_n, int n_shards, int nq, int topk,
-                         float* d_out_sims, int64_t* d_out_ids, int* d_out_shard,
-                         int* d_out_index, int* d_out_n, void* stream);
+ * Every launch also writes one fixed-size RECORD per query, so that a multi-GPU host
+ * can move a shard's whole answer with ONE all-gather:
+ *     int32 n; int32 reserved; int64 ids[topk]; float sims[topk]; (padded to 16 bytes)
+ * topk is the caller's topk (not min(topk, rows)), so records have the same size on
+ * every shard.  tfp_record_bytes gives that size. */
+size_t tfp_record_bytes(int topk);
+/* Device address of the last launch's records ([count] records) and their size. */
+int tfp_find_ctx_device_records(tfp_find_ctx* c, void** d_records, size_t* record_bytes);
+/* After an all-gather of every shard's records for one launch (layout
+ * [n_shards x nq] records in HBM), pick the global top-k per query on the device.
+ * Outputs [nq x topk] / [nq] in HBM; also reports the winning shard and the index
+ * inside that shard's list.  Ties: lower shard, then that shard's own order.
+ * stream is a cudaStream_t (NULL = default stream). */
+int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk,
+                      float* d_out_sims, int64_t* d_out_ids, int* d_out_shard,
+                      int* d_out_index, int* d_out_n, void* stream);
 
 /* Build/version string (contains the SM target the kernels were built for). */
 const char* tfp_version(void);

@@ -9,7 +9,8 @@ _LIB = os.path.join(_HERE, "libtfpstore.so")
 
 
 class TfpCfg(C.Structure):
-    _fields_ = [("device", C.c_int), ("capacity_rows", C.c_int64), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+    _fields_ = [("device", C.c_int), ("capacity_rows", C.c_int64), ("flags", C.c_uint32), ("reserved", C.c_uint32),
+                ("id_base", C.c_int64)]
 
 
 class TfpStats(C.Structure):
@@ -35,6 +36,7 @@ PROTOTYPES = {
     "tfp_store_find": (C.c_int, [vp, fp, C.c_int, C.c_int, i32p, i64p, fp, fp, i32p]),
     "tfp_store_find_batch": (C.c_int, [vp, fp, C.c_int, C.c_int, C.c_int, i32p, i64p, fp, fp]),
     "tfp_store_stats": (C.c_int, [vp, C.POINTER(TfpStats)]),
+    "tfp_store_mark_not_normalized": (C.c_int, [vp]),
     "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_destroy": (None, [vp]),
     "tfp_find_ctx_upload": (C.c_int, [vp, fp, C.c_int, C.c_int]),
@@ -43,8 +45,11 @@ PROTOTYPES = {
     "tfp_find_ctx_sync": (C.c_int, [vp]),
     "tfp_find_ctx_stream": (vp, [vp]),
     "tfp_find_ctx_device_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+    "tfp_find_ctx_gather_keys": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_launch_count": (C.c_int64, [vp]),
-    "tfp_merge_candidates": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
+    "tfp_record_bytes": (C.c_size_t, [C.c_int]),
+    "tfp_find_ctx_device_records": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
+    "tfp_merge_records": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
     "tfp_version": (C.c_char_p, []),
 }
 

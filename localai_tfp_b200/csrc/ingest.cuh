@@ -119,23 +119,24 @@ __global__ void gather_rows_kernel(const float* __restrict__ keys, int dim, cons
 }
 
 // Cross-shard merge: one CTA per query, bitonic sort of
-// n_shards x topk words (sim order, then lower shard, then position).
-__global__ void merge_candidates_kernel(const float* __restrict__ g_sims, const int64_t* __restrict__ g_ids,
-                                        const int* __restrict__ g_n, int n_shards, int nq, int topk, int P,
-                                        float* __restrict__ o_sims, int64_t* __restrict__ o_ids,
-                                        int* __restrict__ o_shard, int* __restrict__ o_index, int* __restrict__ o_n) {
+// n_shards x topk words (sim order, then lower shard, then position).  Input is the
+// all-gathered block of packed records, [n_shards x nq] records of rec_bytes each.
+__global__ void merge_records_kernel(const uint8_t* __restrict__ g, int rec_bytes, int n_shards, int nq, int topk, int P,
+                                     float* __restrict__ o_sims, int64_t* __restrict__ o_ids,
+                                     int* __restrict__ o_shard, int* __restrict__ o_index, int* __restrict__ o_n) {
     extern __shared__ uint64_t mbuf[];
     const int q = blockIdx.x;
     const int total = n_shards * topk;
+    auto rec = [&](int sh) { return g + ((size_t)sh * nq + q) * rec_bytes; };
     for (int i = threadIdx.x; i < P; i += blockDim.x) {
         uint64_t w = 0ull;
         if (i < total) {
             int sh = i / topk, j = i - sh * topk;
-            if (j < g_n[sh * nq + q]) {
-                float s = g_sims[((size_t)sh * nq + q) * topk + j];
+            const uint8_t* r = rec(sh);
+            if (j < *(const int*)r) {
+                float s = ((const float*)(r + 8 + (size_t)topk * 8))[j];
                 // low word: earlier (shard, position) ranks higher among equal scores
                 w = ((uint64_t)score_to_order(s) << 32) | (uint64_t)(0xFFFFFFFFu - (uint32_t)i);
-                if (w == 0ull) w = 1ull;
             }
         }
         mbuf[i] = w;
@@ -153,16 +154,19 @@ __global__ void merge_candidates_kernel(const float* __restrict__ g_sims, const 
         }
     }
     int valid = 0;
-    for (int sh = 0; sh < n_shards; sh++) valid += g_n[sh * nq + q];
+    for (int sh = 0; sh < n_shards; sh++) {
+        int c = *(const int*)rec(sh);
+        valid += c < topk ? c : topk;
+    }
     const int m = valid < topk ? valid : topk;
     for (int i = threadIdx.x; i < topk; i += blockDim.x) {
         size_t at = (size_t)q * topk + i;
         if (i < m) {
             uint32_t pos = 0xFFFFFFFFu - (uint32_t)mbuf[i];
             int sh = (int)(pos / (uint32_t)topk), j = (int)(pos - (uint32_t)sh * topk);
-            size_t from = ((size_t)sh * nq + q) * topk + j;
-            o_sims[at] = g_sims[from];
-            o_ids[at] = g_ids[from];
+            const uint8_t* r = rec(sh);
+            o_sims[at] = ((const float*)(r + 8 + (size_t)topk * 8))[j];
+            o_ids[at] = ((const int64_t*)(r + 8))[j];
             o_shard[at] = sh;
             o_index[at] = j;
         } else {

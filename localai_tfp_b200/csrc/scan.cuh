@@ -28,6 +28,7 @@ constexpr int kStageBytes = kRowsPerTile * kBoxCols * 4;   // 16 KiB
 constexpr int kScanThreads = kRowsPerTile + 32;            // consumers + producer warp
 constexpr int kMaxStages = 12;
 constexpr int kMaxNQ = 8;
+constexpr int kMaxGrid = 512;                              // upper bound on CTAs per scan launch
 
 struct QInfo {        // per staged query, filled on the host (exact reference arithmetic)
     double mag1;      // store.go:435-439
@@ -62,6 +63,9 @@ struct ScanParams {
     float* out_sims;          // [* x topk]
     uint32_t* out_slots;      // [* x topk]
     int* out_n;               // [*]
+    uint8_t* out_rec;         // [*] packed records (include/tfp_store.h), rec_bytes each, rec_topk slots
+    int rec_bytes;
+    int rec_topk;
 };
 
 // ---- per-row arithmetic ----------------------------------------------------
@@ -100,14 +104,24 @@ struct ScanSmem {
     unsigned long long* tau;     // NQ
     int* cnt;                    // NQ
     int* flag;                   // 1
+    int* pref;                   // kMaxGrid + 1 (last-CTA merge: prefix of survivor counts)
 };
+// Packed per-query record: int32 n; int32 reserved; int64 ids[topk]; float sims[topk]; padded to 16.
+__host__ __device__ inline size_t record_bytes(int topk) {
+    return ((size_t)8 + (size_t)topk * 12 + 15) & ~(size_t)15;
+}
+__device__ __forceinline__ void record_write(uint8_t* rec, int rec_topk, int i, int64_t id, float sim) {
+    ((int64_t*)(rec + 8))[i] = id;
+    ((float*)(rec + 8 + (size_t)rec_topk * 8))[i] = sim;
+}
+
 __host__ __device__ inline size_t scan_smem_bytes(int n_stages, int nq, int dpad, int cap) {
     size_t b = (size_t)n_stages * kStageBytes;
     b += (size_t)nq * dpad * 4;
     b = (b + 15) & ~(size_t)15;
     b += (size_t)nq * cap * 8;
     b += (size_t)(2 * n_stages + 1) * 8;
-    b += (size_t)nq * 8 + (size_t)nq * 4 + 16;
+    b += (size_t)nq * 8 + (size_t)nq * 4 + 16 + (size_t)(kMaxGrid + 1) * 4;
     return b + 1024;  // slack for the 1024-byte alignment of the stage ring
 }
 __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int nq, int dpad, int cap) {
@@ -123,14 +137,15 @@ __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int n
     s.qbar = (uint64_t*)p; p += 8;
     s.tau = (unsigned long long*)p; p += (size_t)nq * 8;
     s.cnt = (int*)p; p += (size_t)nq * 4;
-    s.flag = (int*)p;
+    s.flag = (int*)p; p += 4;
+    s.pref = (int*)p;
     return s;
 }
 
 // ---- epilogue shared by the TMA and the generic kernel -----------------------
 // Called by the kSelThreads consumer threads after the CTA's last tile.
 template <int NQ>
-__device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int tid) {
+__device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int* pref, int tid) {
     const int k = p.topk;
     // 1. final local prune, then publish this CTA's survivors
     for (int q = 0; q < NQ; q++) {
@@ -168,11 +183,37 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
     if (tid < NQ) { unsigned long long t = *sel[tid].tau; *sel[tid].tau = t ? t - 1 : 0ull; }
     named_bar_sync(kSelBarrier, kSelThreads);
     for (int q = 0; q < NQ; q++) {
-        for (unsigned b = 0; b < gridDim.x; b++) {
-            if (b == blockIdx.x) continue;
-            int m = ((volatile int*)p.part_cnt)[b * kMaxNQ + q];
-            const uint64_t* src = p.part + ((size_t)b * kMaxNQ + q) * k;
-            for (int i = tid; i < m; i += kSelThreads) sel_offer(sel[q], __ldcg(src + i));
+        // Flatten the other CTAs' lists: pref[b] = number of survivors in CTAs < b.  All loads of
+        // one round are independent, so the merge costs a few L2 round trips, not one per CTA.
+        const int grid = (int)gridDim.x;
+        for (int b = tid; b < grid; b += kSelThreads)
+            pref[b + 1] = (b == (int)blockIdx.x) ? 0 : __ldcg(p.part_cnt + b * kMaxNQ + q);
+        if (tid == 0) pref[0] = 0;
+        named_bar_sync(kSelBarrier, kSelThreads);
+        if (tid < 32) {   // inclusive scan of pref[1..grid] by warp 0
+            const int per = (grid + 31) / 32;
+            int lo = 1 + tid * per, hi = lo + per;
+            if (hi > grid + 1) hi = grid + 1;
+            int sum = 0;
+            for (int i = lo; i < hi; i++) sum += pref[i];
+            int incl = sum;
+            for (int d = 1; d < 32; d <<= 1) {
+                int v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                if (tid >= d) incl += v;
+            }
+            int run = incl - sum;
+            for (int i = lo; i < hi; i++) { run += pref[i]; pref[i] = run; }
+        }
+        named_bar_sync(kSelBarrier, kSelThreads);
+        const int total = pref[grid];
+        const int room = sel[q].room;
+        for (int base = 0; base < total; base += room) {
+            const int stop = base + room < total ? base + room : total;
+            for (int i = base + tid; i < stop; i += kSelThreads) {
+                int lo = 0, hi = grid;   // largest b with pref[b] <= i
+                while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (pref[mid] <= i) lo = mid; else hi = mid; }
+                sel_offer(sel[q], __ldcg(p.part + ((size_t)lo * kMaxNQ + q) * k + (i - pref[lo])));
+            }
             named_bar_sync(kSelBarrier, kSelThreads);
             sel_maybe_prune(sel[q], nullptr, tid);
         }
@@ -184,10 +225,12 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             if (i < m) {
                 uint64_t c = sel[q].buf[i];
                 uint32_t slot = cand_slot(c);
+                const int64_t id = p.ids[slot];
                 p.out_cand[at] = c;
                 p.out_sims[at] = cand_score(c);
                 p.out_slots[at] = slot;
-                p.out_ids[at] = p.ids[slot];
+                p.out_ids[at] = id;
+                record_write(p.out_rec + (size_t)o * p.rec_bytes, p.rec_topk, i, id, cand_score(c));
             } else {
                 p.out_cand[at] = 0ull;
                 p.out_sims[at] = 0.0f;
@@ -197,6 +240,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         }
         if (tid == 0) {
             p.out_n[o] = m;
+            *(int*)(p.out_rec + (size_t)o * p.rec_bytes) = m;
             p.gtau[q] = 0ull;   // leave the scratch clean for the next launch on this context
         }
     }
@@ -211,7 +255,7 @@ __device__ __forceinline__ void sel_setup(const ScanParams& p, const ScanSmem& s
         sel[q].tau = sm.tau + q;
         sel[q].cap = p.cap;
         sel[q].k = p.topk;
-        sel[q].room = p.topk > kRowsPerTile ? p.topk : kRowsPerTile;
+        sel[q].room = p.topk > 2 * kRowsPerTile ? p.topk : 2 * kRowsPerTile;
     }
     if (tid < NQ) { sm.cnt[tid] = 0; sm.tau[tid] = 0ull; }
 }
@@ -356,7 +400,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
         tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
     }
-    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, tid);
+    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid);
 }
 
 // ---- the generic kernel: any dim (dim % 4 != 0, dim < 32, or a query too long
@@ -372,6 +416,7 @@ scan_generic_kernel(const ScanParams p) {
     sm.tau = (unsigned long long*)(base + (size_t)NQ * p.cap * 8);
     sm.cnt = (int*)(sm.tau + NQ);
     sm.flag = sm.cnt + NQ;
+    sm.pref = sm.flag + 1;
     const int tid = threadIdx.x;
     SelState sel[NQ];
     sel_setup<NQ>(p, sm, sel, tid);
@@ -402,26 +447,28 @@ scan_generic_kernel(const ScanParams p) {
         for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
         tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
     }
-    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, tid);
+    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid);
 }
 __host__ inline size_t scan_generic_smem_bytes(int nq, int cap) {
-    return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + 32;
+    return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + (size_t)(kMaxGrid + 1) * 4 + 32;
 }
 
 // ---- big-k path, pass 2: decode the first k of the (already sorted) spill -------
 __global__ void decode_sorted_kernel(const uint64_t* sorted, uint32_t n_rows, int k, const int64_t* ids, int o,
                                      uint64_t* out_cand, int64_t* out_ids, float* out_sims, uint32_t* out_slots,
-                                     int* out_n) {
+                                     int* out_n, uint8_t* out_rec, int rec_bytes, int rec_topk) {
     const int m = (uint32_t)k < n_rows ? k : (int)n_rows;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < k; i += gridDim.x * blockDim.x) {
         size_t at = (size_t)o * k + i;
         if (i < m) {
             uint64_t c = sorted[i];
             uint32_t slot = cand_slot(c);
+            const int64_t id = ids[slot];
             out_cand[at] = c;
             out_sims[at] = cand_score(c);
             out_slots[at] = slot;
-            out_ids[at] = ids[slot];
+            out_ids[at] = id;
+            record_write(out_rec + (size_t)o * rec_bytes, rec_topk, i, id, cand_score(c));
         } else {
             out_cand[at] = 0ull;
             out_sims[at] = 0.0f;
@@ -429,7 +476,7 @@ __global__ void decode_sorted_kernel(const uint64_t* sorted, uint32_t n_rows, in
             out_ids[at] = -1;
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) out_n[o] = m;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { out_n[o] = m; *(int*)(out_rec + (size_t)o * rec_bytes) = m; }
 }
 
 }  // namespace tfp

@@ -143,7 +143,7 @@ struct tfp_find_ctx {
     PinBuf h_in, h_out;
     DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket
     DevBuf all_cand, sorted_cand, cub_tmp;
-    DevBuf out_cand, out_ids, out_sims, out_slots, out_n, out_keys;
+    DevBuf out_cand, out_ids, out_sims, out_slots, out_n, out_keys, out_rec;
     int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
     int64_t launches = 0;
 };
@@ -213,7 +213,6 @@ static int optin_all(int bytes) {
     CU_OK((optin_gen<4, false, false>(bytes))); CU_OK((optin_gen<4, true, false>(bytes)));
     CU_OK((optin_gen<8, false, false>(bytes))); CU_OK((optin_gen<8, true, false>(bytes)));
     CU_OK((optin_gen<1, false, true>(bytes)));  CU_OK((optin_gen<1, true, true>(bytes)));
-    CU_OK(cudaFuncSetAttribute(merge_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
     return 0;
 }
 
@@ -234,6 +233,7 @@ extern "C" int tfp_store_open(const tfp_cfg* cfg, tfp_store** out) {
     tfp_store* s = new tfp_store();
     s->device = cfg ? cfg->device : 0;
     s->cap_hint = cfg ? cfg->capacity_rows : 0;
+    s->next_id = cfg ? cfg->id_base : 0;
     if (s->device < 0 || s->device >= ndev) { delete s; return fail(2, "device %d out of range (have %d)", cfg->device, ndev); }
     if (set_device(s)) { delete s; return -1; }
     cudaDeviceProp prop;
@@ -278,6 +278,13 @@ extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
     out->keys_are_normalized = s->normalized ? 1 : 0;
     out->device = s->device;
     out->reserved = 0;
+    return 0;
+}
+
+extern "C" int tfp_store_mark_not_normalized(tfp_store* s) {
+    if (!s) return fail(2, "tfp_store_mark_not_normalized: store is NULL");
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    s->normalized = false;
     return 0;
 }
 
@@ -583,7 +590,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     tfp_store* s = c->st;
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     DevBuf* bufs[] = {&c->d_q, &c->d_qinfo, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
-                      &c->cub_tmp, &c->out_cand, &c->out_ids, &c->out_sims, &c->out_slots, &c->out_n, &c->out_keys};
+                      &c->cub_tmp, &c->out_cand, &c->out_ids, &c->out_sims, &c->out_slots, &c->out_n, &c->out_keys, &c->out_rec};
     for (DevBuf* b : bufs) b->release();
     c->h_in.release();
     c->h_out.release();
@@ -681,6 +688,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     if (c->dim != s->dim)                                                            // store.go:480-482
         return fail(1, "Try to find key with length %d when existing length is %d", c->dim, s->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
+    if ((int64_t)topk > (int64_t)1 << 26) topk = 1 << 26;   // more than any shard can hold; keeps record sizes sane
     if (first < 0 || count <= 0 || first + count > c->nq) return fail(2, "find: query range [%d,%d) outside the %d staged queries", first, first + count, c->nq);
     const int64_t n = s->n;
     const int ksel = (int)std::min<int64_t>((int64_t)topk, std::max<int64_t>(n, 1));
@@ -691,17 +699,20 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     size_t slots = (size_t)count * ksel;
     if (c->out_cand.reserve(slots * 8) || c->out_ids.reserve(slots * 8) || c->out_sims.reserve(slots * 4) ||
         c->out_slots.reserve(slots * 4) || c->out_n.reserve((size_t)count * 4)) return -1;
+    const size_t rec_bytes = record_bytes(topk);
+    if (c->out_rec.reserve((size_t)count * rec_bytes)) return -1;
     if (n == 0) {   // written-then-emptied store: empty result
         CU_OK(cudaMemsetAsync(c->out_n.p, 0, (size_t)count * 4, c->stream));
+        CU_OK(cudaMemsetAsync(c->out_rec.p, 0, (size_t)count * rec_bytes, c->stream));
         return 0;
     }
     const int dim = s->dim;
     const bool fused = ksel <= TFP_FUSED_TOPK_MAX;
     const int n_chunks = (dim + kBoxCols - 1) / kBoxCols;
     const int dpad = n_chunks * kBoxCols;
-    const int cap = fused ? std::max(512, next_pow2(ksel + std::max(ksel, kRowsPerTile))) : 2;
+    const int cap = fused ? std::max(512, next_pow2(ksel + std::max(ksel, 2 * kRowsPerTile))) : 2;
     const uint32_t n_tiles = (uint32_t)((n + kRowsPerTile - 1) / kRowsPerTile);
-    const int grid = (int)std::min<uint32_t>((uint32_t)s->sm_count, n_tiles);
+    const int grid = (int)std::min<uint32_t>((uint32_t)std::min(s->sm_count, kMaxGrid), n_tiles);
 
     ScanParams p;
     memset(&p, 0, sizeof(p));
@@ -714,6 +725,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     p.ticket = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ);
     p.out_cand = c->out_cand.as<uint64_t>(); p.out_ids = c->out_ids.as<int64_t>();
     p.out_sims = c->out_sims.as<float>(); p.out_slots = c->out_slots.as<uint32_t>(); p.out_n = c->out_n.as<int>();
+    p.out_rec = c->out_rec.as<uint8_t>(); p.rec_bytes = (int)rec_bytes; p.rec_topk = topk;
 
     if (fused) {
         if (c->part.reserve((size_t)grid * kMaxNQ * ksel * 8) || c->part_cnt.reserve((size_t)grid * kMaxNQ * 4)) return -1;
@@ -738,7 +750,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
         size_t smem = 0;
         for (;;) {
             if (use_tma) {
-                size_t fixed = scan_smem_bytes(0, g, dpad, cap);
+                size_t fixed = scan_smem_bytes(0, g, dpad, cap) + 2 * kMaxStages * 8;
                 int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
                 n_stages = std::min(kMaxStages, room);
                 if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, dpad, cap); break; }
@@ -769,7 +781,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
                                                            c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
             decode_sorted_kernel<<<std::min(1024, (ksel + 255) / 256), 256, 0, c->stream>>>(
                 c->sorted_cand.as<uint64_t>(), (uint32_t)n, ksel, s->d_ids, i, p.out_cand, p.out_ids, p.out_sims,
-                p.out_slots, p.out_n);
+                p.out_slots, p.out_n, p.out_rec, p.rec_bytes, p.rec_topk);
             CU_OK(cudaGetLastError());
             c->launches += 2;
         }
@@ -783,6 +795,33 @@ extern "C" int tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int to
     std::shared_lock<std::shared_mutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     return ctx_launch_locked(c, first, count, topk);
+}
+
+// Enqueue the gather of the winning rows of the last launch into c->out_keys.
+static int ctx_gather_locked(tfp_find_ctx* c) {
+    tfp_store* s = c->st;
+    const int count = c->last_count, ks = c->last_stride, dim = s->dim;
+    size_t slots = (size_t)count * ks;
+    if (c->out_keys.reserve(slots * dim * 4)) return -1;
+    if (s->n == 0) return 0;
+    dim3 grid((unsigned)ks, (unsigned)count);
+    int threads = dim >= 256 ? 256 : (dim >= 64 ? 64 : 32);
+    gather_rows_kernel<<<grid, threads, 0, c->stream>>>(s->d_keys, dim, c->out_slots.as<uint32_t>(), c->out_n.as<int>(),
+                                                       ks, c->out_keys.as<float>());
+    CU_OK(cudaGetLastError());
+    c->launches++;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys) {
+    if (!c || !d_keys) return fail(2, "tfp_find_ctx_gather_keys: NULL argument");
+    if (c->last_count <= 0) return fail(2, "tfp_find_ctx_gather_keys: nothing was launched on this context");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    int rc = ctx_gather_locked(c);
+    if (rc) return rc;
+    *d_keys = c->out_keys.as<float>();
+    return 0;
 }
 
 static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys) {
@@ -800,13 +839,7 @@ static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, fl
         CU_OK(cudaMemcpyAsync(h + off_ids, c->out_ids.p, slots * 8, cudaMemcpyDeviceToHost, c->stream));
         CU_OK(cudaMemcpyAsync(h + off_sims, c->out_sims.p, slots * 4, cudaMemcpyDeviceToHost, c->stream));
         if (out_keys) {
-            if (c->out_keys.reserve(slots * dim * 4)) return -1;
-            dim3 grid((unsigned)ks, (unsigned)count);
-            int threads = dim >= 256 ? 256 : (dim >= 64 ? 64 : 32);
-            gather_rows_kernel<<<grid, threads, 0, c->stream>>>(s->d_keys, dim, c->out_slots.as<uint32_t>(),
-                                                               c->out_n.as<int>(), ks, c->out_keys.as<float>());
-            CU_OK(cudaGetLastError());
-            c->launches++;
+            if (ctx_gather_locked(c)) return -1;
             CU_OK(cudaMemcpyAsync(h + off_keys, c->out_keys.p, slots * dim * 4, cudaMemcpyDeviceToHost, c->stream));
         }
     }
@@ -877,19 +910,29 @@ extern "C" int tfp_store_find(tfp_store* s, const float* q, int dim, int topk, i
 // ---------------------------------------------------------------------------
 // cross-shard merge
 // ---------------------------------------------------------------------------
-extern "C" int tfp_merge_candidates(const float* d_sims, const int64_t* d_ids, const int* d_n, int n_shards, int nq,
-                                    int topk, float* o_sims, int64_t* o_ids, int* o_shard, int* o_index, int* o_n,
-                                    void* stream) {
-    if (!d_sims || !d_ids || !d_n || !o_sims || !o_ids || !o_shard || !o_index || !o_n)
-        return fail(2, "tfp_merge_candidates: NULL argument");
-    if (n_shards < 1 || nq < 1 || topk < 1) return fail(2, "tfp_merge_candidates: bad sizes");
+extern "C" size_t tfp_record_bytes(int topk) { return record_bytes(topk < 0 ? 0 : topk); }
+
+extern "C" int tfp_find_ctx_device_records(tfp_find_ctx* c, void** d_records, size_t* rec_bytes) {
+    if (!c || !d_records || !rec_bytes) return fail(2, "tfp_find_ctx_device_records: NULL argument");
+    if (c->last_count <= 0) return fail(2, "tfp_find_ctx_device_records: nothing was launched on this context");
+    *d_records = c->out_rec.p;
+    *rec_bytes = record_bytes(c->last_topk);
+    return 0;
+}
+
+extern "C" int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk, float* o_sims, int64_t* o_ids,
+                                 int* o_shard, int* o_index, int* o_n, void* stream) {
+    if (!d_gathered || !o_sims || !o_ids || !o_shard || !o_index || !o_n)
+        return fail(2, "tfp_merge_records: NULL argument");
+    if (n_shards < 1 || nq < 1 || topk < 1) return fail(2, "tfp_merge_records: bad sizes");
     int64_t total = (int64_t)n_shards * topk;
-    if (total > 16384) return fail(2, "tfp_merge_candidates: n_shards x topk = %lld exceeds 16384", (long long)total);
+    if (total > 16384) return fail(2, "tfp_merge_records: n_shards x topk = %lld exceeds 16384", (long long)total);
     int P = next_pow2((int)std::max<int64_t>(total, 2));
     if ((size_t)P * 8 > 48 * 1024)
-        CU_OK(cudaFuncSetAttribute(merge_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
-    merge_candidates_kernel<<<nq, 256, (size_t)P * 8, (cudaStream_t)stream>>>(d_sims, d_ids, d_n, n_shards, nq, topk, P,
-                                                                              o_sims, o_ids, o_shard, o_index, o_n);
+        CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
+    merge_records_kernel<<<nq, 256, (size_t)P * 8, (cudaStream_t)stream>>>((const uint8_t*)d_gathered,
+                                                                           (int)record_bytes(topk), n_shards, nq, topk, P,
+                                                                           o_sims, o_ids, o_shard, o_index, o_n);
     CU_OK(cudaGetLastError());
     return 0;
 }

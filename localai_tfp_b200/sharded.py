@@ -1,0 +1,309 @@
+"""Key-set sharding across the GPUs of one box: one process per GPU, each
+holding one shard of the store; a find scans every shard, all-gathers the per-shard
+(similarity, id) candidates with torch.distributed (NCCL over NVLink on GPUs) and merges them
+with `tfp_merge_candidates` on the device.
+
+The reference has no counterpart (backend/go/stores/store.go is single-process, single-thread);
+the observable behaviour is that of ONE `Store` holding the union of the shards:
+StoresSet / StoresDelete / StoresGet / StoresFind with the reference's semantics.
+
+Every rank calls every method with the same arguments (SPMD).  Keys are routed to their owner
+rank by a hash of their canonical bits, so exact-match operations touch one shard only.
+
+The device work is behind a small `ShardOps` interface so that the routing / gather / assembly
+logic can be exercised on CPU with the gloo backend (tests/ supplies a CPU double of ShardOps);
+the product implementation below is CUDA-only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Sequence
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from .store import Store, StoreError
+
+ID_SHIFT = 40  # shard r hands out ids in [r << 40, (r + 1) << 40)
+
+
+def canonical_bits(keys: np.ndarray) -> np.ndarray:
+    """uint32 view of fp32 keys with Go's cmp.Compare equality folded in: -0 -> +0, any NaN -> one NaN."""
+    k = np.ascontiguousarray(keys, dtype=np.float32)
+    bits = k.view(np.uint32).copy()
+    bits[(bits & 0x7FFFFFFF) > 0x7F800000] = 0x7FC00000
+    bits[bits == 0x80000000] = 0
+    return bits
+
+
+def owner_of(keys: np.ndarray, world: int) -> np.ndarray:
+    """Owner rank of each key row: a multiplicative hash of the canonical bits, mod world."""
+    bits = canonical_bits(keys).astype(np.uint64)
+    d = bits.shape[1]
+    mult = (np.arange(1, d + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)) | np.uint64(1)
+    with np.errstate(over="ignore"):
+        h = (bits * mult[None, :]).sum(axis=1, dtype=np.uint64)
+        h ^= h >> np.uint64(29)
+        h *= np.uint64(0xBF58476D1CE4E5B9)
+        h ^= h >> np.uint64(32)
+    return (h % np.uint64(world)).astype(np.int64)
+
+
+def record_bytes(topk: int) -> int:
+    """Size of one packed per-query record (include/tfp_store.h): n, ids[topk], sims[topk], padded to 16."""
+    return (8 + 12 * topk + 15) & ~15
+
+
+def pack_record(n: int, ids: np.ndarray, sims: np.ndarray, topk: int) -> np.ndarray:
+    buf = np.zeros(record_bytes(topk), np.uint8)
+    buf[:4] = np.array([n], np.int32).view(np.uint8)
+    buf[8:8 + 8 * topk] = np.ascontiguousarray(ids, np.int64).view(np.uint8)
+    buf[8 + 8 * topk:8 + 12 * topk] = np.ascontiguousarray(sims, np.float32).view(np.uint8)
+    return buf
+
+
+def unpack_record(buf: np.ndarray, topk: int):
+    n = int(buf[:4].view(np.int32)[0])
+    ids = buf[8:8 + 8 * topk].view(np.int64)
+    sims = buf[8 + 8 * topk:8 + 12 * topk].view(np.float32)
+    return n, ids, sims
+
+
+class _DevArray:
+    """A raw device pointer dressed as __cuda_array_interface__ so torch can alias it (zero copy)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2}
+
+
+def _alias(ptr: int, shape, typestr: str, device) -> torch.Tensor:
+    return torch.as_tensor(_DevArray(ptr, shape, typestr), device=device)
+
+
+class CudaShardOps:
+    """Device work of one shard: the local store, its find context, and the merge kernel."""
+
+    def __init__(self, rank: int, device: int, capacity_rows: int = 0):
+        self.store = Store(device=device, capacity_rows=capacity_rows, id_base=rank << ID_SHIFT)
+        self.device = torch.device("cuda", device)
+        self.ctx = self.store.find_context()
+        self._L = self.store._L
+        self._stream = torch.cuda.ExternalStream(self.ctx.stream, device=self.device)
+
+    def stream(self):
+        """Everything a find enqueues (scan, collectives, merge) is ordered on the context's stream."""
+        return torch.cuda.stream(self._stream)
+
+    # exact-match operations
+    def set(self, keys, values):
+        return self.store.StoresSet(keys, values)
+
+    def delete(self, keys):
+        return self.store.StoresDelete(keys)
+
+    def get(self, keys):
+        return self.store.StoresGet(keys)
+
+    def rows(self):
+        return len(self.store)
+
+    def key_len(self):
+        return self.store.key_len
+
+    def keys_are_normalized(self):
+        return self.store.keys_are_normalized
+
+    def mark_not_normalized(self):
+        self.store.mark_not_normalized()
+
+    def latch(self, dim: int):
+        """Fix the key length of a shard that may own no key yet.  A delete on an empty store
+        latches keyLen and removes nothing (store.go:209-210), which is exactly what is needed."""
+        if self.store.key_len == -1:
+            self.store.StoresDelete(np.zeros((1, dim), np.float32))
+
+    def stage_queries(self, qs: np.ndarray):
+        self.ctx.upload(qs)
+
+    def find_local(self, qi: int, topk: int, with_keys: bool):
+        """Scan this shard for staged query qi.  Returns (record, keys): the packed result record as a
+        uint8 device tensor that aliases the library's buffer, and, if asked, the matching key rows
+        [topk, dim] (zero padded)."""
+        self.ctx.launch(qi, 1, topk)
+        ptr, nbytes = self.ctx.device_records()
+        dev = self.device
+        rec = _alias(ptr, (nbytes,), "|u1", dev)
+        keys = None
+        if with_keys:
+            d = max(self.key_len(), 1)
+            keys = torch.zeros((topk, d), dtype=torch.float32, device=dev)
+            if self.rows() > 0:
+                stride = min(topk, self.rows())
+                keys[:stride] = _alias(self.ctx.gather_keys(), (stride, d), "<f4", dev)
+        return rec, keys
+
+    def merge(self, g_rec, world: int, topk: int):
+        dev = self.device
+        o_sims = torch.empty(topk, dtype=torch.float32, device=dev)
+        o_ids = torch.empty(topk, dtype=torch.int64, device=dev)
+        o_shard = torch.empty(topk, dtype=torch.int32, device=dev)
+        o_index = torch.empty(topk, dtype=torch.int32, device=dev)
+        o_n = torch.empty(1, dtype=torch.int32, device=dev)
+        st = torch.cuda.current_stream(dev)
+        rc = self._L.tfp_merge_records(g_rec.data_ptr(), world, 1, topk, o_sims.data_ptr(), o_ids.data_ptr(),
+                                       o_shard.data_ptr(), o_index.data_ptr(), o_n.data_ptr(),
+                                       C.c_void_p(st.cuda_stream))
+        self.store._check(rc)
+        return o_sims, o_ids, o_shard, o_index, o_n
+
+    def close(self):
+        self.ctx.close()
+        self.store.close()
+
+
+class ShardedStore:
+    """One logical store over `world` shards.  SPMD: every rank makes the same calls."""
+
+    def __init__(self, ops, rank: int, world: int, group=None):
+        self.ops = ops
+        self.rank = rank
+        self.world = world
+        self.group = group
+        self.values = {}           # id -> bytes, replicated on every rank (values are tiny; store.go:23)
+        self.key_len = -1          # store.go:29,44
+        self.keys_are_normalized = True
+        self.last_path = None
+
+    # -- helpers -------------------------------------------------------------
+    def _pack(self, keys):
+        if isinstance(keys, np.ndarray) and keys.ndim == 2:
+            return np.ascontiguousarray(keys, dtype=np.float32)
+        ks = [np.asarray(k, dtype=np.float32).reshape(-1) for k in keys]
+        if not ks:
+            return np.zeros((0, 1), np.float32)
+        d = len(ks[0])
+        for k in ks:
+            if len(k) != d:
+                raise StoreError(f"Try to add key with length {len(k)} when existing length is {d}")
+        return np.ascontiguousarray(np.stack(ks), dtype=np.float32)
+
+    def _latch(self, d: int, fmt: str):
+        if self.key_len == -1:
+            self.key_len = d
+            self.ops.latch(d)
+        elif d != self.key_len:
+            raise StoreError(fmt % (d, self.key_len))
+
+    def _allgather_obj(self, obj):
+        out = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    def __len__(self):
+        return int(sum(self._allgather_obj(self.ops.rows())))
+
+    # -- StoresSet (store.go:106-198) ------------------------------------------
+    def StoresSet(self, keys, values: Sequence[bytes]):
+        ks = self._pack(keys)
+        if len(ks) == 0:
+            raise StoreError("no keys to add")
+        if len(ks) != len(values):
+            raise StoreError(f"len(keys) = {len(ks)}, len(values) = {len(values)}")
+        self._latch(ks.shape[1], "Try to add key with length %d when existing length is %d")
+        own = owner_of(ks, self.world)
+        mine = np.nonzero(own == self.rank)[0]
+        local = []
+        if len(mine):
+            ids, _ = self.ops.set(ks[mine], [values[i] for i in mine])
+            local = [(int(i), int(ids[j])) for j, i in enumerate(mine)]
+        for part in self._allgather_obj(local):   # replicate id -> value everywhere
+            for i, gid in part:
+                self.values[gid] = bytes(values[i])
+        flags = self._allgather_obj(bool(self.ops.keys_are_normalized()))
+        if not all(flags):
+            # the sticky flag (store.go:126-127) belongs to the whole store: every shard leaves
+            # the normalised path together, or scores from different shards would not compare
+            self.keys_are_normalized = False
+            self.ops.mark_not_normalized()
+
+    # -- StoresDelete (store.go:200-264) ----------------------------------------
+    def StoresDelete(self, keys):
+        ks = self._pack(keys)
+        if len(ks) == 0:
+            raise StoreError("no keys to delete")
+        self._latch(ks.shape[1], "Trying to delete key with length %d when existing length is %d")
+        own = owner_of(ks, self.world)
+        mine = np.nonzero(own == self.rank)[0]
+        gone = []
+        if len(mine):
+            ids = self.ops.delete(ks[mine])
+            gone = [int(g) for g in ids if g >= 0]
+        for part in self._allgather_obj(gone):
+            for gid in part:
+                self.values.pop(gid, None)
+
+    # -- StoresGet (store.go:266-311) --------------------------------------------
+    def StoresGet(self, keys):
+        ks = self._pack(keys)
+        if len(ks) == 0:
+            raise StoreError("no keys to get")
+        self._latch(ks.shape[1], "Try to get a key with length %d when existing length is %d")
+        own = owner_of(ks, self.world)
+        mine = np.nonzero(own == self.rank)[0]
+        found = []
+        if len(mine) and self.ops.rows() > 0:
+            fk, fv = self.ops.get(ks[mine])
+            found = [(k.tobytes(), v) for k, v in zip(fk, fv)]
+        allf = [item for part in self._allgather_obj(found) for item in part]
+        rows = [np.frombuffer(kb, dtype=np.float32) for kb, _ in allf]
+        order = sorted(range(len(rows)), key=lambda i: _go_sort_key(rows[i]))   # sorted-key order, store.go:269
+        return [rows[i].copy() for i in order], [allf[i][1] for i in order]
+
+    # -- StoresFind (store.go:477-511) ---------------------------------------------
+    def StoresFind(self, key, topk: int, with_keys: bool = True):
+        q = np.ascontiguousarray(np.asarray(key, dtype=np.float32).reshape(-1))
+        if len(q) != self.key_len:
+            raise StoreError(f"Try to find key with length {len(q)} when existing length is {self.key_len}")
+        if topk < 1:
+            raise StoreError(f"opts.TopK = {topk}, must be >= 1")
+        self.ops.stage_queries(q[None, :])
+        with self.ops.stream():
+            sims, ids, shard, index, n, g_keys = self.find_device(0, int(topk), with_keys)
+            m = int(n.item())
+        sims_h = sims[:m].cpu().numpy()
+        ids_h = ids[:m].cpu().numpy()
+        out_keys = []
+        if with_keys and m:
+            sh = shard[:m].long()
+            ix = index[:m].long()
+            out_keys = [r.copy() for r in g_keys[sh, ix].cpu().numpy()]
+        return out_keys, [self.values.get(int(i)) for i in ids_h], sims_h
+
+    def find_device(self, qi: int, topk: int, with_keys: bool = False):
+        """Scan + all-gather + merge for staged query qi; results stay on the device (what bench.py
+        times).  Call inside `with self.ops.stream():` so the collectives follow the scan."""
+        rec, keys = self.ops.find_local(qi, topk, with_keys)
+        # ONE collective per query: every shard's whole answer is one fixed-size record
+        g_rec = torch.empty(self.world * rec.numel(), dtype=torch.uint8, device=rec.device)
+        dist.all_gather_into_tensor(g_rec, rec, group=self.group)
+        g_keys = None
+        if with_keys:
+            g_keys = torch.empty(self.world * keys.numel(), dtype=keys.dtype, device=keys.device)
+            dist.all_gather_into_tensor(g_keys, keys.contiguous().view(-1), group=self.group)
+            g_keys = g_keys.view((self.world,) + tuple(keys.shape))
+        o_sims, o_ids, o_shard, o_index, o_n = self.ops.merge(g_rec, self.world, topk)
+        return o_sims, o_ids, o_shard, o_index, o_n, g_keys
+
+    def close(self):
+        self.ops.close()
+
+
+def _go_sort_key(row: np.ndarray):
+    """Sort key reproducing Go's cmp.Compare order on float32 rows: NaN lowest, -0 == +0."""
+    out = []
+    for x in row:
+        x = float(x)
+        out.append((0, 0.0) if x != x else (1, x + 0.0))
+    return tuple(out)

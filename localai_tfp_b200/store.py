@@ -54,9 +54,9 @@ def _p(a: np.ndarray, t):
 class Store:
     """One store shard resident on one B200."""
 
-    def __init__(self, device: int = 0, capacity_rows: int = 0):
+    def __init__(self, device: int = 0, capacity_rows: int = 0, id_base: int = 0):
         self._L = _lib.load()
-        cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0)
+        cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0, id_base=id_base)
         h = C.c_void_p()
         rc = self._L.tfp_store_open(C.byref(cfg), C.byref(h))
         if rc:
@@ -194,6 +194,9 @@ class Store:
         res = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy()) for i in range(nq)]
         return (res, outk) if with_keys else res
 
+    def mark_not_normalized(self):
+        self._check(self._L.tfp_store_mark_not_normalized(self._h))
+
     def find_context(self) -> "FindContext":
         return FindContext(self)
 
@@ -255,6 +258,18 @@ class FindContext:
     @property
     def launch_count(self) -> int:
         return int(self._L.tfp_find_ctx_launch_count(self._h))
+
+    def gather_keys(self) -> int:
+        """Enqueue the gather of the winning rows; returns the device address of [count, stride, dim] fp32."""
+        p = C.c_void_p()
+        self.store._check(self._L.tfp_find_ctx_gather_keys(self._h, C.byref(p)))
+        return p.value
+
+    def device_records(self):
+        """(device address, record_bytes) of the last launch's packed per-query records."""
+        p, nb = C.c_void_p(), C.c_size_t()
+        self.store._check(self._L.tfp_find_ctx_device_records(self._h, C.byref(p), C.byref(nb)))
+        return p.value, nb.value
 
     def device_results(self):
         """(stride, cand_ptr, ids_ptr, sims_ptr, n_ptr): device addresses of the last launch's results."""

@@ -1,0 +1,86 @@
+"""Worker body for the multi-process sharded-store tests (gloo on CPU, nccl on GPUs)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def scenario(store, single, rank):
+    """Drive the sharded store and a single oracle store with the same calls; compare everything."""
+    from conftest import make_keys
+    f32 = np.float32
+    K = make_keys(400, 48, seed=5, normalized=True)
+    vals = [b"v%d" % i for i in range(len(K))]
+    store.StoresSet(K[:300], vals[:300]); single.StoresSet(K[:300], vals[:300])
+    assert len(store) == len(single) == 300
+    assert store.keys_are_normalized
+
+    def same_find(q, k):
+        a = store.StoresFind(q, k); b = single.StoresFind(q, k)
+        assert np.array_equal(a[2], b[2]), (rank, a[2], b[2])
+        assert a[1] == b[1], (rank, a[1], b[1])
+        assert len(a[0]) == len(b[0]) and all(np.array_equal(x, y) for x, y in zip(a[0], b[0]))
+
+    for qi in (0, 7, 299, 350):
+        same_find(K[qi], 10)
+    same_find(K[3], 500)                      # TopK > N
+    same_find((K[3] * f32(2)).astype(f32), 5)  # non-unit query: fallback path on every shard
+    # get: sorted-key order across shards, missing keys dropped
+    ask = K[[250, 10, 399, 77]]
+    a = store.StoresGet(ask); b = single.StoresGet(ask)
+    assert a[1] == b[1] and all(np.array_equal(x, y) for x, y in zip(a[0], b[0]))
+    # overwrite + delete
+    store.StoresSet(K[10:12], [b"new10", b"new11"]); single.StoresSet(K[10:12], [b"new10", b"new11"])
+    store.StoresDelete(K[100:200]); single.StoresDelete(K[100:200])
+    assert len(store) == len(single) == 200
+    same_find(K[10], 3)
+    same_find(K[150], 10)
+    # one non-unit key on ONE shard flips the whole store to the fallback path (sticky)
+    big = (K[399:400] * f32(3)).astype(f32)
+    store.StoresSet(big, [b"big"]); single.StoresSet(big, [b"big"])
+    assert not store.keys_are_normalized
+    for qi in (0, 7, 399):
+        same_find(K[qi], 10)
+    store.StoresDelete(big); single.StoresDelete(big)
+    assert not store.keys_are_normalized
+    same_find(K[1], 4)
+    # errors carry the reference's texts
+    from localai_tfp_b200 import StoreError
+    for fn, args, text in ((store.StoresFind, (K[0][:5], 3), "Try to find key with length 5 when existing length is 48"),
+                           (store.StoresFind, (K[0], 0), "opts.TopK = 0, must be >= 1"),
+                           (store.StoresSet, ([], []), "no keys to add"),
+                           (store.StoresDelete, ([],), "no keys to delete")):
+        try:
+            fn(*args)
+            raise AssertionError("no error")
+        except StoreError as e:
+            assert str(e) == text, str(e)
+
+
+def run(rank, world, port, backend):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    try:
+        from localai_tfp_b200.sharded import ShardedStore
+        from oracle import oracle as orc
+        if backend == "gloo":
+            from sharded_double import CpuShardOps
+            ops = CpuShardOps(rank)
+        else:
+            from localai_tfp_b200.sharded import CudaShardOps
+            torch.cuda.set_device(rank)
+            ops = CudaShardOps(rank, rank)
+        store = ShardedStore(ops, rank, world)
+        scenario(store, orc.OracleStore(), rank)
+        store.close()
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()

@@ -29,13 +29,13 @@ def same_find(a, b):
     (ka, va, sa), (kb, vb, sb) = a, b
     assert np.array_equal(sa, sb), f"{sa} vs {sb}"
     assert va == vb
-    assert len(ka) == len(kb) and all(np.array_equal(x, y) for x, y in zip(ka, kb))
+    assert len(ka) == len(kb) and all(np.array_equal(x, y, equal_nan=True) for x, y in zip(ka, kb))
 
 
 def same_get(a, b):
     (ka, va), (kb, vb) = a, b
     assert va == vb
-    assert len(ka) == len(kb) and all(np.array_equal(x, y) for x, y in zip(ka, kb))
+    assert len(ka) == len(kb) and all(np.array_equal(x, y, equal_nan=True) for x, y in zip(ka, kb))
 
 
 def test_set_a_key(pair):  # stores_test.go:86-89
