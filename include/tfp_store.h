@@ -176,6 +176,44 @@ int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk,
                       float* d_out_sims, int64_t* d_out_ids, int* d_out_shard,
                       int* d_out_index, int* d_out_n, void* stream);
 
+/* ---- a find that allocates nothing ----------------------------------------------
+ * This entry point has no counterpart in the reference.
+ *
+ * Some hosts must not cause a device allocation while they serve requests: a
+ * runtime that has already handed all of HBM to its own arena (an LLM or
+ * embedding server sharing the GPU with the store) has nothing left for the
+ * driver to give, and a latency-critical loop cannot afford cudaMalloc /
+ * cudaFree, which synchronise the whole device.  Every other find in this
+ * header may grow a buffer the first time it sees a larger top-k or query count.
+ * This one never does: it calls no cudaMalloc, cudaFree or allocating library
+ * routine.  It runs the same scan + fused top-k kernel as tfp_store_find on the
+ * normalised path (fp32 index-order dot, store.go:327-339) over a key matrix
+ * the CALLER owns, and its scratch (per-CTA candidate lists, counters, the
+ * packed record) lives in a fixed array inside the library image:
+ * TFP_NOALLOC_SCRATCH_BYTES of device memory that every GPU which loads the
+ * library holds until the process exits.
+ *
+ * d_keys [n_rows x dim] fp32 row-major, d_ids [n_rows], d_query [dim]: inputs in
+ * the current device's memory.  d_out_sims / d_out_ids [topk], d_out_n [1]:
+ * outputs in device memory, written in stream order (descending similarity,
+ * *d_out_n = min(topk, n_rows) valid entries, ties: lower row first).
+ * Limits, checked and reported through tfp_last_error(): 1 <= topk <=
+ * TFP_NOALLOC_TOPK_MAX, 1 <= dim <= TFP_NOALLOC_DIM_MAX, n_rows < 2^32 - 16.
+ * The first call on each device looks up the scratch array's device address
+ * and opts the kernels into large shared memory; make that first call with the
+ * device current and before starting any stream capture.  All calls on one
+ * device share the one scratch array: the library clears the words that must
+ * start at zero on every call, but two calls whose kernels overlap on the GPU
+ * (different streams, no ordering between them) race on it -- order them.
+ * stream is a cudaStream_t (NULL = default stream); the call returns without
+ * waiting for the GPU. */
+#define TFP_NOALLOC_TOPK_MAX 64
+#define TFP_NOALLOC_DIM_MAX 8192
+#define TFP_NOALLOC_SCRATCH_BYTES (672 * 1024)
+int tfp_scan_topk_noalloc(const float* d_keys, int64_t n_rows, int dim, const int64_t* d_ids,
+                          const float* d_query, int topk,
+                          float* d_out_sims, int64_t* d_out_ids, int* d_out_n, void* stream);
+
 /* Build/version string (contains the SM target the kernels were built for). */
 const char* tfp_version(void);
 

@@ -50,6 +50,7 @@ PROTOTYPES = {
     "tfp_record_bytes": (C.c_size_t, [C.c_int]),
     "tfp_find_ctx_device_records": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "tfp_merge_records": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
+    "tfp_scan_topk_noalloc": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp]),
     "tfp_version": (C.c_char_p, []),
 }
 

@@ -936,3 +936,142 @@ extern "C" int tfp_merge_records(const void* d_gathered, int n_shards, int nq, i
     CU_OK(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// tfp_scan_topk_noalloc: the same scan + fused top-k, with every byte of scratch in a
+// fixed array that is part of the library image (see include/tfp_store.h for who needs
+// this and why).  Nothing below may call cudaMalloc, cudaFree or anything that allocates.
+// ---------------------------------------------------------------------------
+constexpr int kNoAllocMaxGrid = 160;   // CTAs per launch are capped so the candidate lists fit the fixed array
+struct NoAllocLayout {                 // byte offsets inside g_noalloc_scratch
+    static constexpr size_t part = 0;                                                        // [grid x kMaxNQ x topk] u64
+    static constexpr size_t part_cnt = part + (size_t)kNoAllocMaxGrid * kMaxNQ * TFP_NOALLOC_TOPK_MAX * 8;
+    static constexpr size_t sync_words = part_cnt + (size_t)kNoAllocMaxGrid * kMaxNQ * 4;    // gtau[kMaxNQ] + ticket
+    static constexpr size_t out_cand = sync_words + 128;
+    static constexpr size_t out_slots = out_cand + (size_t)TFP_NOALLOC_TOPK_MAX * 8;
+    static constexpr size_t out_rec = out_slots + (size_t)TFP_NOALLOC_TOPK_MAX * 4;
+    static constexpr size_t qinfo = out_rec + 1024;
+    static constexpr size_t end = qinfo + 64;
+};
+static_assert(NoAllocLayout::end <= TFP_NOALLOC_SCRATCH_BYTES, "the fixed scratch array is too small for its layout");
+
+// In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device address.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[TFP_NOALLOC_SCRATCH_BYTES];
+
+struct NoAllocDevice {
+    bool ready = false;
+    unsigned char* scratch = nullptr;   // device address of g_noalloc_scratch on this device
+    int sm_count = 0;
+    int max_smem = 0;
+};
+static NoAllocDevice g_noalloc_dev[64];
+static std::mutex g_noalloc_mu;
+
+// Once per device, with that device current: resolve the array's device address, read the
+// device limits, opt the kernels into large dynamic shared memory.  None of it allocates.
+static int noalloc_setup(int dev, NoAllocDevice** out) {
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    NoAllocDevice& d = g_noalloc_dev[dev];
+    if (!d.ready) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(-1, "cudaGetSymbolAddress(g_noalloc_scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+        int cc_major = 0;
+        CU_OK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+        if (cc_major != 10) return fail(-1, "device %d is not sm_100; libtfpstore is built for sm_100a (B200) only", dev);
+        CU_OK(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+        CU_OK(cudaDeviceGetAttribute(&d.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        CU_OK((optin_tma<1, false, false>(d.max_smem)));
+        CU_OK((optin_gen<1, false, false>(d.max_smem)));
+        d.scratch = (unsigned char*)ptr;
+        d.ready = true;
+    }
+    *out = &d;
+    return 0;
+}
+
+extern "C" int tfp_scan_topk_noalloc(const float* d_keys, int64_t n_rows, int dim, const int64_t* d_ids,
+                                     const float* d_query, int topk, float* d_out_sims, int64_t* d_out_ids,
+                                     int* d_out_n, void* stream) {
+    if (!d_keys || !d_ids || !d_query || !d_out_sims || !d_out_ids || !d_out_n)
+        return fail(2, "tfp_scan_topk_noalloc: NULL argument");
+    if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);
+    if (topk > TFP_NOALLOC_TOPK_MAX)
+        return fail(2, "tfp_scan_topk_noalloc: topk = %d exceeds TFP_NOALLOC_TOPK_MAX = %d (the scratch array is fixed)",
+                    topk, TFP_NOALLOC_TOPK_MAX);
+    if (dim < 1 || dim > TFP_NOALLOC_DIM_MAX)
+        return fail(2, "tfp_scan_topk_noalloc: dim = %d outside [1, TFP_NOALLOC_DIM_MAX = %d]", dim, TFP_NOALLOC_DIM_MAX);
+    if (n_rows < 0 || n_rows >= 0xFFFFFFF0ll)
+        return fail(2, "tfp_scan_topk_noalloc: n_rows = %lld outside [0, 2^32 - 16)", (long long)n_rows);
+    int dev = 0;
+    CU_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(2, "tfp_scan_topk_noalloc: device ordinal %d not supported", dev);
+    NoAllocDevice* nd = nullptr;
+    if (noalloc_setup(dev, &nd)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_rows == 0) {
+        CU_OK(cudaMemsetAsync(d_out_n, 0, sizeof(int), st));
+        return 0;
+    }
+    unsigned char* base = nd->scratch;   // the address from cudaGetSymbolAddress, never the host-side symbol
+    const int ksel = (int)std::min<int64_t>((int64_t)topk, n_rows);
+    const int n_chunks = (dim + kBoxCols - 1) / kBoxCols;
+    const int dpad = n_chunks * kBoxCols;
+    const int cap = std::max(512, next_pow2(ksel + std::max(ksel, 2 * kRowsPerTile)));
+    const uint32_t n_tiles = (uint32_t)((n_rows + kRowsPerTile - 1) / kRowsPerTile);
+    const int grid = (int)std::min<uint32_t>((uint32_t)std::min(nd->sm_count, kNoAllocMaxGrid), n_tiles);
+
+    ScanParams p;
+    memset(&p, 0, sizeof(p));
+    p.keys = d_keys; p.ids = d_ids; p.knorm = nullptr;
+    p.n_rows = (uint32_t)n_rows; p.dim = dim; p.n_chunks = n_chunks;
+    p.topk = ksel; p.cap = cap;
+    p.evict_first = ((size_t)n_rows * dim * 4 > ((size_t)96 << 20)) ? 1 : 0;
+    p.q = d_query; p.qinfo = (const QInfo*)(base + NoAllocLayout::qinfo);   // not read on the fp32 path
+    p.q_first = 0; p.out_first = 0;
+    p.part = (uint64_t*)(base + NoAllocLayout::part);
+    p.part_cnt = (int*)(base + NoAllocLayout::part_cnt);
+    p.gtau = (unsigned long long*)(base + NoAllocLayout::sync_words);
+    p.ticket = (unsigned int*)(base + NoAllocLayout::sync_words + kMaxNQ * 8);
+    p.out_cand = (uint64_t*)(base + NoAllocLayout::out_cand);
+    p.out_slots = (uint32_t*)(base + NoAllocLayout::out_slots);
+    p.out_rec = base + NoAllocLayout::out_rec;
+    p.rec_bytes = (int)record_bytes(ksel); p.rec_topk = ksel;
+    p.out_ids = d_out_ids; p.out_sims = d_out_sims; p.out_n = d_out_n;
+
+    // The array keeps whatever the previous call left.  The grid-wide bounds and the ticket must
+    // start at zero; everything else is written before it is read.
+    CU_OK(cudaMemsetAsync(base + NoAllocLayout::sync_words, 0, (kMaxNQ + 1) * 8, st));
+
+    // TMA needs 16-byte aligned rows and a box that fits the tensor; otherwise the generic kernel.
+    bool use_tma = dim >= kBoxCols && (dim % 4) == 0 && n_rows >= kRowsPerTile &&
+                   (((uintptr_t)d_keys | (uintptr_t)d_query) & 15) == 0;
+    int n_stages = 0;
+    size_t smem = 0;
+    if (use_tma) {
+        size_t fixed = scan_smem_bytes(0, 1, dpad, cap) + 2 * kMaxStages * 8;
+        n_stages = std::min(kMaxStages, ((int)nd->max_smem - (int)fixed) / kStageBytes);
+        if (n_stages >= 3) smem = scan_smem_bytes(n_stages, 1, dpad, cap);
+        else use_tma = false;
+    }
+    if (use_tma) {
+        if (get_encoder()) return -2;
+        CUtensorMap tmap;
+        cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)n_rows};
+        cuuint64_t gstride[1] = {(cuuint64_t)dim * 4};
+        cuuint32_t box[2] = {(cuuint32_t)kBoxCols, (cuuint32_t)kRowsPerTile};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = g_encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)d_keys, gdim, gstride, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+        p.n_stages = n_stages;
+        scan_tma_kernel<1, false, false><<<grid, kScanThreads, smem, st>>>(tmap, p);
+    } else {
+        smem = scan_generic_smem_bytes(1, cap);
+        scan_generic_kernel<1, false, false><<<grid, kSelThreads, smem, st>>>(p);
+    }
+    CU_OK(cudaGetLastError());
+    return 0;
+}
