@@ -56,6 +56,7 @@ struct ScanParams {
     int* part_cnt;            // [grid x kMaxNQ]
     unsigned long long* gtau; // [kMaxNQ] grid-wide admission bounds
     unsigned int* ticket;     // [1]
+    unsigned int* tile_counter; // [1] dynamic tile scheduler: next tile = gridDim.x + counter++
     uint64_t* all_cand;       // big-k path: [kMaxNQ? no: 1 x n_rows] every row's candidate word
     // outputs, indexed by out_first + query
     uint64_t* out_cand;       // [* x topk]
@@ -105,6 +106,7 @@ struct ScanSmem {
     int* cnt;                    // NQ
     int* flag;                   // 1
     int* pref;                   // kMaxGrid + 1 (last-CTA merge: prefix of survivor counts)
+    uint32_t* tile_id;           // n_stages: which tile the stage's first chunk belongs to
 };
 // Packed per-query record: int32 n; int32 reserved; int64 ids[topk]; float sims[topk]; padded to 16.
 __host__ __device__ inline size_t record_bytes(int topk) {
@@ -121,7 +123,7 @@ __host__ __device__ inline size_t scan_smem_bytes(int n_stages, int nq, int dpad
     b = (b + 15) & ~(size_t)15;
     b += (size_t)nq * cap * 8;
     b += (size_t)(2 * n_stages + 1) * 8;
-    b += (size_t)nq * 8 + (size_t)nq * 4 + 16 + (size_t)(kMaxGrid + 1) * 4;
+    b += (size_t)nq * 8 + (size_t)nq * 4 + 16 + (size_t)(kMaxGrid + 1) * 4 + (size_t)kMaxStages * 4;
     return b + 1024;  // slack for the 1024-byte alignment of the stage ring
 }
 __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int nq, int dpad, int cap) {
@@ -138,7 +140,8 @@ __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int n
     s.tau = (unsigned long long*)p; p += (size_t)nq * 8;
     s.cnt = (int*)p; p += (size_t)nq * 4;
     s.flag = (int*)p; p += 4;
-    s.pref = (int*)p;
+    s.pref = (int*)p; p += (size_t)(kMaxGrid + 1) * 4;
+    s.tile_id = (uint32_t*)p;
     return s;
 }
 
@@ -244,7 +247,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             p.gtau[q] = 0ull;   // leave the scratch clean for the next launch on this context
         }
     }
-    if (tid == 0) *p.ticket = 0u;
+    if (tid == 0) { *p.ticket = 0u; *p.tile_counter = 0u; }
 }
 
 template <int NQ>
@@ -323,15 +326,27 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
             const uint64_t policy = p.evict_first ? l2_policy_evict_first() : l2_policy_evict_normal();
             int stage = 0;
             uint32_t phase = 0;
-            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            // Dynamic tile scheduler: SMs do not pull from HBM at equal rates (measured: busy time
+            // 712k..937k cycles under a static deal), so tiles are claimed from a grid-wide counter.
+            // The first tile is static; the next claim is issued a whole tile ahead, so the atomic's
+            // round trip is hidden behind ~9 us of TMA issue.
+            uint32_t tile = blockIdx.x;
+            while (tile < n_tiles) {
+                const uint32_t next = gridDim.x + atomicAdd(p.tile_counter, 1u);
                 for (int c = 0; c < p.n_chunks; c++) {
                     mbar_wait(sm.empty + stage, phase ^ 1u);
+                    if (c == 0) sm.tile_id[stage] = tile;   // published by the arrive below
                     mbar_arrive_expect_tx(sm.full + stage, kStageBytes);
                     tma_load_2d(sm.stages + (size_t)stage * kStageBytes, &tmap, sm.full + stage, c * kBoxCols,
                                 (int)(tile * kRowsPerTile), policy);
                     if (++stage == p.n_stages) { stage = 0; phase ^= 1u; }
                 }
+                tile = next;
             }
+            // end marker: a stage with no bytes whose tile id says "done"
+            mbar_wait(sm.empty + stage, phase ^ 1u);
+            sm.tile_id[stage] = 0xFFFFFFFFu;
+            mbar_arrive(sm.full + stage);
         }
         return;
     }
@@ -350,10 +365,13 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
     const uint32_t row_off = (uint32_t)tid * 128u;
     int stage = 0;
     uint32_t phase = 0;
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (;;) {
         Acc<F64> acc[NQ];
 #pragma unroll
         for (int q = 0; q < NQ; q++) acc[q].zero();
+        mbar_wait(sm.full + stage, phase);   // first chunk of the next tile, or the end marker
+        const uint32_t tile = sm.tile_id[stage];
+        if (tile == 0xFFFFFFFFu) break;
         const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
         const bool valid = row < p.n_rows;
         // issued now, consumed at the end of the tile: their latency hides behind the row walk
@@ -361,7 +379,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         unsigned long long g_seen = 0ull;
         if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
         for (int c = 0; c < p.n_chunks; c++) {
-            mbar_wait(sm.full + stage, phase);
+            if (c) mbar_wait(sm.full + stage, phase);
             const uint8_t* srow = sm.stages + (size_t)stage * kStageBytes + row_off;
             const float* qc = sm.q + c * kBoxCols;
             const int nvalid = p.dim - c * kBoxCols;  // >= 32 except in a ragged last chunk
