@@ -25,7 +25,7 @@ namespace tfp {
 
 constexpr int kBoxCols = 32;                               // floats per row per TMA box (128 B)
 constexpr int kStageBytes = kRowsPerTile * kBoxCols * 4;   // 16 KiB
-constexpr int kScanThreads = kRowsPerTile + 32;            // consumers + producer warp
+constexpr int kScanThreads = kRowsPerTile + 64;            // consumers + producer warp + bound-refresher warp
 constexpr int kMaxStages = 12;
 constexpr int kMaxNQ = 8;
 constexpr int kMaxGrid = 512;                              // upper bound on CTAs per scan launch
@@ -57,6 +57,10 @@ struct ScanParams {
     unsigned long long* gtau; // [kMaxNQ] grid-wide admission bounds
     unsigned int* ticket;     // [1]
     unsigned int* tile_counter; // [1] dynamic tile scheduler: next tile = gridDim.x + counter++
+    unsigned long long* lbest; // [kMaxNQ x lbest_stride] per-CTA "m-th best so far" (0 = not published)
+    int lbest_stride;
+    int m_local;              // ceil(topk / grid)
+    int refresh_ns;           // refresher warp's poll period; 0 = no refresher
     uint64_t* all_cand;       // big-k path: [kMaxNQ? no: 1 x n_rows] every row's candidate word
     // outputs, indexed by out_first + query
     uint64_t* out_cand;       // [* x topk]
@@ -107,6 +111,9 @@ struct ScanSmem {
     int* flag;                   // 1
     int* pref;                   // kMaxGrid + 1 (last-CTA merge: prefix of survivor counts)
     uint32_t* tile_id;           // n_stages: which tile the stage's first chunk belongs to
+    unsigned long long* ext;     // NQ: grid-wide bound kept fresh by the refresher warp
+    unsigned long long* lmax;    // NQ: best word this CTA has seen (published as lbest when m == 1)
+    int* done;                   // 1: consumers are finished, refresher may exit
 };
 // Packed per-query record: int32 n; int32 reserved; int64 ids[topk]; float sims[topk]; padded to 16.
 __host__ __device__ inline size_t record_bytes(int topk) {
@@ -124,6 +131,7 @@ __host__ __device__ inline size_t scan_smem_bytes(int n_stages, int nq, int dpad
     b += (size_t)nq * cap * 8;
     b += (size_t)(2 * n_stages + 1) * 8;
     b += (size_t)nq * 8 + (size_t)nq * 4 + 16 + (size_t)(kMaxGrid + 1) * 4 + (size_t)kMaxStages * 4;
+    b += (size_t)nq * 16 + 16;
     return b + 1024;  // slack for the 1024-byte alignment of the stage ring
 }
 __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int nq, int dpad, int cap) {
@@ -134,6 +142,8 @@ __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int n
     s.stages = p; p += (size_t)n_stages * kStageBytes;
     s.q = (float*)p; p += ((size_t)nq * dpad * 4 + 15) & ~(size_t)15;
     s.sel = (uint64_t*)p; p += (size_t)nq * cap * 8;
+    s.ext = (unsigned long long*)p; p += (size_t)nq * 8;
+    s.lmax = (unsigned long long*)p; p += (size_t)nq * 8;
     s.full = (uint64_t*)p; p += (size_t)n_stages * 8;
     s.empty = (uint64_t*)p; p += (size_t)n_stages * 8;
     s.qbar = (uint64_t*)p; p += 8;
@@ -141,23 +151,41 @@ __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int n
     s.cnt = (int*)p; p += (size_t)nq * 4;
     s.flag = (int*)p; p += 4;
     s.pref = (int*)p; p += (size_t)(kMaxGrid + 1) * 4;
-    s.tile_id = (uint32_t*)p;
+    s.tile_id = (uint32_t*)p; p += (size_t)kMaxStages * 4;
+    s.done = (int*)p;
     return s;
 }
 
+// min over the CTAs of the published "m-th best so far" words for query q, by one warp.
+// 0 while any CTA has not published yet (then it is no bound at all).
+__device__ __forceinline__ unsigned long long lbest_min(const ScanParams& p, int q, int lane) {
+    unsigned long long v = ~0ull;
+    const volatile unsigned long long* a = p.lbest + (size_t)q * p.lbest_stride;
+    for (int b = lane; b < (int)gridDim.x; b += 32) {
+        unsigned long long u = a[b];
+        v = u < v ? u : v;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, v, d);
+        v = o < v ? o : v;
+    }
+    return v;
+}
+
 // ---- epilogue shared by the TMA and the generic kernel -----------------------
-// Called by the kSelThreads consumer threads after the CTA's last tile.
+// Called by the kSelThreads consumer threads after the CTA's last tile.  big_buf/big_cap: a
+// larger buffer the last CTA may merge in (the TMA kernel lends its idle stage ring), or nullptr.
 template <int NQ>
-__device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int* pref, int tid) {
+__device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int* pref, int tid,
+                                              uint64_t* big_buf, int big_cap) {
     const int k = p.topk;
     // 1. final local prune, then publish this CTA's survivors
     for (int q = 0; q < NQ; q++) {
-        sel_prune(sel[q], p.gtau + q, tid);
+        sel_prune(sel[q], tid, true);
         int m = *sel[q].cnt;
-        unsigned long long bound = *sel[q].tau;   // includes the grid-wide bound seen so far
+        unsigned long long bound = *sel[q].tau;   // includes the grid-wide bounds seen so far
         uint64_t* dst = p.part + ((size_t)blockIdx.x * kMaxNQ + q) * k;
         // survivors are sorted descending, so those >= bound form a prefix
-        int keep = 0;
         for (int i = tid; i < m; i += kSelThreads) {
             uint64_t c = sel[q].buf[i];
             if (c >= bound) dst[i] = c;
@@ -165,8 +193,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         if (tid == 0) {
             int lo = 0, hi = m;   // first index with buf[i] < bound
             while (lo < hi) { int mid = (lo + hi) >> 1; if (sel[q].buf[mid] >= bound) lo = mid + 1; else hi = mid; }
-            keep = lo;
-            p.part_cnt[blockIdx.x * kMaxNQ + q] = keep;
+            p.part_cnt[blockIdx.x * kMaxNQ + q] = lo;
         }
     }
     __threadfence();
@@ -180,15 +207,23 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
     __threadfence();
 
     // 2. last CTA: merge every CTA's survivors (own list is already in sel[q].buf).
-    // tau may BE another CTA's k-th best (it travelled through gtau), and that row is
-    // part of the answer: admit words >= tau here, i.e. > tau - 1.  No word is offered
-    // twice (own rows are not re-offered), so equality can only be that one row.
+    // Every CTA's final bounds are visible now: fold them in.  tau may then BE another CTA's row
+    // (it travelled through gtau / lbest), and that row is part of the answer: admit words
+    // >= tau, i.e. > tau - 1.  No word is offered twice (own rows are not re-offered), so
+    // equality can only be that one row.
+    if (p.lbest && tid < 32) {
+        for (int q = 0; q < NQ; q++) {
+            unsigned long long v = lbest_min(p, q, tid);
+            if (tid == 0 && v > *sel[q].tau) *sel[q].tau = v;
+        }
+    }
+    named_bar_sync(kSelBarrier, kSelThreads);
     if (tid < NQ) { unsigned long long t = *sel[tid].tau; *sel[tid].tau = t ? t - 1 : 0ull; }
     named_bar_sync(kSelBarrier, kSelThreads);
+    const int grid = (int)gridDim.x;
     for (int q = 0; q < NQ; q++) {
         // Flatten the other CTAs' lists: pref[b] = number of survivors in CTAs < b.  All loads of
         // one round are independent, so the merge costs a few L2 round trips, not one per CTA.
-        const int grid = (int)gridDim.x;
         for (int b = tid; b < grid; b += kSelThreads)
             pref[b + 1] = (b == (int)blockIdx.x) ? 0 : __ldcg(p.part_cnt + b * kMaxNQ + q);
         if (tid == 0) pref[0] = 0;
@@ -209,24 +244,35 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         }
         named_bar_sync(kSelBarrier, kSelThreads);
         const int total = pref[grid];
-        const int room = sel[q].room;
+        // merge buffer: everything in ONE round in the lent buffer when it fits, else rounds in the
+        // query's own buffer (a huge survivor count means the bounds did not bite; rounds keep the
+        // sorts small)
+        SelState ms = sel[q];
+        ms.gtau = nullptr; ms.lbest = nullptr; ms.lmax = nullptr;
+        if (big_buf && big_cap >= 2 * sel[q].cap && *sel[q].cnt + total <= big_cap / 4) {
+            const int own = *sel[q].cnt;
+            for (int i = tid; i < own; i += kSelThreads) big_buf[i] = sel[q].buf[i];
+            ms.buf = big_buf; ms.cap = big_cap; ms.room = big_cap - k;
+            named_bar_sync(kSelBarrier, kSelThreads);
+        }
+        const int room = ms.room;
         for (int base = 0; base < total; base += room) {
             const int stop = base + room < total ? base + room : total;
             for (int i = base + tid; i < stop; i += kSelThreads) {
                 int lo = 0, hi = grid;   // largest b with pref[b] <= i
                 while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (pref[mid] <= i) lo = mid; else hi = mid; }
-                sel_offer(sel[q], __ldcg(p.part + ((size_t)lo * kMaxNQ + q) * k + (i - pref[lo])));
+                sel_offer(ms, __ldcg(p.part + ((size_t)lo * kMaxNQ + q) * k + (i - pref[lo])));
             }
             named_bar_sync(kSelBarrier, kSelThreads);
-            sel_maybe_prune(sel[q], nullptr, tid);
+            sel_maybe_prune(ms, tid, false);
         }
-        sel_prune(sel[q], nullptr, tid);
-        int m = *sel[q].cnt;
+        sel_prune(ms, tid, false);
+        int m = *ms.cnt;
         const int o = p.out_first + q;
         for (int i = tid; i < k; i += kSelThreads) {
             size_t at = (size_t)o * k + i;
             if (i < m) {
-                uint64_t c = sel[q].buf[i];
+                uint64_t c = ms.buf[i];
                 uint32_t slot = cand_slot(c);
                 const int64_t id = p.ids[slot];
                 p.out_cand[at] = c;
@@ -246,6 +292,9 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             *(int*)(p.out_rec + (size_t)o * p.rec_bytes) = m;
             p.gtau[q] = 0ull;   // leave the scratch clean for the next launch on this context
         }
+        if (p.lbest)
+            for (int b = tid; b < grid; b += kSelThreads) p.lbest[(size_t)q * p.lbest_stride + b] = 0ull;
+        named_bar_sync(kSelBarrier, kSelThreads);
     }
     if (tid == 0) { *p.ticket = 0u; *p.tile_counter = 0u; }
 }
@@ -259,14 +308,21 @@ __device__ __forceinline__ void sel_setup(const ScanParams& p, const ScanSmem& s
         sel[q].cap = p.cap;
         sel[q].k = p.topk;
         sel[q].room = p.topk > 2 * kRowsPerTile ? p.topk : 2 * kRowsPerTile;
+        sel[q].gtau = p.gtau + q;
+        sel[q].lbest = p.lbest ? p.lbest + (size_t)q * p.lbest_stride + blockIdx.x : nullptr;
+        sel[q].m_local = p.m_local;
+        sel[q].lmax = (sm.lmax && p.lbest && p.m_local == 1) ? sm.lmax + q : nullptr;
     }
     if (tid < NQ) { sm.cnt[tid] = 0; sm.tau[tid] = 0ull; }
 }
 
 // Offer one finished tile's scores and keep the buffers within capacity.
+// ext_bound (threads < NQ): a grid-wide lower bound of the k-th best for "their" query.
+// last_pub (threads < NQ): the lbest word this thread last published for its query.
 template <int NQ, bool SPILL>
 __device__ __forceinline__ void tile_offer(const ScanParams& p, SelState* sel, const float* score, uint32_t row,
-                                           bool valid, int tid, unsigned long long g_seen) {
+                                           bool valid, int tid, unsigned long long ext_bound,
+                                           unsigned long long& last_pub) {
     if constexpr (SPILL) {
         // big-k path: every row's candidate word goes to HBM, selection happens in a later pass
         if (valid) {
@@ -279,11 +335,16 @@ __device__ __forceinline__ void tile_offer(const ScanParams& p, SelState* sel, c
             for (int q = 0; q < NQ; q++) sel_offer(sel[q], pack_cand(score[q], row));
         }
         named_bar_sync(kSelBarrier, kSelThreads);
-        if (tid < NQ) {  // fold in the grid-wide bound read at the start of this tile
-            if (g_seen > *sel[tid].tau) *sel[tid].tau = g_seen;
+        if (tid < NQ) {
+            if (ext_bound > *sel[tid].tau) *sel[tid].tau = ext_bound;
+            // keep this CTA's published "best so far" fresh (m == 1; larger m publishes at prunes)
+            if (sel[tid].lmax && *sel[tid].lmax > last_pub) {
+                last_pub = *sel[tid].lmax;
+                *((volatile unsigned long long*)sel[tid].lbest) = last_pub;
+            }
         }
 #pragma unroll
-        for (int q = 0; q < NQ; q++) sel_maybe_prune(sel[q], p.gtau + q, tid);
+        for (int q = 0; q < NQ; q++) sel_maybe_prune(sel[q], tid, true);
     }
 }
 
@@ -305,7 +366,9 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         }
         mbar_init(sm.qbar, 1);
         fence_mbar_init();
+        *sm.done = 0;
     }
+    if (tid < NQ) { sm.ext[tid] = 0ull; sm.lmax[tid] = 0ull; }
     // zero the padded query tail (columns >= dim) before the bulk copies land
     for (int i = tid; i < NQ * dpad; i += kScanThreads) {
         int c = i % dpad;
@@ -350,6 +413,29 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         }
         return;
     }
+    if (warp == kRowsPerTile / 32 + 1) {
+        // ===================== bound-refresher warp =====================
+        // Polls the grid-wide bounds in HBM (gtau, and the min over CTAs of lbest) and keeps the
+        // freshest value in shared memory, so the consumer threads never wait on a global load.
+        if constexpr (!SPILL) {
+            const int lane = tid & 31;
+            if (p.refresh_ns <= 0) return;
+            for (;;) {
+                // one lane reads the flag and the warp follows it, so every lane leaves together
+                int d = (lane == 0) ? *((volatile int*)sm.done) : 0;
+                if (__shfl_sync(0xFFFFFFFFu, d, 0)) break;
+                for (int q = 0; q < NQ; q++) {
+                    unsigned long long v = p.lbest ? lbest_min(p, q, lane) : 0ull;
+                    if (lane == 0) {
+                        unsigned long long g = *((volatile unsigned long long*)(p.gtau + q));
+                        *((volatile unsigned long long*)(sm.ext + q)) = g > v ? g : v;
+                    }
+                }
+                __nanosleep((unsigned)p.refresh_ns);
+            }
+        }
+        return;
+    }
 
     // ========================= consumer threads: one row each =========================
     SelState sel[NQ];
@@ -365,6 +451,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
     const uint32_t row_off = (uint32_t)tid * 128u;
     int stage = 0;
     uint32_t phase = 0;
+    unsigned long long last_pub = 0ull;
     for (;;) {
         Acc<F64> acc[NQ];
 #pragma unroll
@@ -374,10 +461,8 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         if (tile == 0xFFFFFFFFu) break;
         const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
         const bool valid = row < p.n_rows;
-        // issued now, consumed at the end of the tile: their latency hides behind the row walk
+        // issued now, consumed at the end of the tile: its latency hides behind the row walk
         const double kn = (F64 && valid) ? __ldg(p.knorm + row) : 1.0;
-        unsigned long long g_seen = 0ull;
-        if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
         for (int c = 0; c < p.n_chunks; c++) {
             if (c) mbar_wait(sm.full + stage, phase);
             const uint8_t* srow = sm.stages + (size_t)stage * kStageBytes + row_off;
@@ -416,9 +501,17 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         float score[NQ];
 #pragma unroll
         for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
-        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
+        unsigned long long ext_bound = 0ull;
+        if (!SPILL && tid < NQ) ext_bound = *((volatile unsigned long long*)(sm.ext + tid));
+        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, ext_bound, last_pub);
     }
-    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid);
+    if (tid == 0) *((volatile int*)sm.done) = 1;   // the refresher warp may leave
+    if constexpr (!SPILL) {
+        // the stage ring is idle now (every TMA box has landed and been consumed): lend it to the merge
+        int big_cap = 1;
+        while ((size_t)big_cap * 2 * 8 <= (size_t)p.n_stages * kStageBytes) big_cap <<= 1;
+        scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid, (uint64_t*)sm.stages, big_cap);
+    }
 }
 
 // ---- the generic kernel: any dim (dim % 4 != 0, dim < 32, or a query too long
@@ -435,6 +528,7 @@ scan_generic_kernel(const ScanParams p) {
     sm.cnt = (int*)(sm.tau + NQ);
     sm.flag = sm.cnt + NQ;
     sm.pref = sm.flag + 1;
+    sm.lmax = nullptr;   // the generic kernel publishes lbest at prunes only
     const int tid = threadIdx.x;
     SelState sel[NQ];
     sel_setup<NQ>(p, sm, sel, tid);
@@ -443,6 +537,7 @@ scan_generic_kernel(const ScanParams p) {
 #pragma unroll
     for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
     const uint32_t n_tiles = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+    unsigned long long last_pub = 0ull;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
         const bool valid = row < p.n_rows;
@@ -463,9 +558,9 @@ scan_generic_kernel(const ScanParams p) {
         const double kn = (F64 && valid) ? p.knorm[row] : 1.0;
 #pragma unroll
         for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
-        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen);
+        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen, last_pub);
     }
-    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid);
+    if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid, nullptr, 0);
 }
 __host__ inline size_t scan_generic_smem_bytes(int nq, int cap) {
     return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + (size_t)(kMaxGrid + 1) * 4 + 32;

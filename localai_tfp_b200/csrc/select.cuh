@@ -7,10 +7,13 @@
 //   * a row is appended only if it beats the current k-th best (`tau`);
 //   * when the buffer is nearly full the CTA sorts it (bitonic, descending),
 //     keeps the best k and raises tau;
-//   * tau is also raised from a grid-wide bound (`gtau`, atomicMax in HBM): the
-//     k-th best of ANY CTA is a lower bound of the global k-th best, so rows
-//     below it can never be in the answer.  This only drops non-winners, so the
-//     result is deterministic.
+//   * tau is also raised from two grid-wide bounds kept in HBM, both lower bounds
+//     of the global k-th best, so rows below them can never be in the answer:
+//       gtau  = max over CTAs of "my k-th best" (atomicMax);
+//       lbest = min over CTAs of "my m-th best", m = ceil(k / #CTAs): every CTA
+//               holds m rows at least that good, so #CTAs * m >= k rows are.
+//     The second one is what keeps the per-CTA survivor lists short when k is
+//     large.  Both only drop non-winners, so the result is deterministic.
 // The selection costs nothing in HBM traffic: the key stream is read once.
 #pragma once
 #include "common.cuh"
@@ -28,6 +31,10 @@ struct SelState {
     int cap;                 // power of two
     int k;
     int room;                // pushes that may happen between two capacity checks
+    unsigned long long* gtau;   // grid-wide max of local k-th bests (HBM), or nullptr
+    unsigned long long* lbest;  // this CTA's slot in the per-CTA "m-th best" array (HBM), or nullptr
+    int m_local;                // m = ceil(k / #CTAs)
+    unsigned long long* lmax;   // shared: best word this CTA has admitted (tracked when m == 1), or nullptr
 };
 
 // Bitonic sort, descending, of buf[0..P) with P a power of two, by kSelThreads threads.
@@ -49,9 +56,9 @@ __device__ __forceinline__ void sel_sort_desc(uint64_t* buf, int P, int tid) {
     }
 }
 
-// Keep the best k of buf[0..cnt); raise tau; fold in / publish the grid-wide bound.
+// Keep the best k of buf[0..cnt); raise tau; publish this CTA's bounds.
 // Must be called by all kSelThreads threads with a uniform view of *cnt.
-__device__ __forceinline__ void sel_prune(const SelState& s, unsigned long long* gtau, int tid) {
+__device__ __forceinline__ void sel_prune(const SelState& s, int tid, bool publish) {
     int n = *s.cnt;
     int P = 2;
     while (P < n) P <<= 1;
@@ -64,11 +71,13 @@ __device__ __forceinline__ void sel_prune(const SelState& s, unsigned long long*
         if (m == s.k) {
             unsigned long long kth = s.buf[s.k - 1];
             if (kth > t) t = kth;
+            if (publish && s.gtau) {
+                unsigned long long g = atomicMax(s.gtau, kth);
+                if (g > t) t = g;
+            }
         }
-        if (gtau) {
-            unsigned long long g = (m == s.k) ? atomicMax(gtau, t) : *((volatile unsigned long long*)gtau);
-            if (g > t) t = g;
-        }
+        if (publish && s.lbest && n >= s.m_local)
+            *((volatile unsigned long long*)s.lbest) = s.buf[s.m_local - 1];
         *s.tau = t;
         *s.cnt = m;
     }
@@ -80,15 +89,18 @@ __device__ __forceinline__ void sel_offer(const SelState& s, uint64_t cand) {
     if (cand > *((volatile unsigned long long*)s.tau)) {
         int pos = atomicAdd(s.cnt, 1);
         s.buf[pos] = cand;
+        // m == 1: the best admitted word is this CTA's lbest.  Admissions are rare, so this costs
+        // nothing per row; a row that was not admitted is below tau and cannot matter.
+        if (s.lmax && cand > *((volatile unsigned long long*)s.lmax)) atomicMax(s.lmax, cand);
     }
 }
 
 // Call after a round of offers, with a barrier already between the offers and
 // this call.  Uniform across the consumer threads.
-__device__ __forceinline__ void sel_maybe_prune(const SelState& s, unsigned long long* gtau, int tid) {
+__device__ __forceinline__ void sel_maybe_prune(const SelState& s, int tid, bool publish) {
     int n = *((volatile int*)s.cnt);
     named_bar_sync(kSelBarrier, kSelThreads);  // everyone has read cnt before anyone changes it
-    if (n > s.cap - s.room) sel_prune(s, gtau, tid);
+    if (n > s.cap - s.room) sel_prune(s, tid, publish);
 }
 
 }  // namespace tfp

@@ -107,6 +107,23 @@ static int get_encoder() {
 }
 
 // ---------------------------------------------------------------------------
+// development knobs (environment; defaults are what ships)
+// ---------------------------------------------------------------------------
+struct Tuning {
+    int refresh_ns = 4000;
+    bool disable_lbest = false;
+};
+static const Tuning& tuning() {
+    static Tuning t = [] {
+        Tuning x;
+        if (const char* e = getenv("TFP_REFRESH_NS")) x.refresh_ns = atoi(e);
+        if (const char* e = getenv("TFP_DISABLE_LBEST")) x.disable_lbest = atoi(e) != 0;
+        return x;
+    }();
+    return t;
+}
+
+// ---------------------------------------------------------------------------
 // the store
 // ---------------------------------------------------------------------------
 struct tfp_find_ctx;
@@ -141,7 +158,7 @@ struct tfp_find_ctx {
     std::vector<QInfo> qinfo;
     DevBuf d_q, d_qinfo;
     PinBuf h_in, h_out;
-    DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket + tile counter
+    DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket + tile counter + lbest[kMaxNQ x kMaxGrid]
     DevBuf all_cand, sorted_cand, cub_tmp;
     DevBuf out_cand, out_ids, out_sims, out_slots, out_n, out_keys, out_rec;
     int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
@@ -579,8 +596,8 @@ static int ctx_create(tfp_store* s, tfp_find_ctx** out) {
     tfp_find_ctx* c = new tfp_find_ctx();
     c->st = s;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(-1, "cudaStreamCreate failed"); }
-    if (c->sync_words.reserve((kMaxNQ + 2) * 8)) { cudaStreamDestroy(c->stream); delete c; return -1; }
-    if (cudaMemset(c->sync_words.p, 0, (kMaxNQ + 2) * 8) != cudaSuccess) { ctx_destroy(c); return fail(-1, "cudaMemset failed"); }
+    if (c->sync_words.reserve((kMaxNQ + 2 + kMaxNQ * kMaxGrid) * 8)) { cudaStreamDestroy(c->stream); delete c; return -1; }
+    if (cudaMemset(c->sync_words.p, 0, (kMaxNQ + 2 + kMaxNQ * kMaxGrid) * 8) != cudaSuccess) { ctx_destroy(c); return fail(-1, "cudaMemset failed"); }
     s->ctxs.push_back(c);
     *out = c;
     return 0;
@@ -724,6 +741,11 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     p.gtau = c->sync_words.as<unsigned long long>();
     p.ticket = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ);
     p.tile_counter = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ + 1);
+    p.lbest = c->sync_words.as<unsigned long long>() + kMaxNQ + 2;
+    p.lbest_stride = kMaxGrid;
+    p.m_local = (ksel + grid - 1) / grid;
+    p.refresh_ns = tuning().refresh_ns;
+    if (tuning().disable_lbest) p.lbest = nullptr;
     p.out_cand = c->out_cand.as<uint64_t>(); p.out_ids = c->out_ids.as<int64_t>();
     p.out_sims = c->out_sims.as<float>(); p.out_slots = c->out_slots.as<uint32_t>(); p.out_n = c->out_n.as<int>();
     p.out_rec = c->out_rec.as<uint8_t>(); p.rec_bytes = (int)rec_bytes; p.rec_topk = topk;
@@ -950,7 +972,7 @@ struct NoAllocLayout {                 // byte offsets inside g_noalloc_scratch
     static constexpr size_t part = 0;                                                        // [grid x kMaxNQ x topk] u64
     static constexpr size_t part_cnt = part + (size_t)kNoAllocMaxGrid * kMaxNQ * TFP_NOALLOC_TOPK_MAX * 8;
     static constexpr size_t sync_words = part_cnt + (size_t)kNoAllocMaxGrid * kMaxNQ * 4;    // gtau[kMaxNQ] + ticket + tile counter
-    static constexpr size_t out_cand = sync_words + 128;
+    static constexpr size_t out_cand = sync_words + (size_t)(kMaxNQ + 2 + kMaxNQ * kNoAllocMaxGrid) * 8;
     static constexpr size_t out_slots = out_cand + (size_t)TFP_NOALLOC_TOPK_MAX * 8;
     static constexpr size_t out_rec = out_slots + (size_t)TFP_NOALLOC_TOPK_MAX * 4;
     static constexpr size_t qinfo = out_rec + 1024;
@@ -1038,15 +1060,20 @@ extern "C" int tfp_scan_topk_noalloc(const float* d_keys, int64_t n_rows, int di
     p.gtau = (unsigned long long*)(base + NoAllocLayout::sync_words);
     p.ticket = (unsigned int*)(base + NoAllocLayout::sync_words + kMaxNQ * 8);
     p.tile_counter = (unsigned int*)(base + NoAllocLayout::sync_words + (kMaxNQ + 1) * 8);
+    p.lbest = (unsigned long long*)(base + NoAllocLayout::sync_words + (kMaxNQ + 2) * 8);
+    p.lbest_stride = kNoAllocMaxGrid;
+    p.m_local = (ksel + grid - 1) / grid;
+    p.refresh_ns = tuning().refresh_ns;
+    if (tuning().disable_lbest) p.lbest = nullptr;
     p.out_cand = (uint64_t*)(base + NoAllocLayout::out_cand);
     p.out_slots = (uint32_t*)(base + NoAllocLayout::out_slots);
     p.out_rec = base + NoAllocLayout::out_rec;
     p.rec_bytes = (int)record_bytes(ksel); p.rec_topk = ksel;
     p.out_ids = d_out_ids; p.out_sims = d_out_sims; p.out_n = d_out_n;
 
-    // The array keeps whatever the previous call left.  The grid-wide bounds, the ticket and the
-    // tile counter must start at zero; everything else is written before it is read.
-    CU_OK(cudaMemsetAsync(base + NoAllocLayout::sync_words, 0, (kMaxNQ + 2) * 8, st));
+    // The array keeps whatever the previous call left.  The grid-wide bounds (gtau, lbest), the
+    // ticket and the tile counter must start at zero; everything else is written before it is read.
+    CU_OK(cudaMemsetAsync(base + NoAllocLayout::sync_words, 0, (kMaxNQ + 2 + kMaxNQ * kNoAllocMaxGrid) * 8, st));
 
     // TMA needs 16-byte aligned rows and a box that fits the tensor; otherwise the generic kernel.
     bool use_tma = dim >= kBoxCols && (dim % 4) == 0 && n_rows >= kRowsPerTile &&
