@@ -156,11 +156,18 @@ struct tfp_find_ctx {
     cudaStream_t stream = nullptr;
     int nq = 0, dim = 0;
     std::vector<QInfo> qinfo;
-    DevBuf d_q, d_qinfo;
+    DevBuf d_in;                         // staged queries, then their QInfo records (one H2D copy)
+    float* d_q = nullptr;
+    QInfo* d_qinfo = nullptr;
     PinBuf h_in, h_out;
     DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket + tile counter + lbest[kMaxNQ x kMaxGrid]
     DevBuf all_cand, sorted_cand, cub_tmp;
-    DevBuf out_cand, out_ids, out_sims, out_slots, out_n, out_keys, out_rec;
+    // Results of the last launch live in ONE block so that a download is one D2H copy:
+    // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
+    DevBuf out_block;
+    int* out_n = nullptr; int64_t* out_ids = nullptr; float* out_sims = nullptr; float* out_keys = nullptr;
+    uint64_t* out_cand = nullptr; uint32_t* out_slots = nullptr; uint8_t* out_rec = nullptr;
+    size_t off_ids = 0, off_sims = 0, off_keys = 0;   // byte offsets inside out_block
     int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
     int64_t launches = 0;
 };
@@ -606,8 +613,8 @@ static void ctx_destroy(tfp_find_ctx* c) {
     if (!c) return;
     tfp_store* s = c->st;
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
-    DevBuf* bufs[] = {&c->d_q, &c->d_qinfo, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
-                      &c->cub_tmp, &c->out_cand, &c->out_ids, &c->out_sims, &c->out_slots, &c->out_n, &c->out_keys, &c->out_rec};
+    DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
+                      &c->cub_tmp, &c->out_block};
     for (DevBuf* b : bufs) b->release();
     c->h_in.release();
     c->h_out.release();
@@ -647,7 +654,10 @@ static double host_query_mag(const float* q, int d) {
 static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim) {
     tfp_store* s = c->st;
     size_t qbytes = (size_t)nq * dim * 4, ibytes = (size_t)nq * sizeof(QInfo);
-    if (c->h_in.reserve(qbytes + ibytes) || c->d_q.reserve(qbytes + 256) || c->d_qinfo.reserve(ibytes)) return -1;
+    qbytes = (qbytes + 15) & ~(size_t)15;
+    if (c->h_in.reserve(qbytes + ibytes) || c->d_in.reserve(qbytes + ibytes + 256)) return -1;
+    c->d_q = c->d_in.as<float>();
+    c->d_qinfo = (QInfo*)((uint8_t*)c->d_in.p + qbytes);
     c->qinfo.resize((size_t)nq);
     for (int i = 0; i < nq; i++) {
         const float* qi = q + (size_t)i * dim;
@@ -656,10 +666,9 @@ static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim) {
         info.mag1 = host_query_mag(qi, dim);
         info.pad = 0;
     }
-    memcpy(c->h_in.p, q, qbytes);
+    memcpy(c->h_in.p, q, (size_t)nq * dim * 4);
     memcpy((uint8_t*)c->h_in.p + qbytes, c->qinfo.data(), ibytes);
-    CU_OK(cudaMemcpyAsync(c->d_q.p, c->h_in.p, qbytes, cudaMemcpyHostToDevice, c->stream));
-    CU_OK(cudaMemcpyAsync(c->d_qinfo.p, (uint8_t*)c->h_in.p + qbytes, ibytes, cudaMemcpyHostToDevice, c->stream));
+    CU_OK(cudaMemcpyAsync(c->d_in.p, c->h_in.p, qbytes + ibytes, cudaMemcpyHostToDevice, c->stream));
     c->nq = nq;
     c->dim = dim;
     (void)s;
@@ -714,13 +723,25 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     c->last_stride = ksel;
     c->last_path = (s->normalized && c->qinfo[(size_t)first].normalized) ? TFP_PATH_NORMALIZED : TFP_PATH_FALLBACK;
     size_t slots = (size_t)count * ksel;
-    if (c->out_cand.reserve(slots * 8) || c->out_ids.reserve(slots * 8) || c->out_sims.reserve(slots * 4) ||
-        c->out_slots.reserve(slots * 4) || c->out_n.reserve((size_t)count * 4)) return -1;
     const size_t rec_bytes = record_bytes(topk);
-    if (c->out_rec.reserve((size_t)count * rec_bytes)) return -1;
+    {
+        auto up16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
+        const size_t kd = (size_t)(s->dim > 0 ? s->dim : 1);
+        c->off_ids = up16((size_t)count * 4);
+        c->off_sims = c->off_ids + slots * 8;
+        c->off_keys = up16(c->off_sims + slots * 4);
+        const size_t off_cand = up16(c->off_keys + slots * kd * 4);
+        const size_t off_slots = off_cand + slots * 8;
+        const size_t off_rec = up16(off_slots + slots * 4);
+        if (c->out_block.reserve(off_rec + (size_t)count * rec_bytes)) return -1;
+        uint8_t* b = c->out_block.as<uint8_t>();
+        c->out_n = (int*)b; c->out_ids = (int64_t*)(b + c->off_ids); c->out_sims = (float*)(b + c->off_sims);
+        c->out_keys = (float*)(b + c->off_keys); c->out_cand = (uint64_t*)(b + off_cand);
+        c->out_slots = (uint32_t*)(b + off_slots); c->out_rec = b + off_rec;
+    }
     if (n == 0) {   // written-then-emptied store: empty result
-        CU_OK(cudaMemsetAsync(c->out_n.p, 0, (size_t)count * 4, c->stream));
-        CU_OK(cudaMemsetAsync(c->out_rec.p, 0, (size_t)count * rec_bytes, c->stream));
+        CU_OK(cudaMemsetAsync(c->out_n, 0, (size_t)count * 4, c->stream));
+        CU_OK(cudaMemsetAsync(c->out_rec, 0, (size_t)count * rec_bytes, c->stream));
         return 0;
     }
     const int dim = s->dim;
@@ -737,7 +758,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     p.n_rows = (uint32_t)n; p.dim = dim; p.n_chunks = n_chunks;
     p.topk = ksel; p.cap = cap;
     p.evict_first = ((size_t)n * dim * 4 > ((size_t)96 << 20)) ? 1 : 0;   // larger than L2: stream it
-    p.q = c->d_q.as<float>(); p.qinfo = c->d_qinfo.as<QInfo>();
+    p.q = c->d_q; p.qinfo = c->d_qinfo;
     p.gtau = c->sync_words.as<unsigned long long>();
     p.ticket = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ);
     p.tile_counter = (unsigned int*)(c->sync_words.as<unsigned long long>() + kMaxNQ + 1);
@@ -746,9 +767,9 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     p.m_local = (ksel + grid - 1) / grid;
     p.refresh_ns = tuning().refresh_ns;
     if (tuning().disable_lbest) p.lbest = nullptr;
-    p.out_cand = c->out_cand.as<uint64_t>(); p.out_ids = c->out_ids.as<int64_t>();
-    p.out_sims = c->out_sims.as<float>(); p.out_slots = c->out_slots.as<uint32_t>(); p.out_n = c->out_n.as<int>();
-    p.out_rec = c->out_rec.as<uint8_t>(); p.rec_bytes = (int)rec_bytes; p.rec_topk = topk;
+    p.out_cand = c->out_cand; p.out_ids = c->out_ids;
+    p.out_sims = c->out_sims; p.out_slots = c->out_slots; p.out_n = c->out_n;
+    p.out_rec = c->out_rec; p.rec_bytes = (int)rec_bytes; p.rec_topk = topk;
 
     if (fused) {
         if (c->part.reserve((size_t)grid * kMaxNQ * ksel * 8) || c->part_cnt.reserve((size_t)grid * kMaxNQ * 4)) return -1;
@@ -826,13 +847,10 @@ extern "C" int tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int to
 static int ctx_gather_locked(tfp_find_ctx* c) {
     tfp_store* s = c->st;
     const int count = c->last_count, ks = c->last_stride, dim = s->dim;
-    size_t slots = (size_t)count * ks;
-    if (c->out_keys.reserve(slots * dim * 4)) return -1;
     if (s->n == 0) return 0;
     dim3 grid((unsigned)ks, (unsigned)count);
     int threads = dim >= 256 ? 256 : (dim >= 64 ? 64 : 32);
-    gather_rows_kernel<<<grid, threads, 0, c->stream>>>(s->d_keys, dim, c->out_slots.as<uint32_t>(), c->out_n.as<int>(),
-                                                       ks, c->out_keys.as<float>());
+    gather_rows_kernel<<<grid, threads, 0, c->stream>>>(s->d_keys, dim, c->out_slots, c->out_n, ks, c->out_keys);
     CU_OK(cudaGetLastError());
     c->launches++;
     return 0;
@@ -845,7 +863,7 @@ extern "C" int tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys) {
     if (set_device(c->st)) return -1;
     int rc = ctx_gather_locked(c);
     if (rc) return rc;
-    *d_keys = c->out_keys.as<float>();
+    *d_keys = c->out_keys;
     return 0;
 }
 
@@ -853,29 +871,23 @@ static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, fl
     tfp_store* s = c->st;
     const int count = c->last_count, topk = c->last_topk, ks = c->last_stride, dim = s->dim;
     if (count <= 0) return fail(2, "find download: nothing was launched on this context");
-    size_t slots = (size_t)count * ks;
-    size_t off_n = 0, off_ids = ((size_t)count * 4 + 15) & ~(size_t)15, off_sims = off_ids + slots * 8;
-    size_t off_keys = (off_sims + slots * 4 + 15) & ~(size_t)15;
-    size_t total = off_keys + (out_keys ? slots * dim * 4 : 0);
+    const size_t slots = (size_t)count * ks;
+    // one D2H copy of the block's head: [n | ids | sims] and, when asked for, the key rows
+    const size_t total = out_keys ? c->off_keys + slots * dim * 4 : c->off_sims + slots * 4;
     if (c->h_out.reserve(total)) return -1;
     uint8_t* h = (uint8_t*)c->h_out.p;
-    CU_OK(cudaMemcpyAsync(h + off_n, c->out_n.p, (size_t)count * 4, cudaMemcpyDeviceToHost, c->stream));
     if (s->n > 0) {
-        CU_OK(cudaMemcpyAsync(h + off_ids, c->out_ids.p, slots * 8, cudaMemcpyDeviceToHost, c->stream));
-        CU_OK(cudaMemcpyAsync(h + off_sims, c->out_sims.p, slots * 4, cudaMemcpyDeviceToHost, c->stream));
-        if (out_keys) {
-            if (ctx_gather_locked(c)) return -1;
-            CU_OK(cudaMemcpyAsync(h + off_keys, c->out_keys.p, slots * dim * 4, cudaMemcpyDeviceToHost, c->stream));
-        }
+        if (out_keys && ctx_gather_locked(c)) return -1;
+        CU_OK(cudaMemcpyAsync(h, c->out_block.p, total, cudaMemcpyDeviceToHost, c->stream));
     }
     CU_OK(cudaStreamSynchronize(c->stream));
-    const int* hn = (const int*)(h + off_n);
+    const int* hn = (const int*)h;
     for (int q = 0; q < count; q++) {
         int m = s->n > 0 ? hn[q] : 0;
         if (out_n) out_n[q] = m;
-        if (out_ids) memcpy(out_ids + (size_t)q * topk, h + off_ids + (size_t)q * ks * 8, (size_t)m * 8);
-        if (out_sims) memcpy(out_sims + (size_t)q * topk, h + off_sims + (size_t)q * ks * 4, (size_t)m * 4);
-        if (out_keys) memcpy(out_keys + (size_t)q * topk * dim, h + off_keys + (size_t)q * ks * dim * 4, (size_t)m * dim * 4);
+        if (out_ids) memcpy(out_ids + (size_t)q * topk, h + c->off_ids + (size_t)q * ks * 8, (size_t)m * 8);
+        if (out_sims) memcpy(out_sims + (size_t)q * topk, h + c->off_sims + (size_t)q * ks * 4, (size_t)m * 4);
+        if (out_keys) memcpy(out_keys + (size_t)q * topk * dim, h + c->off_keys + (size_t)q * ks * dim * 4, (size_t)m * dim * 4);
     }
     return 0;
 }
@@ -896,10 +908,10 @@ extern "C" void* tfp_find_ctx_stream(tfp_find_ctx* c) { return c ? (void*)c->str
 extern "C" int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c) { return c ? c->launches : 0; }
 extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids, float** d_sims, int** d_n) {
     if (!c) return fail(2, "tfp_find_ctx_device_results: ctx is NULL");
-    if (d_cand) *d_cand = c->out_cand.as<uint64_t>();
-    if (d_ids) *d_ids = c->out_ids.as<int64_t>();
-    if (d_sims) *d_sims = c->out_sims.as<float>();
-    if (d_n) *d_n = c->out_n.as<int>();
+    if (d_cand) *d_cand = c->out_cand;
+    if (d_ids) *d_ids = c->out_ids;
+    if (d_sims) *d_sims = c->out_sims;
+    if (d_n) *d_n = c->out_n;
     return c->last_stride;   // entries per query in the device arrays (min(topk, rows))
 }
 
@@ -940,7 +952,7 @@ extern "C" size_t tfp_record_bytes(int topk) { return record_bytes(topk < 0 ? 0 
 extern "C" int tfp_find_ctx_device_records(tfp_find_ctx* c, void** d_records, size_t* rec_bytes) {
     if (!c || !d_records || !rec_bytes) return fail(2, "tfp_find_ctx_device_records: NULL argument");
     if (c->last_count <= 0) return fail(2, "tfp_find_ctx_device_records: nothing was launched on this context");
-    *d_records = c->out_rec.p;
+    *d_records = c->out_rec;
     *rec_bytes = record_bytes(c->last_topk);
     return 0;
 }
