@@ -177,7 +177,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     n_blocks = N_KEYS // BLOCK_ROWS
     b0, b1 = rank * n_blocks // world, (rank + 1) * n_blocks // world
     rows_local = (b1 - b0) * BLOCK_ROWS
-    ops = CudaShardOps(rank, local_rank, capacity_rows=rows_local)
+    ops = CudaShardOps(rank, local_rank, capacity_rows=rows_local, lanes=2)
     store = ops.store
     for b in range(b0, b1):
         blk = gen_block_torch(b, device)
@@ -195,22 +195,20 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     ctx.upload(Q)              # queries resident in HBM before the timed region
     ctx.sync()
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
-    # N = 1 keeps two finds in flight (two find-contexts, alternating): the next query's CTAs fill
-    # the SMs that the previous query's tail and merge leave idle.  Every query is still its own
-    # scan (batch 1); nothing is shared between the two.
-    in_flight = 2 if world == 1 else 1
-    ctx_b = stream_b = None
-    if in_flight == 2:
-        ctx_b = store.find_context()
-        ctx_b.upload(Q)
-        ctx_b.sync()
-        stream_b = torch.cuda.ExternalStream(ctx_b.stream, device=device)
+    # Two finds are kept in flight (two find-contexts, alternating): the next query's CTAs fill the
+    # SMs that the previous query's tail and merge leave idle and, at N > 1, its scan overlaps the
+    # previous query's all-gather.  Every query is still its own scan (batch 1).
+    in_flight = 2
+    ctx_b = ops.lanes[1].ctx
+    ctx_b.upload(Q)
+    ctx_b.sync()
+    stream_b = ops.lanes[1].stream
 
     def step_device(i: int):
         if world == 1:
             (ctx if i % 2 == 0 else ctx_b).launch(i % N_QUERIES, 1, TOPK)
         else:
-            sharded.find_device(i % N_QUERIES, TOPK, with_keys=False)
+            sharded.find_device(i % N_QUERIES, TOPK, with_keys=False, lane=i % 2)
 
     def barrier():
         if world > 1:

@@ -82,19 +82,46 @@ def _alias(ptr: int, shape, typestr: str, device) -> torch.Tensor:
     return torch.as_tensor(_DevArray(ptr, shape, typestr), device=device)
 
 
-class CudaShardOps:
-    """Device work of one shard: the local store, its find context, and the merge kernel."""
+class _Lane:
+    """One find in flight on a shard: a find context, its stream, and cached device tensors."""
 
-    def __init__(self, rank: int, device: int, capacity_rows: int = 0):
+    def __init__(self, store: Store, device):
+        self.ctx = store.find_context()
+        self.stream = torch.cuda.ExternalStream(self.ctx.stream, device=device)
+        self.alias = {}       # (ptr, shape, typestr) -> tensor aliasing library memory
+        self.bufs = {}        # (tag, shape) -> reusable tensor
+
+
+class CudaShardOps:
+    """Device work of one shard: the local store, its find contexts ("lanes": finds that may be in
+    flight at once, each with its own stream and scratch), and the merge kernel."""
+
+    def __init__(self, rank: int, device: int, capacity_rows: int = 0, lanes: int = 1):
         self.store = Store(device=device, capacity_rows=capacity_rows, id_base=rank << ID_SHIFT)
         self.device = torch.device("cuda", device)
-        self.ctx = self.store.find_context()
         self._L = self.store._L
-        self._stream = torch.cuda.ExternalStream(self.ctx.stream, device=self.device)
+        self.lanes = [_Lane(self.store, self.device) for _ in range(max(1, lanes))]
+        self.ctx = self.lanes[0].ctx
 
-    def stream(self):
-        """Everything a find enqueues (scan, collectives, merge) is ordered on the context's stream."""
-        return torch.cuda.stream(self._stream)
+    def stream(self, lane: int = 0):
+        """Everything a find enqueues (scan, collective, merge) is ordered on its lane's stream."""
+        return torch.cuda.stream(self.lanes[lane].stream)
+
+    def _alias(self, lane: _Lane, ptr: int, shape, typestr: str) -> torch.Tensor:
+        key = (ptr, tuple(shape), typestr)
+        t = lane.alias.get(key)
+        if t is None:
+            if len(lane.alias) > 64:
+                lane.alias.clear()
+            t = lane.alias[key] = _alias(ptr, shape, typestr, self.device)
+        return t
+
+    def _buf(self, lane: _Lane, tag: str, shape, dtype) -> torch.Tensor:
+        key = (tag, tuple(shape))
+        t = lane.bufs.get(key)
+        if t is None:
+            t = lane.bufs[key] = torch.empty(shape, dtype=dtype, device=self.device)
+        return t
 
     # exact-match operations
     def set(self, keys, values):
@@ -125,41 +152,47 @@ class CudaShardOps:
             self.store.StoresDelete(np.zeros((1, dim), np.float32))
 
     def stage_queries(self, qs: np.ndarray):
-        self.ctx.upload(qs)
+        for lane in self.lanes:
+            lane.ctx.upload(qs)
 
-    def find_local(self, qi: int, topk: int, with_keys: bool):
+    def find_local(self, qi: int, topk: int, with_keys: bool, lane: int = 0):
         """Scan this shard for staged query qi.  Returns (record, keys): the packed result record as a
         uint8 device tensor that aliases the library's buffer, and, if asked, the matching key rows
         [topk, dim] (zero padded)."""
-        self.ctx.launch(qi, 1, topk)
-        ptr, nbytes = self.ctx.device_records()
-        dev = self.device
-        rec = _alias(ptr, (nbytes,), "|u1", dev)
+        ln = self.lanes[lane]
+        ln.ctx.launch(qi, 1, topk)
+        ptr, nbytes = ln.ctx.device_records()
+        rec = self._alias(ln, ptr, (nbytes,), "|u1")
         keys = None
         if with_keys:
             d = max(self.key_len(), 1)
-            keys = torch.zeros((topk, d), dtype=torch.float32, device=dev)
-            if self.rows() > 0:
-                stride = min(topk, self.rows())
-                keys[:stride] = _alias(self.ctx.gather_keys(), (stride, d), "<f4", dev)
+            keys = torch.zeros((topk, d), dtype=torch.float32, device=self.device)
+            rows = self.rows()
+            if rows > 0:
+                stride = min(topk, rows)
+                keys[:stride] = self._alias(ln, ln.ctx.gather_keys(), (stride, d), "<f4")
         return rec, keys
 
-    def merge(self, g_rec, world: int, topk: int):
-        dev = self.device
-        o_sims = torch.empty(topk, dtype=torch.float32, device=dev)
-        o_ids = torch.empty(topk, dtype=torch.int64, device=dev)
-        o_shard = torch.empty(topk, dtype=torch.int32, device=dev)
-        o_index = torch.empty(topk, dtype=torch.int32, device=dev)
-        o_n = torch.empty(1, dtype=torch.int32, device=dev)
-        st = torch.cuda.current_stream(dev)
+    def gather_buffer(self, nbytes: int, lane: int = 0) -> torch.Tensor:
+        return self._buf(self.lanes[lane], "g_rec", (nbytes,), torch.uint8)
+
+    def merge(self, g_rec, world: int, topk: int, lane: int = 0):
+        ln = self.lanes[lane]
+        o_sims = self._buf(ln, "o_sims", (topk,), torch.float32)
+        o_ids = self._buf(ln, "o_ids", (topk,), torch.int64)
+        o_shard = self._buf(ln, "o_shard", (topk,), torch.int32)
+        o_index = self._buf(ln, "o_index", (topk,), torch.int32)
+        o_n = self._buf(ln, "o_n", (1,), torch.int32)
         rc = self._L.tfp_merge_records(g_rec.data_ptr(), world, 1, topk, o_sims.data_ptr(), o_ids.data_ptr(),
                                        o_shard.data_ptr(), o_index.data_ptr(), o_n.data_ptr(),
-                                       C.c_void_p(st.cuda_stream))
+                                       C.c_void_p(ln.stream.cuda_stream))
         self.store._check(rc)
         return o_sims, o_ids, o_shard, o_index, o_n
 
     def close(self):
-        self.ctx.close()
+        for ln in self.lanes:
+            ln.alias.clear(); ln.bufs.clear()
+            ln.ctx.close()
         self.store.close()
 
 
@@ -269,8 +302,8 @@ class ShardedStore:
         if topk < 1:
             raise StoreError(f"opts.TopK = {topk}, must be >= 1")
         self.ops.stage_queries(q[None, :])
+        sims, ids, shard, index, n, g_keys = self.find_device(0, int(topk), with_keys)
         with self.ops.stream():
-            sims, ids, shard, index, n, g_keys = self.find_device(0, int(topk), with_keys)
             m = int(n.item())
         sims_h = sims[:m].cpu().numpy()
         ids_h = ids[:m].cpu().numpy()
@@ -281,19 +314,20 @@ class ShardedStore:
             out_keys = [r.copy() for r in g_keys[sh, ix].cpu().numpy()]
         return out_keys, [self.values.get(int(i)) for i in ids_h], sims_h
 
-    def find_device(self, qi: int, topk: int, with_keys: bool = False):
-        """Scan + all-gather + merge for staged query qi; results stay on the device (what bench.py
-        times).  Call inside `with self.ops.stream():` so the collectives follow the scan."""
-        rec, keys = self.ops.find_local(qi, topk, with_keys)
-        # ONE collective per query: every shard's whole answer is one fixed-size record
-        g_rec = torch.empty(self.world * rec.numel(), dtype=torch.uint8, device=rec.device)
-        dist.all_gather_into_tensor(g_rec, rec, group=self.group)
-        g_keys = None
-        if with_keys:
-            g_keys = torch.empty(self.world * keys.numel(), dtype=keys.dtype, device=keys.device)
-            dist.all_gather_into_tensor(g_keys, keys.contiguous().view(-1), group=self.group)
-            g_keys = g_keys.view((self.world,) + tuple(keys.shape))
-        o_sims, o_ids, o_shard, o_index, o_n = self.ops.merge(g_rec, self.world, topk)
+    def find_device(self, qi: int, topk: int, with_keys: bool = False, lane: int = 0):
+        """Scan + all-gather + merge for staged query qi on one lane; results stay on the device (what
+        bench.py times) in buffers that the lane reuses for its next find."""
+        with self.ops.stream(lane):
+            rec, keys = self.ops.find_local(qi, topk, with_keys, lane)
+            # ONE collective per query: every shard's whole answer is one fixed-size record
+            g_rec = self.ops.gather_buffer(self.world * rec.numel(), lane)
+            dist.all_gather_into_tensor(g_rec, rec, group=self.group)
+            g_keys = None
+            if with_keys:
+                g_keys = torch.empty(self.world * keys.numel(), dtype=keys.dtype, device=keys.device)
+                dist.all_gather_into_tensor(g_keys, keys.contiguous().view(-1), group=self.group)
+                g_keys = g_keys.view((self.world,) + tuple(keys.shape))
+            o_sims, o_ids, o_shard, o_index, o_n = self.ops.merge(g_rec, self.world, topk, lane)
         return o_sims, o_ids, o_shard, o_index, o_n, g_keys
 
     def close(self):

@@ -18,7 +18,7 @@ class CpuShardOps:
         self.qs = None
         self.vals = {}
 
-    def stream(self):
+    def stream(self, lane=0):
         return contextlib.nullcontext()
 
     def latch(self, dim):
@@ -57,7 +57,7 @@ class CpuShardOps:
     def stage_queries(self, qs):
         self.qs = np.array(qs, np.float32)
 
-    def find_local(self, qi, topk, with_keys):
+    def find_local(self, qi, topk, with_keys, lane=0):
         from localai_tfp_b200.sharded import pack_record
         q = self.qs[qi]
         n = len(self.o)
@@ -79,7 +79,10 @@ class CpuShardOps:
                 keys[:m] = torch.from_numpy(K[order])
         return torch.from_numpy(pack_record(m, ids, sims, topk)), keys
 
-    def merge(self, g_rec, world, topk):
+    def gather_buffer(self, nbytes, lane=0):
+        return torch.empty(nbytes, dtype=torch.uint8)
+
+    def merge(self, g_rec, world, topk, lane=0):
         from localai_tfp_b200.sharded import record_bytes, unpack_record
         return merge_records_numpy(g_rec.numpy(), world, topk)
 
