@@ -1,0 +1,144 @@
+"""The `local-store` backend process, speaking LocalAI's gRPC contract over the B200 store.
+
+    python -m localai_tfp_b200.server --addr 127.0.0.1:50051
+
+Stand-in for the Go binary of go/local-store/ (the build image has no Go toolchain): same flag
+(`--addr`, backend/go/stores/main.go:14-16), same service and method paths
+(`/backend.Backend/StoresSet` ..., backend/backend.proto:10-34), same replies as the reference's
+gRPC shell (pkg/grpc/server.go:45-55, 185-240): Health -> Reply{message: "OK"}, LoadModel ->
+Result{success: true}, StoresSet/StoresDelete -> Result{"Set key"/"Deleted key", true} or an error
+whose text is the store's, StoresGet/StoresFind -> their result messages, errors as gRPC UNKNOWN.
+The reference serialises RPCs with a mutex (base.SingleThread); so does this server.
+"""
+from __future__ import annotations
+
+import argparse
+import threading
+from concurrent import futures
+
+import grpc
+
+from . import wire
+from .store import Store, StoreError
+
+SERVICE = "backend.Backend"
+STATE_READY, STATE_BUSY = 2, 1
+
+
+def _ident(b):
+    return b
+
+
+class Backend:
+    def __init__(self, device: int = 0):
+        self.store = Store(device=device)
+        self.lock = threading.Lock()          # base.SingleThread (pkg/grpc/base/singlethread.go:13-29)
+        self.busy = False
+
+    # -- lifecycle ---------------------------------------------------------------------------
+    def Health(self, request: bytes, context) -> bytes:
+        return wire.enc_reply(b"OK")                                   # pkg/grpc/server.go:45-47
+
+    def LoadModel(self, request: bytes, context) -> bytes:
+        return wire.enc_result("Loading succeeded", True)              # store.go:101-103 Load is a no-op
+
+    def Status(self, request: bytes, context) -> bytes:
+        st = self.store.stats()
+        state = STATE_BUSY if self.busy else STATE_READY
+        return wire.enc_status(state, int(st.hbm_bytes), {f"hbm-bytes-gpu{st.device}": int(st.hbm_bytes),
+                                                         "rows": int(st.rows)})
+
+    # -- the four store RPCs -------------------------------------------------------------------
+    def _run(self, context, fn):
+        with self.lock:
+            self.busy = True
+            try:
+                return fn()
+            except StoreError as e:                                    # err != nil -> gRPC status Unknown
+                context.abort(grpc.StatusCode.UNKNOWN, str(e))
+            finally:
+                self.busy = False
+
+    def StoresSet(self, request: bytes, context) -> bytes:
+        keys, values = wire.dec_set(request)
+        self._run(context, lambda: self.store.StoresSet(keys, values))
+        return wire.enc_result("Set key", True)                        # pkg/grpc/server.go:203
+
+    def StoresDelete(self, request: bytes, context) -> bytes:
+        keys = wire.dec_keys(request)
+        self._run(context, lambda: self.store.StoresDelete(keys))
+        return wire.enc_result("Deleted key", True)                    # pkg/grpc/server.go:215
+
+    def StoresGet(self, request: bytes, context) -> bytes:
+        keys = wire.dec_keys(request)
+        ks, vs = self._run(context, lambda: self.store.StoresGet(keys))
+        return wire.enc_get_result(ks, vs)
+
+    def StoresFind(self, request: bytes, context) -> bytes:
+        key, topk = wire.dec_find(request)
+        ks, vs, sims = self._run(context, lambda: self.store.StoresFind(key, topk))
+        return wire.enc_find_result(ks, vs, sims)
+
+
+def make_server(addr: str, device: int = 0, workers: int = 8):
+    backend = Backend(device)
+    methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,
+                                                         response_serializer=_ident)
+               for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=workers),
+                         options=[("grpc.max_receive_message_length", wire.MAX_MESSAGE),
+                                  ("grpc.max_send_message_length", wire.MAX_MESSAGE)])
+    server.add_generic_rpc_handlers((grpc.method_handlers_generic_handler(SERVICE, methods),))
+    port = server.add_insecure_port(addr)
+    if port == 0:
+        raise RuntimeError(f"cannot listen on {addr}")
+    return server, backend, port
+
+
+class Client:
+    """What pkg/grpc/client.go + pkg/store/client.go do, for tests and the C1 measurement."""
+
+    def __init__(self, addr: str):
+        self.ch = grpc.insecure_channel(addr, options=[("grpc.max_receive_message_length", wire.MAX_MESSAGE),
+                                                       ("grpc.max_send_message_length", wire.MAX_MESSAGE)])
+        self._m = {name: self.ch.unary_unary(f"/{SERVICE}/{name}", request_serializer=_ident,
+                                             response_deserializer=_ident)
+                   for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}
+
+    def health(self) -> bytes:
+        return wire.dec_reply(self._m["Health"](b"", timeout=10))
+
+    def load_model(self):
+        return wire.dec_result(self._m["LoadModel"](b""))
+
+    def status(self):
+        return wire.dec_status(self._m["Status"](b""))
+
+    def set(self, keys, values):
+        return wire.dec_result(self._m["StoresSet"](wire.enc_set(keys, values)))
+
+    def delete(self, keys):
+        return wire.dec_result(self._m["StoresDelete"](wire.enc_keys(keys)))
+
+    def get(self, keys):
+        return wire.dec_get_result(self._m["StoresGet"](wire.enc_keys(keys)))
+
+    def find(self, key, topk: int):
+        return wire.dec_find_result(self._m["StoresFind"](wire.enc_find(key, topk)))
+
+    def close(self):
+        self.ch.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--addr", default="localhost:50051", help="the address to connect to")   # main.go:14-16
+    ap.add_argument("--device", type=int, default=0)
+    args = ap.parse_args()
+    server, _, _ = make_server(args.addr, args.device)
+    server.start()
+    server.wait_for_termination()
+
+
+if __name__ == "__main__":
+    main()

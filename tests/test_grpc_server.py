@@ -1,0 +1,107 @@
+"""Wire-level test of the backend process: spawn `python -m localai_tfp_b200.server --addr ...` the way
+LocalAI's loader spawns `local-store` (pkg/model/process.go:94-124: binary + `--addr`), poll Health
+(pkg/model/initializers.go:375-387), LoadModel, then replay tests/integration/stores_test.go and
+core/http/app_test.go:904-974 over loopback gRPC.  Same idiom as backend/python/rerankers/test.py:17-45."""
+import socket
+import subprocess
+import sys
+import time
+
+import grpc
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+@pytest.fixture()
+def client(tfp):
+    from localai_tfp_b200.server import Client
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    addr = f"127.0.0.1:{port}"
+    proc = subprocess.Popen([sys.executable, "-m", "localai_tfp_b200.server", "--addr", addr])
+    c = Client(addr)
+    try:
+        for attempt in range(60):                       # the loader polls Health up to 20 x 2 s
+            try:
+                if c.health() == b"OK":
+                    break
+            except grpc.RpcError:
+                time.sleep(0.5)
+        else:
+            raise RuntimeError("backend did not become healthy")
+        assert c.load_model()[1] is True
+        yield c
+    finally:
+        c.close()
+        proc.terminate()                                # SIGTERM must end the process
+        assert proc.wait(timeout=20) is not None
+
+
+def test_set_get_delete_over_grpc(client):              # stores_test.go:86-181
+    assert client.set([[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]], [b"test1", b"test2", b"test3"]) == ("Set key", True)
+    ks, vs = client.get([[0.7, 0.8, 0.9], [0.1, 0.2, 0.3]])
+    assert vs == [b"test1", b"test3"] and np.array_equal(ks[0], np.array([0.1, 0.2, 0.3], f32))
+    assert client.delete([[0.1, 0.2, 0.3], [0.7, 0.8, 0.9]]) == ("Deleted key", True)
+    ks, vs = client.get([[0.4, 0.5, 0.6]])
+    assert vs == [b"test2"]
+    ks, vs = client.get([[0.1, 0.2, 0.3], [0.7, 0.8, 0.9]])
+    assert ks == [] and vs == []
+
+
+def test_find_over_grpc(client):                         # stores_test.go:183-203, 234-244
+    client.set([[0.5, 0.5, 0.5], [0.6, 0.6, -0.6], [0.7, -0.7, -0.7]], [b"test1", b"test2", b"test3"])
+    ks, vs, sims = client.find([0.1, 0.3, 0.5], 2)
+    assert vs == [b"test1", b"test2"] and np.array_equal(ks[0], np.array([0.5, 0.5, 0.5], f32))
+    assert sims[0] == f32(0.8783101) and sims[1] == f32(-0.09759001)
+
+
+def test_exact_unit_vectors_over_grpc(client):
+    keys = [[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0], [-1.0, 0.0, 0.0]]
+    client.set(keys, [b"x", b"y", b"z", b"-z"])
+    _, _, sims = client.find(keys[0], 4)
+    assert np.array_equal(sims, np.array([1.0, 0.0, 0.0, -1.0], f32))
+
+
+def test_http_app_sequence_over_grpc(client):            # core/http/app_test.go:904-974
+    client.set([[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]], [b"test1", b"test2", b"test3"])
+    assert len(client.get([[0.1, 0.2, 0.3], [0.4, 0.5, 0.6], [0.7, 0.8, 0.9]])[0]) == 3
+    client.delete([[0.1, 0.2, 0.3]])
+    ks, vs, sims = client.find([0.1, 0.3, 0.7], 10)
+    assert vs == [b"test2", b"test3"] and all(-1 <= s <= 1 for s in sims)
+
+
+def test_errors_are_grpc_unknown_with_the_reference_text(client):   # pkg/grpc/server.go:194-240
+    with pytest.raises(grpc.RpcError) as e:
+        client.find([1.0, 0.0, 0.0], 1)
+    assert e.value.code() == grpc.StatusCode.UNKNOWN
+    assert e.value.details() == "Try to find key with length 3 when existing length is -1"
+    with pytest.raises(grpc.RpcError) as e:
+        client.set([], [])
+    assert e.value.details() == "no keys to add"
+    client.set([[1.0, 0.0, 0.0]], [b"a"])
+    with pytest.raises(grpc.RpcError) as e:
+        client.find([1.0, 0.0, 0.0], 0)
+    assert e.value.details() == "opts.TopK = 0, must be >= 1"
+
+
+def test_status_reports_hbm(client):
+    client.set([[1.0, 0.0, 0.0]], [b"a"])
+    state, total, breakdown = client.status()
+    assert state == 2 and breakdown["rows"] == 1 and total > 0
+
+
+def test_c1_shape_over_grpc(client, oracle):             # BASELINE.json configs[0]: 10k x 384, top-10, via gRPC
+    from conftest import make_keys
+    K = make_keys(10000, 384, seed=1, normalized=True)
+    for lo in range(0, 10000, 2500):
+        client.set(K[lo:lo + 2500], [b"%d" % i for i in range(lo, lo + 2500)])
+    q = make_keys(1, 384, seed=2, normalized=True)[0]
+    rows, osims = oracle.scan_block(K, q, 10, True)
+    ks, vs, sims = client.find(q, 10)
+    assert np.array_equal(sims, osims) and [int(v) for v in vs] == [int(r) for r in rows]
+    t0 = time.perf_counter()
+    for _ in range(50):
+        client.find(q, 10)
+    print(f"C1 over loopback gRPC: {(time.perf_counter() - t0) / 50 * 1e6:.0f} us per StoresFind")
