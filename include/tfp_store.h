@@ -155,6 +155,10 @@ int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d
  * address: [count x stride x dim] floats, stride as returned by
  * tfp_find_ctx_device_results (what StoresFindResult.Keys is built from). */
 int  tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys);
+/* How often this context took the tensor-core path (batches of >= 32 same-path queries on a
+ * large store: tcgen05 3xTF32 filter + exact re-score) and how many queries it then had to
+ * re-run on the exact scan kernel.  Either pointer may be NULL. */
+int  tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64_t* exact_reruns);
 /* Number of kernels the context has launched so far (for bench accounting). */
 int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c);
 

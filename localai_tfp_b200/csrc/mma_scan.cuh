@@ -1,0 +1,421 @@
+// mma_scan.cuh -- batched StoresFind on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// For >= 32 concurrent queries the scan is a dense contraction S = K . Q^T
+// (K: [rows x D] keys, Q: [nq x D] queries).  It replaces nq sequential runs of the
+// reference loop (backend/go/stores/store.go:378-389 / :441-452) -- the reference has no
+// batched path at all.
+//
+// Numerics: tensor cores only FILTER.  Each fp32 operand is split into a TF32 "hi" part and a
+// TF32 "lo" remainder (a = hi + lo up to 2^-22); S ~= hi.hi + hi.lo + lo.hi (3xTF32, fp32
+// accumulation in TMEM), good to ~1e-6.  Per query the rows whose approximate score clears a
+// proven lower bound of its 148th best score are kept as candidates; finalize (below) takes the
+// best k+48 of them and RE-SCORES them in the reference's exact arithmetic (index-order fp32
+// dot, or fp64-accumulated cosine), so the similarities returned are bit-identical to the Go
+// code, exactly as on the single-query path.  A query whose candidate list overflowed or came
+// out short is flagged and re-run by the host on the exact scan kernel -- still on the GPU.
+//
+// Kernel anatomy (one persistent CTA per SM, 12 warps):
+//   warp 0      TMA producer: per 32-column chunk one key box [128 rows x 128 B] (HBM, read once)
+//               and two query boxes [nq x 128 B] (hi and lo parts, L2-resident), 128-B swizzle;
+//   warps 8-11  converters: split the landed key tile into hi (in place) and lo (second tile),
+//               fence.proxy.async so the tensor core sees the generic-proxy writes;
+//   warp 1      MMA issuer: one elected thread issues tcgen05.mma.kind::tf32 (M=128, N=nq, K=8),
+//               3 per K-step, accumulating in one of two TMEM buffers; tcgen05.commit releases
+//               the shared-memory stage and, after the last chunk, hands the accumulator over;
+//   warps 4-7   epilogue: tcgen05.ld the finished accumulator (thread = key row, registers =
+//               queries), scale by 1/|k| on the cosine path, compare against the per-query
+//               threshold, append survivors to the query's candidate list in HBM;
+//   warp 2      bound refresher: publishes this CTA's best score per query and keeps the
+//               thresholds (min over CTAs of those bests: >= 148 rows are at least that good).
+// No score matrix is ever written to HBM.
+#pragma once
+#include "scan.cuh"
+
+namespace tfp {
+
+constexpr int kMmaThreads = 384;
+constexpr int kMmaStages = 2;
+constexpr int kMmaMaxNQ = 256;         // queries per pass == UMMA N (multiple of 16)
+constexpr int kMmaCandCap = 16384;     // candidate words per query
+constexpr int kMmaMargin = 48;         // candidates re-scored beyond k
+constexpr int kMmaMaxTopK = 100;       // k + margin must stay within the 148 rows the bound guarantees
+constexpr int kMmaATile = kRowsPerTile * kBoxCols * 4;   // 16 KiB
+
+struct MmaParams {
+    uint32_t n_rows;
+    int dim, n_chunks;
+    int nq, nqp;                 // queries in this pass, padded to a multiple of 16
+    int f64;                     // cosine path: approximate score = dot / |k|
+    int mode;                    // 0 = bound-only pass over the first tile of every CTA, 1 = full pass
+    const double* knorm;
+    unsigned int* lbest;         // [grid x kMmaMaxNQ] orderable word of each CTA's best approximate score
+    uint64_t* cand;              // [nq x kMmaCandCap]
+    unsigned int* cand_cnt;      // [nq]
+    int refresh_ns;
+};
+
+// ---- tcgen05 wrappers ---------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]^T, TF32 inputs, fp32 accumulate
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// mbarrier arrives when every MMA issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// K-major, 128-byte-swizzled operand tile: rows of 128 B, 8-row groups 1024 B apart
+// (cute::UMMA::SmemDescriptor: start>>4 | LBO=1<<16 | SBO=64<<32 | version=1<<46 | SWIZZLE_128B=2<<61)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::tf32, fp32 accumulator, both operands K-major, M = 128, N = n
+__host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+constexpr uint32_t kTf32Mask = 0xFFFFE000u;   // sign, exponent, 10 mantissa bits
+__device__ __forceinline__ void tf32_split(float a, float& hi, float& lo) {
+    hi = __uint_as_float(__float_as_uint(a) & kTf32Mask);
+    lo = __uint_as_float(__float_as_uint(__fsub_rn(a, hi)) & kTf32Mask);   // a - hi is exact in fp32
+}
+
+// ---- query preparation: [nq x D] -> hi parts in rows [0, nqp), lo parts in rows [nqp, 2 nqp) -------
+__global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int dim, float* __restrict__ out) {
+    const size_t total = (size_t)nqp * dim;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i / dim);
+        float hi = 0.0f, lo = 0.0f;
+        if (r < nq) tf32_split(q[i], hi, lo);
+        out[i] = hi;
+        out[total + i] = lo;
+    }
+}
+
+__host__ __device__ inline size_t mma_smem_bytes(int nqp) {
+    size_t stage = 2 * (size_t)kMmaATile + 2 * (size_t)nqp * 128;
+    return kMmaStages * stage + 10 * 8 + 16 + 2 * kMmaMaxNQ * 4 + 1024;
+}
+
+__global__ void __launch_bounds__(kMmaThreads, 1)
+mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_q, const MmaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const size_t b_bytes = (size_t)p.nqp * 128;
+    const size_t stage_bytes = 2 * (size_t)kMmaATile + 2 * b_bytes;
+    auto a_hi = [&](int s) { return base + s * stage_bytes; };
+    auto a_lo = [&](int s) { return base + s * stage_bytes + kMmaATile; };
+    auto b_hi = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile; };
+    auto b_lo = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile + b_bytes; };
+    uint8_t* tail = base + kMmaStages * stage_bytes;
+    uint64_t* full = (uint64_t*)tail;            // [2] TMA landed
+    uint64_t* conv = full + 2;                   // [2] hi/lo tiles ready
+    uint64_t* empty = conv + 2;                  // [2] stage consumed by the tensor core
+    uint64_t* acc_full = empty + 2;              // [2] accumulator complete
+    uint64_t* acc_empty = acc_full + 2;          // [2] accumulator drained
+    uint32_t* tmem_base_s = (uint32_t*)(acc_empty + 2);
+    volatile int* flags = (volatile int*)(tmem_base_s + 1);   // [0] done, [1] thresholds ready
+    unsigned int* tau = (unsigned int*)(tmem_base_s + 4);     // [kMmaMaxNQ] admission thresholds (orderable words)
+    unsigned int* lb = tau + kMmaMaxNQ;                       // [kMmaMaxNQ] this CTA's best score per query
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t n_tiles_all = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+    const uint32_t n_tiles = p.mode == 0 ? (n_tiles_all < gridDim.x ? n_tiles_all : gridDim.x) : n_tiles_all;
+    const uint32_t tmem_cols = 2 * p.nqp <= 32 ? 32 : (2 * p.nqp <= 64 ? 64 : (2 * p.nqp <= 128 ? 128 : (2 * p.nqp <= 256 ? 256 : 512)));
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; s++) {
+            mbar_init(full + s, 1);
+            mbar_init(conv + s, 4);        // one arrive per converter warp
+            mbar_init(empty + s, 1);       // tcgen05.commit
+            mbar_init(acc_full + s, 1);    // tcgen05.commit
+            mbar_init(acc_empty + s, 4);   // one arrive per epilogue warp
+        }
+        fence_mbar_init();
+        flags[0] = 0;
+        flags[1] = p.mode == 0 ? 1 : 0;    // the bound-only pass needs no thresholds
+    }
+    for (int i = tid; i < kMmaMaxNQ; i += kMmaThreads) {
+        tau[i] = 0u;
+        // the full pass continues from what the bound-only pass published for this CTA
+        lb[i] = p.mode == 1 ? p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + i] : 0u;
+    }
+    if (warp == 1) tmem_alloc(tmem_base_s, tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_s;
+
+    if (warp == 0) {
+        // ============================ TMA producer ============================
+        if (lane == 0) {
+            tma_prefetch_desc(&tmap_k);
+            tma_prefetch_desc(&tmap_q);
+            const uint64_t pol_stream = l2_policy_evict_first();
+            const uint64_t pol_keep = l2_policy_evict_normal();
+            int stage = 0; uint32_t phase = 0;
+            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                for (int c = 0; c < p.n_chunks; c++) {
+                    mbar_wait(empty + stage, phase ^ 1u);
+                    mbar_arrive_expect_tx(full + stage, (uint32_t)(kMmaATile + 2 * b_bytes));
+                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kBoxCols, (int)(tile * kRowsPerTile), pol_stream);
+                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * kBoxCols, 0, pol_keep);
+                    tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kBoxCols, p.nqp, pol_keep);
+                    if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ============================ MMA issuer ============================
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_tf32(p.nqp);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                mbar_wait(acc_empty + acc, acc_phase ^ 1u);     // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.nqp);
+                for (int c = 0; c < p.n_chunks; c++) {
+                    mbar_wait(full + stage, phase);             // query boxes landed (keys are covered by conv)
+                    mbar_wait(conv + stage, phase);             // hi / lo key tiles written and fenced
+                    tc_fence_after();
+                    const uint32_t ah = smem_u32(a_hi(stage)), al = smem_u32(a_lo(stage));
+                    const uint32_t bh = smem_u32(b_hi(stage)), bl = smem_u32(b_lo(stage));
+#pragma unroll
+                    for (int k = 0; k < kBoxCols / 8; k++) {    // UMMA K = 8 TF32 = 32 bytes along the swizzled row
+                        const uint32_t off = (uint32_t)k * 32u;
+                        umma_tf32(d_tmem, umma_desc_sw128(ah + off), umma_desc_sw128(bh + off), idesc, (c | k) != 0);
+                        umma_tf32(d_tmem, umma_desc_sw128(ah + off), umma_desc_sw128(bl + off), idesc, 1u);
+                        umma_tf32(d_tmem, umma_desc_sw128(al + off), umma_desc_sw128(bh + off), idesc, 1u);
+                    }
+                    umma_commit(empty + stage);                 // stage is free once these MMAs retire
+                    if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(acc_full + acc);                    // accumulator complete
+                if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+            }
+        }
+    } else if (warp == 2) {
+        // ============================ bound refresher ============================
+        // tau[q] = min over CTAs of their best score so far for q.  Every CTA holds at least one
+        // row that good, so >= gridDim.x rows of the store reach tau: it can never cut into the
+        // best gridDim.x rows (k + margin is kept below that by the host).
+        if (p.mode == 1) {
+            for (;;) {
+                for (int q = lane; q < p.nq; q += 32) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
+                for (int q = lane; q < p.nq; q += 32) {
+                    unsigned int m = 0xFFFFFFFFu;
+                    for (unsigned b = 0; b < gridDim.x; b++) {
+                        unsigned int v = ((volatile unsigned int*)p.lbest)[(size_t)b * kMmaMaxNQ + q];
+                        m = v < m ? v : m;
+                    }
+                    if (m > tau[q]) ((volatile unsigned int*)tau)[q] = m;
+                }
+                __syncwarp();
+                if (lane == 0) flags[1] = 1;
+                int d = (lane == 0) ? flags[0] : 0;
+                if (__shfl_sync(0xFFFFFFFFu, d, 0)) break;
+                __nanosleep((unsigned)p.refresh_ns);
+            }
+        }
+    } else if (warp >= 4 && warp < 8) {
+        // ============================ epilogue ============================
+        const int wq = warp & 3;                                // TMEM lane quadrant this warp may read
+        const int row_in_tile = wq * 32 + lane;
+        {   // first thresholds are in place (bounded wait: a protocol bug must trap, not hang)
+            const long long t0 = clock64();
+            while (flags[1] == 0) {
+                __nanosleep(200);
+                if (clock64() - t0 > 4000000000ll) { printf("tfp: mma epilogue never saw thresholds\n"); __trap(); }
+            }
+        }
+        int acc = 0; uint32_t acc_phase = 0;
+        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const uint32_t row = tile * kRowsPerTile + (uint32_t)row_in_tile;
+            const bool valid = row < p.n_rows;
+            const float inv = (p.f64 && valid) ? (float)(1.0 / __ldg(p.knorm + row)) : 1.0f;
+            mbar_wait(acc_full + acc, acc_phase);
+            tc_fence_after();
+            for (int col0 = 0; col0 < p.nqp; col0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(acc * p.nqp + col0), v);
+                if (valid) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const int q = col0 + j;
+                        if (q < p.nq) {
+                            const float s = __uint_as_float(v[j]) * inv;
+                            const unsigned int o = score_to_order(s);
+                            if (o > ((volatile unsigned int*)lb)[q]) atomicMax(lb + q, o);
+                            if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
+                                const unsigned int pos = atomicAdd(p.cand_cnt + q, 1u);
+                                if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)q * kMmaCandCap + pos] = pack_cand(s, row);
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty + acc);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+        }
+        // publish this CTA's bests (the bound-only pass exists to produce exactly this)
+        named_bar_sync(2, 128);
+        for (int q = tid - 128; q < p.nq; q += 128) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
+        if (tid == 128) flags[0] = 1;
+    } else if (warp >= 8) {
+        // ============================ converters ============================
+        const int ct = tid - 256;                               // 0..127
+        int stage = 0; uint32_t phase = 0;
+        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            for (int c = 0; c < p.n_chunks; c++) {
+                mbar_wait(full + stage, phase);
+                float4* hi4 = reinterpret_cast<float4*>(a_hi(stage));
+                float4* lo4 = reinterpret_cast<float4*>(a_lo(stage));
+#pragma unroll
+                for (int i = 0; i < kMmaATile / 16 / 128; i++) {   // element-wise: the swizzle does not matter
+                    float4 a = hi4[ct + i * 128], h, l;
+                    tf32_split(a.x, h.x, l.x);
+                    tf32_split(a.y, h.y, l.y);
+                    tf32_split(a.z, h.z, l.z);
+                    tf32_split(a.w, h.w, l.w);
+                    hi4[ct + i * 128] = h;
+                    lo4[ct + i * 128] = l;
+                }
+                fence_proxy_async_smem();                        // generic-proxy writes -> visible to the tensor core
+                __syncwarp();
+                if (lane == 0) mbar_arrive(conv + stage);
+                if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
+            }
+        }
+    }
+    // ---- teardown: every MMA has retired (the epilogue consumed the last accumulator) ----
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ---- finalize: per query, best k+margin candidates by approximate score, exact re-score, top-k ----
+struct FinalizeParams {
+    const float* keys; const int64_t* ids; const double* knorm;
+    uint32_t n_rows; int dim;
+    const float* q; const QInfo* qinfo; int q_first;     // original (unsplit) staged queries
+    const uint64_t* cand; const unsigned int* cand_cnt;
+    int topk;
+    int out_first;
+    uint64_t* out_cand; int64_t* out_ids; float* out_sims; uint32_t* out_slots; int* out_n;
+    uint8_t* out_rec; int rec_bytes; int rec_topk;
+    int* status;                                         // [nq] 0 ok, else the host re-runs the query exactly
+};
+
+__device__ __forceinline__ void block_sort_desc(uint64_t* buf, int P, int tid, int nthreads) {
+    for (int k2 = 2; k2 <= P; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < (P >> 1); i += nthreads) {
+                int lo = ((i / j) * (j << 1)) + (i % j), hi = lo + j;
+                uint64_t x = buf[lo], y = buf[hi];
+                bool desc = ((lo & k2) == 0);
+                if ((x < y) == desc && x != y) { buf[lo] = y; buf[hi] = x; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+template <bool F64>
+__global__ void __launch_bounds__(512, 1)
+mma_finalize_kernel(const FinalizeParams p) {
+    extern __shared__ uint64_t fbuf[];                   // [P] candidate words, then reused for the exact words
+    __shared__ uint64_t exact[256];
+    const int q = blockIdx.x, tid = threadIdx.x;
+    const unsigned int cnt = p.cand_cnt[q];
+    const int n = cnt < (unsigned)kMmaCandCap ? (int)cnt : kMmaCandCap;
+    int P = 2;
+    while (P < n) P <<= 1;
+    for (int i = tid; i < P; i += blockDim.x) fbuf[i] = i < n ? p.cand[(size_t)q * kMmaCandCap + i] : 0ull;
+    __syncthreads();
+    block_sort_desc(fbuf, P, tid, blockDim.x);
+    const int k = p.topk;
+    const int want = k + kMmaMargin;
+    const int C = n < want ? n : want;                   // <= 148 <= 256
+    // exact re-score, one thread per candidate row, the reference's arithmetic (scan.cuh Acc<>)
+    const float* qv = p.q + (size_t)(p.q_first + q) * p.dim;
+    const double mag1 = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    if (tid < 256) {
+        uint64_t w = 0ull;
+        if (tid < C) {
+            const uint32_t slot = cand_slot(fbuf[tid]);
+            const float* kr = p.keys + (size_t)slot * p.dim;
+            Acc<F64> acc;
+            acc.zero();
+            for (int i = 0; i < p.dim; i++) acc.add(__ldg(qv + i), kr[i]);
+            w = pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[slot] : 1.0), slot);
+        }
+        exact[tid] = w;
+    }
+    __syncthreads();
+    const uint64_t cut = C > 0 ? fbuf[C - 1] : 0ull;     // approximate word of the last candidate re-scored
+    __syncthreads();
+    block_sort_desc(exact, 256, tid, blockDim.x);
+    const int lim = (uint32_t)k < p.n_rows ? k : (int)p.n_rows;
+    const int m = C < lim ? C : lim;
+    const int o = p.out_first + q;
+    for (int i = tid; i < k; i += blockDim.x) {
+        size_t at = (size_t)o * k + i;
+        if (i < m) {
+            const uint64_t c = exact[i];
+            const uint32_t slot = cand_slot(c);
+            const int64_t id = p.ids[slot];
+            p.out_cand[at] = c; p.out_sims[at] = cand_score(c); p.out_slots[at] = slot; p.out_ids[at] = id;
+            record_write(p.out_rec + (size_t)o * p.rec_bytes, p.rec_topk, i, id, cand_score(c));
+        } else {
+            p.out_cand[at] = 0ull; p.out_sims[at] = 0.0f; p.out_slots[at] = 0xFFFFFFFFu; p.out_ids[at] = -1;
+        }
+    }
+    if (tid == 0) {
+        p.out_n[o] = m;
+        *(int*)(p.out_rec + (size_t)o * p.rec_bytes) = m;
+        int st = 0;
+        if (cnt > (unsigned)kMmaCandCap) st = 1;                     // candidate list overflowed
+        else if (m < lim) st = 2;                                    // came out short
+        else if ((uint32_t)C < p.n_rows && m > 0) {
+            // Rows that were NOT re-scored all have an approximate score <= `cut` (the last re-scored
+            // candidate; rows never listed are below the threshold, which is below it too).  They are
+            // irrelevant iff cut + (3xTF32 error) is still below the k-th exact score.
+            const float kth = cand_score(exact[m - 1]);
+            const float nxt = cand_score(cut);
+            if (!(nxt + 2e-5f * (fabsf(kth) + 1.0f) < kth)) st = 3;  // too close to call: exact re-run
+        }
+        p.status[q] = st;
+    }
+}
+
+}  // namespace tfp

@@ -24,6 +24,7 @@
 #include "host_index.hpp"
 #include "ingest.cuh"
 #include "scan.cuh"
+#include "mma_scan.cuh"
 
 using namespace tfp;
 
@@ -112,12 +113,16 @@ static int get_encoder() {
 struct Tuning {
     int refresh_ns = 4000;
     bool disable_lbest = false;
+    int mma_min_queries = 32;      // batches at least this large go to the tensor-core path
+    int64_t mma_min_rows = 65536;
 };
 static const Tuning& tuning() {
     static Tuning t = [] {
         Tuning x;
         if (const char* e = getenv("TFP_REFRESH_NS")) x.refresh_ns = atoi(e);
         if (const char* e = getenv("TFP_DISABLE_LBEST")) x.disable_lbest = atoi(e) != 0;
+        if (const char* e = getenv("TFP_MMA_MIN_QUERIES")) x.mma_min_queries = atoi(e);
+        if (const char* e = getenv("TFP_MMA_MIN_ROWS")) x.mma_min_rows = atoll(e);
         return x;
     }();
     return t;
@@ -162,6 +167,9 @@ struct tfp_find_ctx {
     PinBuf h_in, h_out;
     DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket + tile counter + lbest[kMaxNQ x kMaxGrid]
     DevBuf all_cand, sorted_cand, cub_tmp;
+    DevBuf mma_qsplit, mma_cand, mma_small;   // tensor-core path: split queries, candidate lists, counters/bounds/status
+    PinBuf h_status;
+    int64_t mma_passes = 0, mma_fallbacks = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
     DevBuf out_block;
@@ -237,6 +245,9 @@ static int optin_all(int bytes) {
     CU_OK((optin_gen<4, false, false>(bytes))); CU_OK((optin_gen<4, true, false>(bytes)));
     CU_OK((optin_gen<8, false, false>(bytes))); CU_OK((optin_gen<8, true, false>(bytes)));
     CU_OK((optin_gen<1, false, true>(bytes)));  CU_OK((optin_gen<1, true, true>(bytes)));
+    CU_OK(cudaFuncSetAttribute(mma_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    CU_OK(cudaFuncSetAttribute(mma_finalize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8));
+    CU_OK(cudaFuncSetAttribute(mma_finalize_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8));
     return 0;
 }
 
@@ -614,10 +625,11 @@ static void ctx_destroy(tfp_find_ctx* c) {
     tfp_store* s = c->st;
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
-                      &c->cub_tmp, &c->out_block};
+                      &c->cub_tmp, &c->out_block, &c->mma_qsplit, &c->mma_cand, &c->mma_small};
     for (DevBuf* b : bufs) b->release();
     c->h_in.release();
     c->h_out.release();
+    c->h_status.release();
     if (s) s->ctxs.erase(std::remove(s->ctxs.begin(), s->ctxs.end(), c), s->ctxs.end());
     delete c;
 }
@@ -708,6 +720,80 @@ static int launch_scan_nq(tfp_find_ctx* c, int nq, const ScanParams& p, bool use
     }
 }
 
+// Tensor-core path for one group of g same-path queries (staged [q0, q0+g), outputs from slot o0).
+// Enqueues: query split, bound-only pass, full pass, finalize; then reads the per-query status and
+// re-runs flagged queries on the exact scan kernel.  `exact_one` launches that kernel for one query.
+template <class ExactOne>
+static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o0, int g, bool norm, int grid,
+                            ExactOne&& exact_one) {
+    tfp_store* s = c->st;
+    const int dim = s->dim;
+    const int nqp = (g + 15) & ~15;
+    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 2 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
+    if (c->mma_qsplit.reserve((size_t)2 * kMmaMaxNQ * dim * 4 + 256) || c->mma_cand.reserve((size_t)kMmaMaxNQ * kMmaCandCap * 8) ||
+        c->mma_small.reserve(small_bytes) || c->h_status.reserve(kMmaMaxNQ * 4)) return -1;
+    unsigned int* cand_cnt = c->mma_small.as<unsigned int>();
+    int* status = (int*)(cand_cnt + kMmaMaxNQ);
+    unsigned int* lbest = (unsigned int*)(status + kMmaMaxNQ);
+    float* qs = c->mma_qsplit.as<float>();
+
+    qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(
+        sp.q + (size_t)q0 * dim, g, nqp, dim, qs);
+    CU_OK(cudaGetLastError());
+    CU_OK(cudaMemsetAsync(cand_cnt, 0, (size_t)kMmaMaxNQ * 4, c->stream));
+
+    if (get_encoder()) return -2;
+    CUtensorMap tmap_q;
+    cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)(2 * nqp)};
+    cuuint64_t gstride[1] = {(cuuint64_t)dim * 4};
+    cuuint32_t box[2] = {(cuuint32_t)kBoxCols, (cuuint32_t)nqp};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(&tmap_q, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, qs, gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled (queries) failed with CUresult %d", (int)r);
+
+    MmaParams mp;
+    memset(&mp, 0, sizeof(mp));
+    mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = sp.n_chunks;
+    mp.nq = g; mp.nqp = nqp; mp.f64 = norm ? 0 : 1;
+    mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
+    mp.refresh_ns = 20000;
+    const size_t smem = mma_smem_bytes(nqp);
+    mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
+    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap, tmap_q, mp);
+    CU_OK(cudaGetLastError());
+    mp.mode = 1;
+    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap, tmap_q, mp);
+    CU_OK(cudaGetLastError());
+
+    FinalizeParams fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.keys = sp.keys; fp.ids = sp.ids; fp.knorm = sp.knorm; fp.n_rows = sp.n_rows; fp.dim = dim;
+    fp.q = sp.q; fp.qinfo = sp.qinfo; fp.q_first = q0;
+    fp.cand = mp.cand; fp.cand_cnt = cand_cnt; fp.topk = sp.topk; fp.out_first = o0;
+    fp.out_cand = sp.out_cand; fp.out_ids = sp.out_ids; fp.out_sims = sp.out_sims; fp.out_slots = sp.out_slots;
+    fp.out_n = sp.out_n; fp.out_rec = sp.out_rec; fp.rec_bytes = sp.rec_bytes; fp.rec_topk = sp.rec_topk;
+    fp.status = status;
+    if (norm) mma_finalize_kernel<false><<<g, 512, (size_t)kMmaCandCap * 8, c->stream>>>(fp);
+    else      mma_finalize_kernel<true><<<g, 512, (size_t)kMmaCandCap * 8, c->stream>>>(fp);
+    CU_OK(cudaGetLastError());
+    c->launches += 4;
+    c->mma_passes++;
+    // the status decides whether a query must be re-run exactly; this is the one place a launch waits
+    CU_OK(cudaMemcpyAsync(c->h_status.p, status, (size_t)g * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_OK(cudaStreamSynchronize(c->stream));
+    const int* hs = c->h_status.as<int>();
+    for (int j = 0; j < g; j++) {
+        if (hs[j] != 0) {
+            c->mma_fallbacks++;
+            int rc = exact_one(q0 + j, o0 + j);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
 // Enqueue the scan(s) for staged queries [first, first+count).  Caller holds the shared lock.
 static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     tfp_store* s = c->st;
@@ -779,15 +865,9 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
         p.all_cand = c->all_cand.as<uint64_t>();
     }
 
-    int i = 0;
-    while (i < count) {
-        const bool norm = s->normalized && c->qinfo[(size_t)(first + i)].normalized;   // store.go:496
-        int g = 1;
-        if (fused) {
-            while (i + g < count && g < kMaxNQ &&
-                   (s->normalized && c->qinfo[(size_t)(first + i + g)].normalized) == norm) g++;
-            g = g >= 8 ? 8 : (g >= 4 ? 4 : (g >= 2 ? 2 : 1));
-        }
+    // Launch the exact scan for staged queries [qf, qf+g) (same path, g in {1,2,4,8} or any g: it is
+    // reduced to what fits) writing output slots [of, ...).  Returns the group size actually launched.
+    auto launch_exact = [&](int qf, int of, int g, bool norm, int* launched) -> int {
         // pick the kernel flavour and the stage count that fits shared memory
         bool use_tma = s->tmap_ok;
         int n_stages = 0;
@@ -807,8 +887,8 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
             return fail(-4, "internal: selection buffers do not fit shared memory (k=%d)", ksel);
         }
         p.n_stages = n_stages;
-        p.q_first = first + i;
-        p.out_first = i;
+        p.q_first = qf;
+        p.out_first = of;
         int rc;
         if (fused) rc = norm ? launch_scan_nq<false, false>(c, g, p, use_tma, grid, smem)
                              : launch_scan_nq<true, false>(c, g, p, use_tma, grid, smem);
@@ -826,12 +906,43 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
             CU_OK(cub::DeviceRadixSort::SortKeysDescending(c->cub_tmp.p, tmp, c->all_cand.as<uint64_t>(),
                                                            c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
             decode_sorted_kernel<<<std::min(1024, (ksel + 255) / 256), 256, 0, c->stream>>>(
-                c->sorted_cand.as<uint64_t>(), (uint32_t)n, ksel, s->d_ids, i, p.out_cand, p.out_ids, p.out_sims,
+                c->sorted_cand.as<uint64_t>(), (uint32_t)n, ksel, s->d_ids, of, p.out_cand, p.out_ids, p.out_sims,
                 p.out_slots, p.out_n, p.out_rec, p.rec_bytes, p.rec_topk);
             CU_OK(cudaGetLastError());
             c->launches += 2;
         }
-        i += g;
+        if (launched) *launched = g;
+        return 0;
+    };
+    auto path_of = [&](int qi) { return s->normalized && c->qinfo[(size_t)qi].normalized; };   // store.go:496
+
+    // Tensor-core path: large same-path batches on a large store.  The lower bound it
+    // relies on counts one row per CTA, so k + margin must not exceed the grid.
+    const bool mma_ok = fused && s->tmap_ok && ksel <= kMmaMaxTopK && grid >= ksel + kMmaMargin &&
+                        n >= tuning().mma_min_rows && tuning().mma_min_queries > 0 &&
+                        mma_smem_bytes(kMmaMaxNQ) <= (size_t)s->max_smem;
+    int i = 0;
+    while (i < count) {
+        const bool norm = path_of(first + i);
+        int run = 1;
+        while (i + run < count && path_of(first + i + run) == norm) run++;
+        if (mma_ok && run >= tuning().mma_min_queries) {
+            const int g = std::min(run, kMmaMaxNQ);
+            int rc = mma_group_launch(c, p, first + i, i, g, norm, grid,
+                                      [&](int qf, int of) { return launch_exact(qf, of, 1, norm, nullptr); });
+            if (rc) return rc;
+            i += g;
+            continue;
+        }
+        int g = 1;
+        if (fused) {
+            g = std::min(run, kMaxNQ);
+            g = g >= 8 ? 8 : (g >= 4 ? 4 : (g >= 2 ? 2 : 1));
+        }
+        int done = 0;
+        int rc = launch_exact(first + i, i, g, norm, &done);
+        if (rc) return rc;
+        i += done;
     }
     return 0;
 }
@@ -906,6 +1017,12 @@ extern "C" int tfp_find_ctx_sync(tfp_find_ctx* c) {
 }
 extern "C" void* tfp_find_ctx_stream(tfp_find_ctx* c) { return c ? (void*)c->stream : nullptr; }
 extern "C" int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c) { return c ? c->launches : 0; }
+extern "C" int tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64_t* exact_reruns) {
+    if (!c) return fail(2, "tfp_find_ctx_mma_counters: ctx is NULL");
+    if (passes) *passes = c->mma_passes;
+    if (exact_reruns) *exact_reruns = c->mma_fallbacks;
+    return 0;
+}
 extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids, float** d_sims, int** d_n) {
     if (!c) return fail(2, "tfp_find_ctx_device_results: ctx is NULL");
     if (d_cand) *d_cand = c->out_cand;

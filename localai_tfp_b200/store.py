@@ -265,6 +265,12 @@ class FindContext:
         self.store._check(self._L.tfp_find_ctx_gather_keys(self._h, C.byref(p)))
         return p.value
 
+    def mma_counters(self):
+        """(tensor-core passes, queries re-run on the exact kernel) so far on this context."""
+        a, b = C.c_int64(), C.c_int64()
+        self.store._check(self._L.tfp_find_ctx_mma_counters(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def device_records(self):
         """(device address, record_bytes) of the last launch's packed per-query records."""
         p, nb = C.c_void_p(), C.c_size_t()

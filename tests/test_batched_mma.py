@@ -1,0 +1,78 @@
+"""The tensor-core path (>= 32 same-path queries on a large store): tcgen05 3xTF32 filter + exact
+re-score.  Results must be what nq single finds return: similarities bit-identical to the oracle."""
+import numpy as np
+import pytest
+
+from conftest import check_find_against_scores, make_keys, normalize_rows
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def run_batch(tfp, oracle, K, Q, k, normalized, expect_mma=True):
+    s = tfp.Store()
+    s.StoresSet(K, [b""] * len(K))
+    c = s.find_context()
+    c.upload(Q)
+    c.launch(0, len(Q), k)
+    res = c.download()
+    passes, reruns = c.mma_counters()
+    if expect_mma:
+        assert passes >= 1, "the batch did not take the tensor-core path"
+    for i in range(len(Q)):
+        norm_i = normalized and oracle.is_normalized(Q[i])
+        check_find_against_scores(res[i][0], res[i][1], oracle.scores_block(K, Q[i], norm_i), k)
+    c.close(); s.close()
+    return passes, reruns
+
+
+@pytest.mark.parametrize("nq,d,k", [(32, 256, 10), (64, 768, 10), (200, 128, 100), (256, 64, 100), (300, 96, 7)])
+def test_mma_path_matches_oracle_normalized(tfp, oracle, nq, d, k):
+    K = make_keys(70000, d, seed=nq + d, normalized=True)
+    Q = make_keys(nq, d, seed=nq + d + 1, normalized=True)
+    passes, reruns = run_batch(tfp, oracle, K, Q, k, True)
+    assert reruns <= nq // 8          # random data: the filter should almost never be "too close to call"
+
+
+@pytest.mark.parametrize("nq,d,k", [(48, 128, 10), (256, 256, 100)])
+def test_mma_path_matches_oracle_fallback(tfp, oracle, nq, d, k):
+    K = make_keys(70000, d, seed=nq + d, normalized=False)          # row norms in [0.5, 2]: cosine path
+    Q = (make_keys(nq, d, seed=nq + d + 1, normalized=True) * f32(1.7)).astype(f32)
+    run_batch(tfp, oracle, K, Q, k, False)
+
+
+def test_mma_path_ragged_dim_and_partial_tile(tfp, oracle):
+    K = make_keys(66001, 100, seed=5, normalized=True)                # D % 32 != 0, last tile partial
+    Q = make_keys(40, 100, seed=6, normalized=True)
+    run_batch(tfp, oracle, K, Q, 10, True)
+
+
+def test_mma_path_near_ties_fall_back_to_exact(tfp, oracle):
+    """Rows that differ by less than the 3xTF32 error around the k-th place: the filter cannot order
+    them, the status check must notice and the exact kernel must decide."""
+    rng = np.random.default_rng(9)
+    base = normalize_rows(rng.standard_normal((1, 64)).astype(f32))[0]
+    K = make_keys(70000, 64, seed=11, normalized=True)
+    K[:400] = normalize_rows(base[None, :] + rng.standard_normal((400, 64)).astype(f32) * f32(2e-7))
+    Q = np.repeat(base[None, :], 32, axis=0) + rng.standard_normal((32, 64)).astype(f32) * f32(1e-3)
+    Q = normalize_rows(Q)
+    passes, reruns = run_batch(tfp, oracle, K, Q, 50, True)
+    assert reruns >= 1
+
+
+def test_mma_path_mixed_paths_split_into_runs(tfp, oracle):
+    K = make_keys(70000, 64, seed=21, normalized=True)
+    Q = make_keys(80, 64, seed=22, normalized=True)
+    Q[40:] *= f32(2.0)                                                 # second run takes the cosine path
+    run_batch(tfp, oracle, K, Q, 10, True)
+
+
+def test_small_batches_and_small_stores_stay_on_the_exact_kernel(tfp, oracle):
+    K = make_keys(70000, 64, seed=31, normalized=True)
+    Q = make_keys(16, 64, seed=32, normalized=True)
+    passes, _ = run_batch(tfp, oracle, K, Q, 10, True, expect_mma=False)
+    assert passes == 0
+    K = make_keys(5000, 64, seed=33, normalized=True)
+    Q = make_keys(64, 64, seed=34, normalized=True)
+    passes, _ = run_batch(tfp, oracle, K, Q, 10, True, expect_mma=False)
+    assert passes == 0
