@@ -15,8 +15,9 @@
 // out short is flagged and re-run by the host on the exact scan kernel -- still on the GPU.
 //
 // Kernel anatomy (one persistent CTA per SM, 12 warps):
-//   warp 0      TMA producer: per 32-column chunk one key box [128 rows x 128 B] (HBM, read once)
-//               and two query boxes [nq x 128 B] (hi and lo parts, L2-resident), 128-B swizzle;
+//   warp 0      TMA producer: per 16-column chunk one key box [128 rows x 64 B] (HBM, read once)
+//               and two query boxes [nq x 64 B] (hi and lo parts, L2-resident), 64-B swizzle,
+//               into a ring of 4 stages of 48 KiB (at nq = 256);
 //   warps 8-11  converters: split the landed key tile into hi (in place) and lo (second tile),
 //               fence.proxy.async so the tensor core sees the generic-proxy writes;
 //   warp 1      MMA issuer: one elected thread issues tcgen05.mma.kind::tf32 (M=128, N=nq, K=8),
@@ -34,12 +35,14 @@
 namespace tfp {
 
 constexpr int kMmaThreads = 384;
-constexpr int kMmaStages = 2;
+constexpr int kMmaStages = 4;
+constexpr int kMmaBoxCols = 16;         // floats per row per stage (64 B, 64-byte swizzle): small stages, deep ring
 constexpr int kMmaMaxNQ = 256;         // queries per pass == UMMA N (multiple of 16)
 constexpr int kMmaCandCap = 16384;     // candidate words per query
 constexpr int kMmaMargin = 48;         // candidates re-scored beyond k
 constexpr int kMmaMaxTopK = 100;       // k + margin must stay within the 148 rows the bound guarantees
-constexpr int kMmaATile = kRowsPerTile * kBoxCols * 4;   // 16 KiB
+constexpr int kMmaATile = kRowsPerTile * kMmaBoxCols * 4;   // 8 KiB
+constexpr int kMmaRowBytes = kMmaBoxCols * 4;                // 64
 
 struct MmaParams {
     uint32_t n_rows;
@@ -91,10 +94,10 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-// K-major, 128-byte-swizzled operand tile: rows of 128 B, 8-row groups 1024 B apart
-// (cute::UMMA::SmemDescriptor: start>>4 | LBO=1<<16 | SBO=64<<32 | version=1<<46 | SWIZZLE_128B=2<<61)
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+// K-major, 64-byte-swizzled operand tile: rows of 64 B, 8-row groups 512 B apart
+// (cute::UMMA::SmemDescriptor: start>>4 | LBO=1<<16 | SBO=32<<32 | version=1<<46 | SWIZZLE_64B=4<<61)
+__device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
 }
 // kind::tf32, fp32 accumulator, both operands K-major, M = 128, N = n
 __host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
@@ -119,25 +122,25 @@ __global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int 
 }
 
 __host__ __device__ inline size_t mma_smem_bytes(int nqp) {
-    size_t stage = 2 * (size_t)kMmaATile + 2 * (size_t)nqp * 128;
-    return kMmaStages * stage + 10 * 8 + 16 + 2 * kMmaMaxNQ * 4 + 1024;
+    size_t stage = 2 * (size_t)kMmaATile + 2 * (size_t)nqp * kMmaRowBytes;
+    return kMmaStages * stage + (3 * kMmaStages + 4) * 8 + 16 + 2 * kMmaMaxNQ * 4 + 1024;
 }
 
 __global__ void __launch_bounds__(kMmaThreads, 1)
 mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_q, const MmaParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const size_t b_bytes = (size_t)p.nqp * 128;
+    const size_t b_bytes = (size_t)p.nqp * kMmaRowBytes;
     const size_t stage_bytes = 2 * (size_t)kMmaATile + 2 * b_bytes;
     auto a_hi = [&](int s) { return base + s * stage_bytes; };
     auto a_lo = [&](int s) { return base + s * stage_bytes + kMmaATile; };
     auto b_hi = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile; };
     auto b_lo = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile + b_bytes; };
     uint8_t* tail = base + kMmaStages * stage_bytes;
-    uint64_t* full = (uint64_t*)tail;            // [2] TMA landed
-    uint64_t* conv = full + 2;                   // [2] hi/lo tiles ready
-    uint64_t* empty = conv + 2;                  // [2] stage consumed by the tensor core
-    uint64_t* acc_full = empty + 2;              // [2] accumulator complete
+    uint64_t* full = (uint64_t*)tail;            // [stages] TMA landed
+    uint64_t* conv = full + kMmaStages;          // [stages] hi/lo tiles ready
+    uint64_t* empty = conv + kMmaStages;         // [stages] stage consumed by the tensor core
+    uint64_t* acc_full = empty + kMmaStages;     // [2] accumulator complete
     uint64_t* acc_empty = acc_full + 2;          // [2] accumulator drained
     uint32_t* tmem_base_s = (uint32_t*)(acc_empty + 2);
     volatile int* flags = (volatile int*)(tmem_base_s + 1);   // [0] done, [1] thresholds ready
@@ -150,10 +153,12 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
     const uint32_t tmem_cols = 2 * p.nqp <= 32 ? 32 : (2 * p.nqp <= 64 ? 64 : (2 * p.nqp <= 128 ? 128 : (2 * p.nqp <= 256 ? 256 : 512)));
 
     if (tid == 0) {
-        for (int s = 0; s < 2; s++) {
+        for (int s = 0; s < kMmaStages; s++) {
             mbar_init(full + s, 1);
             mbar_init(conv + s, 4);        // one arrive per converter warp
             mbar_init(empty + s, 1);       // tcgen05.commit
+        }
+        for (int s = 0; s < 2; s++) {
             mbar_init(acc_full + s, 1);    // tcgen05.commit
             mbar_init(acc_empty + s, 4);   // one arrive per epilogue warp
         }
@@ -184,9 +189,9 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                 for (int c = 0; c < p.n_chunks; c++) {
                     mbar_wait(empty + stage, phase ^ 1u);
                     mbar_arrive_expect_tx(full + stage, (uint32_t)(kMmaATile + 2 * b_bytes));
-                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kBoxCols, (int)(tile * kRowsPerTile), pol_stream);
-                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * kBoxCols, 0, pol_keep);
-                    tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kBoxCols, p.nqp, pol_keep);
+                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kMmaBoxCols, (int)(tile * kRowsPerTile), pol_stream);
+                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * kMmaBoxCols, 0, pol_keep);
+                    tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kMmaBoxCols, p.nqp, pol_keep);
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -208,11 +213,11 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                     const uint32_t ah = smem_u32(a_hi(stage)), al = smem_u32(a_lo(stage));
                     const uint32_t bh = smem_u32(b_hi(stage)), bl = smem_u32(b_lo(stage));
 #pragma unroll
-                    for (int k = 0; k < kBoxCols / 8; k++) {    // UMMA K = 8 TF32 = 32 bytes along the swizzled row
+                    for (int k = 0; k < kMmaBoxCols / 8; k++) { // UMMA K = 8 TF32 = 32 bytes along the swizzled row
                         const uint32_t off = (uint32_t)k * 32u;
-                        umma_tf32(d_tmem, umma_desc_sw128(ah + off), umma_desc_sw128(bh + off), idesc, (c | k) != 0);
-                        umma_tf32(d_tmem, umma_desc_sw128(ah + off), umma_desc_sw128(bl + off), idesc, 1u);
-                        umma_tf32(d_tmem, umma_desc_sw128(al + off), umma_desc_sw128(bh + off), idesc, 1u);
+                        umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bh + off), idesc, (c | k) != 0);
+                        umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bl + off), idesc, 1u);
+                        umma_tf32(d_tmem, umma_desc_sw64(al + off), umma_desc_sw64(bh + off), idesc, 1u);
                     }
                     umma_commit(empty + stage);                 // stage is free once these MMAs retire
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }

@@ -143,7 +143,8 @@ struct tfp_store {
     float* d_keys = nullptr;
     int64_t* d_ids = nullptr;
     double* d_knorm = nullptr;
-    CUtensorMap tmap;
+    CUtensorMap tmap;        // exact scan: box [32 floats x 128 rows], 128-byte swizzle
+    CUtensorMap tmap_mma;    // tensor-core path: box [16 floats x 128 rows], 64-byte swizzle
     bool tmap_ok = false;
     FlatIndex index;
     std::vector<uint64_t> slot_hash;   // host mirror: slot -> row hash
@@ -199,6 +200,11 @@ static int encode_tmap(tfp_store* s) {
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    cuuint32_t box2[2] = {(cuuint32_t)kMmaBoxCols, (cuuint32_t)kRowsPerTile};
+    r = g_encode(&s->tmap_mma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_keys, gdim, gstride, box2, estr,
+                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled (mma) failed with CUresult %d", (int)r);
     s->tmap_ok = true;
     return 0;
 }
@@ -746,25 +752,25 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     CUtensorMap tmap_q;
     cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)(2 * nqp)};
     cuuint64_t gstride[1] = {(cuuint64_t)dim * 4};
-    cuuint32_t box[2] = {(cuuint32_t)kBoxCols, (cuuint32_t)nqp};
+    cuuint32_t box[2] = {(cuuint32_t)kMmaBoxCols, (cuuint32_t)nqp};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(&tmap_q, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, qs, gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled (queries) failed with CUresult %d", (int)r);
 
     MmaParams mp;
     memset(&mp, 0, sizeof(mp));
-    mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = sp.n_chunks;
+    mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = (dim + kMmaBoxCols - 1) / kMmaBoxCols;
     mp.nq = g; mp.nqp = nqp; mp.f64 = norm ? 0 : 1;
     mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
     mp.refresh_ns = 20000;
     const size_t smem = mma_smem_bytes(nqp);
     mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
-    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap, tmap_q, mp);
+    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
     CU_OK(cudaGetLastError());
     mp.mode = 1;
-    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap, tmap_q, mp);
+    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
     CU_OK(cudaGetLastError());
 
     FinalizeParams fp;
