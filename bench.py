@@ -189,6 +189,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     sharded = ShardedStore(ops, rank, world) if world > 1 else None
     if sharded:
         sharded.key_len = DIM
+        ops.init_native_comm(rank, world)     # scan + ncclAllGather + merge become one library call
 
     Q = gen_queries()
     ctx = ops.ctx
@@ -318,7 +319,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                        "path": "normalized", "rows_per_gpu": rows_local, "finds_in_flight": in_flight,
                        "l2": "inputs larger than L2 (keys %.2f GB per GPU vs 126 MB); no flush" % (algo_bytes / 1e9)
                              if algo_bytes > 4 * 126e6 else "keys per GPU %.0f MB: partly L2-resident" % (algo_bytes / 1e6),
-                       "parallelism": "row-sharded x%d, NCCL all-gather of top-k records + device merge" % world
+                       "parallelism": "row-sharded x%d, one ncclAllGather of top-k records + device merge per query" % world
                                       if world > 1 else "single GPU"},
             "clocks": clk,
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

@@ -180,6 +180,30 @@ int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk,
                       float* d_out_sims, int64_t* d_out_ids, int* d_out_shard,
                       int* d_out_index, int* d_out_n, void* stream);
 
+/* ---- sharded find in one call (no reference counterpart) --------------
+ * The exchange step of a multi-GPU find -- one ncclAllGather of every shard's fixed-size
+ * record over NVLink, then the device merge -- enqueued by the library itself on the
+ * context's stream, so that a host pays one call per query instead of three.
+ * NCCL is resolved at run time from the process (dlopen of libnccl.so.2: the copy the
+ * host already uses, e.g. the one bundled with PyTorch, else the system one); the library
+ * does not link against it.  One communicator per find context: contexts are independent
+ * lanes, and NCCL serialises what shares a communicator.
+ *   tfp_nccl_unique_id   rank 0 creates the 128-byte id and hands it to the other ranks
+ *                        by whatever means the host has (torch.distributed, MPI, a file).
+ *   tfp_find_ctx_comm_init   collective: every rank calls it with the same id.
+ *   tfp_find_ctx_launch_sharded  scan this shard for staged query `qi`, all-gather the
+ *                        records, merge.  Returns without waiting.  Every rank must issue
+ *                        the same sequence of sharded launches per context.
+ *   tfp_find_ctx_merged_results  device pointers of the merged answer ([topk] each, n[1]).
+ *   tfp_find_ctx_download_merged wait and copy the merged answer to the host. */
+int tfp_nccl_unique_id(void* out_id, size_t out_bytes);
+int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int world);
+int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk);
+int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard,
+                                int** d_index, int** d_n);
+int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims,
+                                 int* out_shard, int* out_index);
+
 /* ---- a find that allocates nothing ----------------------------------------------
  * This entry point has no counterpart in the reference.
  *

@@ -51,6 +51,11 @@ PROTOTYPES = {
     "tfp_record_bytes": (C.c_size_t, [C.c_int]),
     "tfp_find_ctx_device_records": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
     "tfp_merge_records": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]),
+    "tfp_nccl_unique_id": (C.c_int, [vp, C.c_size_t]),
+    "tfp_find_ctx_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+    "tfp_find_ctx_launch_sharded": (C.c_int, [vp, C.c_int, C.c_int]),
+    "tfp_find_ctx_merged_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+    "tfp_find_ctx_download_merged": (C.c_int, [vp, i32p, i64p, fp, i32p, i32p]),
     "tfp_scan_topk_noalloc": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp]),
     "tfp_version": (C.c_char_p, []),
 }

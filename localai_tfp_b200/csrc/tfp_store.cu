@@ -14,6 +14,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <dlfcn.h>
 #include <mutex>
 #include <shared_mutex>
 #include <string>
@@ -128,6 +129,20 @@ static const Tuning& tuning() {
     return t;
 }
 
+// NCCL, resolved at run time (see tfp_find_ctx_launch_sharded); declared early because a find
+// context owns a communicator.
+struct NcclId { char internal[128]; };   // ncclUniqueId
+struct NcclApi {
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+static NcclApi g_nccl;
+static std::once_flag g_nccl_once;
+
 // ---------------------------------------------------------------------------
 // the store
 // ---------------------------------------------------------------------------
@@ -170,6 +185,11 @@ struct tfp_find_ctx {
     DevBuf all_cand, sorted_cand, cub_tmp;
     DevBuf mma_qsplit, mma_cand, mma_small;   // tensor-core path: split queries, candidate lists, counters/bounds/status
     PinBuf h_status;
+    // sharded finds: communicator, gathered records, merged answer
+    void* nccl_comm = nullptr;
+    int comm_rank = 0, comm_world = 0;
+    DevBuf gathered, merged;
+    int merged_topk = 0;
     int64_t mma_passes = 0, mma_fallbacks = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
@@ -629,9 +649,11 @@ static int ctx_create(tfp_store* s, tfp_find_ctx** out) {
 static void ctx_destroy(tfp_find_ctx* c) {
     if (!c) return;
     tfp_store* s = c->st;
-    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->nccl_comm && g_nccl.CommDestroy) { g_nccl.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+    if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
-                      &c->cub_tmp, &c->out_block, &c->mma_qsplit, &c->mma_cand, &c->mma_small};
+                      &c->cub_tmp, &c->out_block, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
     for (DevBuf* b : bufs) b->release();
     c->h_in.release();
     c->h_out.release();
@@ -1239,5 +1261,121 @@ extern "C" int tfp_scan_topk_noalloc(const float* d_keys, int64_t n_rows, int di
         scan_generic_kernel<1, false, false><<<grid, kSelThreads, smem, st>>>(p);
     }
     CU_OK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// sharded find in one call: scan + ncclAllGather(records) + merge on the context's stream
+// ---------------------------------------------------------------------------
+static int nccl_api() {
+    std::call_once(g_nccl_once, [] {
+        // prefer the copy the process already loaded (the host's own NCCL), then the system one
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return;
+        g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+        g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+        g_nccl.AllGather = (decltype(g_nccl.AllGather))dlsym(h, "ncclAllGather");
+        g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+        g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+        g_nccl.ok = g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.AllGather && g_nccl.CommDestroy;
+    });
+    return g_nccl.ok ? 0 : fail(-5, "NCCL (libnccl.so.2) could not be resolved in this process");
+}
+#define NCCL_OK(expr)                                                                                    \
+    do {                                                                                                 \
+        int r__ = (expr);                                                                                \
+        if (r__ != 0)                                                                                    \
+            return fail(-5, "NCCL error %d (%s) at %s:%d", r__,                                          \
+                        g_nccl.GetErrorString ? g_nccl.GetErrorString(r__) : "?", __FILE__, __LINE__);   \
+    } while (0)
+
+extern "C" int tfp_nccl_unique_id(void* out_id, size_t out_bytes) {
+    if (!out_id || out_bytes < sizeof(NcclId)) return fail(2, "tfp_nccl_unique_id: need a 128-byte buffer");
+    if (nccl_api()) return -5;
+    NCCL_OK(g_nccl.GetUniqueId(out_id));
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int world) {
+    if (!c || !unique_id || world < 1 || rank < 0 || rank >= world) return fail(2, "tfp_find_ctx_comm_init: bad argument");
+    if (nccl_api()) return -5;
+    if (set_device(c->st)) return -1;
+    if (c->nccl_comm) { g_nccl.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+    NcclId id;
+    memcpy(&id, unique_id, sizeof(id));
+    NCCL_OK(g_nccl.CommInitRank(&c->nccl_comm, world, id, rank));
+    c->comm_rank = rank;
+    c->comm_world = world;
+    return 0;
+}
+
+// merged buffer layout: sims[topk] f32 | ids[topk] i64 | shard[topk] i32 | index[topk] i32 | n i32 (each 16-aligned)
+struct MergedLayout {
+    size_t sims, ids, shard, index, n, total;
+    explicit MergedLayout(int k) {
+        auto up = [](size_t v) { return (v + 15) & ~(size_t)15; };
+        sims = 0; ids = up((size_t)k * 4); shard = ids + (size_t)k * 8; index = up(shard + (size_t)k * 4);
+        n = up(index + (size_t)k * 4); total = n + 16;
+    }
+};
+
+extern "C" int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk) {
+    if (!c) return fail(2, "tfp_find_ctx_launch_sharded: ctx is NULL");
+    if (!c->nccl_comm) return fail(2, "tfp_find_ctx_launch_sharded: call tfp_find_ctx_comm_init first");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    int rc = ctx_launch_locked(c, qi, 1, topk);
+    if (rc) return rc;
+    const size_t rb = record_bytes(c->last_topk);
+    const int world = c->comm_world;
+    if ((int64_t)world * c->last_topk > 16384) return fail(2, "sharded find: world x topk = %lld exceeds 16384", (long long)world * c->last_topk);
+    MergedLayout L(c->last_topk);
+    if (c->gathered.reserve(rb * world) || c->merged.reserve(L.total)) return -1;
+    NCCL_OK(g_nccl.AllGather(c->out_rec, c->gathered.p, rb, /*ncclUint8*/ 1, c->nccl_comm, c->stream));
+    uint8_t* m = c->merged.as<uint8_t>();
+    const int k = c->last_topk;
+    int P = next_pow2(std::max(world * k, 2));
+    if ((size_t)P * 8 > 48 * 1024)
+        CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
+    merge_records_kernel<<<1, 256, (size_t)P * 8, c->stream>>>(c->gathered.as<uint8_t>(), (int)rb, world, 1, k, P,
+                                                              (float*)(m + L.sims), (int64_t*)(m + L.ids),
+                                                              (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n));
+    CU_OK(cudaGetLastError());
+    c->launches++;
+    c->merged_topk = k;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard, int** d_index,
+                                           int** d_n) {
+    if (!c || c->merged_topk <= 0) return fail(2, "tfp_find_ctx_merged_results: no sharded launch on this context");
+    MergedLayout L(c->merged_topk);
+    uint8_t* m = c->merged.as<uint8_t>();
+    if (d_sims) *d_sims = (float*)(m + L.sims);
+    if (d_ids) *d_ids = (int64_t*)(m + L.ids);
+    if (d_shard) *d_shard = (int*)(m + L.shard);
+    if (d_index) *d_index = (int*)(m + L.index);
+    if (d_n) *d_n = (int*)(m + L.n);
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, int* out_shard,
+                                            int* out_index) {
+    if (!c || c->merged_topk <= 0) return fail(2, "tfp_find_ctx_download_merged: no sharded launch on this context");
+    if (set_device(c->st)) return -1;
+    const int k = c->merged_topk;
+    MergedLayout L(k);
+    if (c->h_out.reserve(L.total)) return -1;
+    uint8_t* h = (uint8_t*)c->h_out.p;
+    CU_OK(cudaMemcpyAsync(h, c->merged.p, L.total, cudaMemcpyDeviceToHost, c->stream));
+    CU_OK(cudaStreamSynchronize(c->stream));
+    const int m = *(const int*)(h + L.n);
+    if (out_n) *out_n = m;
+    if (out_ids) memcpy(out_ids, h + L.ids, (size_t)m * 8);
+    if (out_sims) memcpy(out_sims, h + L.sims, (size_t)m * 4);
+    if (out_shard) memcpy(out_shard, h + L.shard, (size_t)m * 4);
+    if (out_index) memcpy(out_index, h + L.index, (size_t)m * 4);
     return 0;
 }

@@ -23,7 +23,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .store import Store, StoreError
+from .store import Store, StoreError, nccl_unique_id
 
 ID_SHIFT = 40  # shard r hands out ids in [r << 40, (r + 1) << 40)
 
@@ -102,6 +102,7 @@ class CudaShardOps:
         self._L = self.store._L
         self.lanes = [_Lane(self.store, self.device) for _ in range(max(1, lanes))]
         self.ctx = self.lanes[0].ctx
+        self.native = False
 
     def stream(self, lane: int = 0):
         """Everything a find enqueues (scan, collective, merge) is ordered on its lane's stream."""
@@ -154,6 +155,28 @@ class CudaShardOps:
     def stage_queries(self, qs: np.ndarray):
         for lane in self.lanes:
             lane.ctx.upload(qs)
+
+    def init_native_comm(self, rank: int, world: int, group=None):
+        """One NCCL communicator per lane, created inside libtfpstore (the id travels over
+        torch.distributed).  After this, find_merged() does scan + all-gather + merge in ONE call."""
+        for lane in self.lanes:
+            box = [nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=group)
+            lane.ctx.comm_init(box[0], rank, world)
+        self.native = True
+
+    def find_merged(self, qi: int, topk: int, lane: int = 0):
+        """Native path: returns device tensors (sims, ids, shard, index, n) aliasing the lane's merged buffers."""
+        ln = self.lanes[lane]
+        ln.ctx.launch_sharded(qi, topk)
+        key = ("merged", topk)
+        t = ln.bufs.get(key)
+        if t is None:
+            ps, pi, psh, pix, pn = ln.ctx.merged_results()
+            t = ln.bufs[key] = (_alias(ps, (topk,), "<f4", self.device), _alias(pi, (topk,), "<i8", self.device),
+                                _alias(psh, (topk,), "<i4", self.device), _alias(pix, (topk,), "<i4", self.device),
+                                _alias(pn, (1,), "<i4", self.device))
+        return t
 
     def find_local(self, qi: int, topk: int, with_keys: bool, lane: int = 0):
         """Scan this shard for staged query qi.  Returns (record, keys): the packed result record as a
@@ -317,6 +340,8 @@ class ShardedStore:
     def find_device(self, qi: int, topk: int, with_keys: bool = False, lane: int = 0):
         """Scan + all-gather + merge for staged query qi on one lane; results stay on the device (what
         bench.py times) in buffers that the lane reuses for its next find."""
+        if not with_keys and getattr(self.ops, "native", False):
+            return self.ops.find_merged(qi, topk, lane) + (None,)     # one library call: scan + all-gather + merge
         with self.ops.stream(lane):
             rec, keys = self.ops.find_local(qi, topk, with_keys, lane)
             # ONE collective per query: every shard's whole answer is one fixed-size record

@@ -22,6 +22,15 @@ from . import _lib
 from ._lib import TfpCfg, TfpStats, fp, i32p, i64p, u8p
 
 
+def nccl_unique_id() -> bytes:
+    """A fresh 128-byte NCCL unique id (rank 0 makes it, every rank passes it to comm_init)."""
+    L = _lib.load()
+    buf = C.create_string_buffer(128)
+    if L.tfp_nccl_unique_id(buf, 128) != 0:
+        raise RuntimeError(L.tfp_last_error().decode())
+    return buf.raw
+
+
 class StoreError(Exception):
     """An error the reference would also return (same message text)."""
 
@@ -264,6 +273,31 @@ class FindContext:
         p = C.c_void_p()
         self.store._check(self._L.tfp_find_ctx_gather_keys(self._h, C.byref(p)))
         return p.value
+
+    # -- sharded finds in one call (native NCCL) ------------------------------------------------
+    def comm_init(self, unique_id: bytes, rank: int, world: int):
+        buf = C.create_string_buffer(unique_id, 128)
+        self.store._check(self._L.tfp_find_ctx_comm_init(self._h, buf, rank, world))
+
+    def launch_sharded(self, qi: int, topk: int):
+        self.store._check(self._L.tfp_find_ctx_launch_sharded(self._h, qi, topk))
+        self._topk = topk
+
+    def merged_results(self):
+        """Device addresses (sims, ids, shard, index, n) of the last sharded launch's merged answer."""
+        p = [C.c_void_p() for _ in range(5)]
+        self.store._check(self._L.tfp_find_ctx_merged_results(self._h, *[C.byref(x) for x in p]))
+        return tuple(x.value for x in p)
+
+    def download_merged(self):
+        k = self._topk
+        n = C.c_int()
+        ids = np.empty(k, np.int64); sims = np.empty(k, np.float32)
+        shard = np.empty(k, np.int32); index = np.empty(k, np.int32)
+        self.store._check(self._L.tfp_find_ctx_download_merged(self._h, C.byref(n), _p(ids, i64p), _p(sims, fp),
+                                                               _p(shard, i32p), _p(index, i32p)))
+        m = n.value
+        return ids[:m].copy(), sims[:m].copy(), shard[:m].copy(), index[:m].copy()
 
     def mma_counters(self):
         """(tensor-core passes, queries re-run on the exact kernel) so far on this context."""

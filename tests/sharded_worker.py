@@ -64,6 +64,30 @@ def scenario(store, single, rank):
             assert str(e) == text, str(e)
 
 
+def native_path_matches(store, single, rank, world):
+    """scan + ncclAllGather + merge inside libtfpstore (one call) must equal the torch.distributed path."""
+    from conftest import make_keys
+    K = make_keys(400, 48, seed=5, normalized=True)
+    Q = np.ascontiguousarray(K[[1, 7, 150, 399]])
+    store.ops.stage_queries(Q)
+    ref = []
+    for qi in range(len(Q)):
+        sims, ids, shard, index, n, _ = store.find_device(qi, 10, with_keys=False)
+        torch.cuda.synchronize()
+        m = int(n.item())
+        ref.append((ids[:m].cpu().numpy().copy(), sims[:m].cpu().numpy().copy()))
+    store.ops.init_native_comm(rank, world)
+    for qi in range(len(Q)):
+        sims, ids, shard, index, n, _ = store.find_device(qi, 10, with_keys=False)
+        torch.cuda.synchronize()
+        m = int(n.item())
+        assert np.array_equal(ids[:m].cpu().numpy(), ref[qi][0]) and np.array_equal(sims[:m].cpu().numpy(), ref[qi][1])
+        got_ids, got_sims, got_shard, got_index = store.ops.lanes[0].ctx.download_merged()
+        assert np.array_equal(got_ids, ref[qi][0]) and np.array_equal(got_sims, ref[qi][1])
+        want = single.StoresFind(Q[qi], 10)
+        assert np.array_equal(got_sims, want[2])
+
+
 def run(rank, world, port, backend):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -79,7 +103,10 @@ def run(rank, world, port, backend):
             torch.cuda.set_device(rank)
             ops = CudaShardOps(rank, rank)
         store = ShardedStore(ops, rank, world)
-        scenario(store, orc.OracleStore(), rank)
+        single = orc.OracleStore()
+        scenario(store, single, rank)
+        if backend == "nccl":
+            native_path_matches(store, single, rank, world)
         store.close()
         dist.barrier()
     finally:
