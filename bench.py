@@ -38,6 +38,15 @@ WORKLOAD = "C2 (BASELINE.json configs[1]): 1M keys x 768-d fp32, single-query to
 METRIC = "StoresFind queries/sec (top-10)"
 
 
+def select_workload(name: str):
+    """`c2` is the bench contract's workload.  `target` is the north star's stated target shape
+    (10M keys x 1024-d, top-10, batch 1: 41 GB, strong-scaled over the GPUs) for extra evidence."""
+    global N_KEYS, DIM, WORKLOAD, SEED
+    if name == "target":
+        N_KEYS, DIM, SEED = 10_000_000, 1024, 0x5EED0003
+        WORKLOAD = "north-star target: 10M keys x 1024-d fp32, single-query top-10, normalised-key fast path"
+
+
 # ----------------------------------------------------------------------------- inputs
 def gen_block_torch(block: int, device):
     import torch
@@ -121,7 +130,7 @@ def cpu_reference_qps(budget_s: float, steps: int, warmup: int, full: bool):
     t0 = time.perf_counter()
     st.StoresFind(q[0], TOPK, faithful=True)
     per_row = (time.perf_counter() - t0) / probe_rows
-    rows = int(min(N_KEYS, max(probe_rows, budget_s / max(steps + warmup, 1) / per_row)))
+    rows = int(min(N_KEYS, 1_000_000, max(probe_rows, budget_s / max(steps + warmup, 1) / per_row)))
     if rows > probe_rows:
         keys = gen_keys_numpy(rows)
         st = orc.OracleStore()
@@ -136,7 +145,7 @@ def cpu_reference_qps(budget_s: float, steps: int, warmup: int, full: bool):
     assert st.last_path == "normalized"
     qps_full = 1.0 / (dt * N_KEYS / rows)
     sample = (f"{steps} single-query top-{TOPK} finds over a {rows}-row x {DIM}-d sample of the store, "
-              f"1 thread (the reference scan is single-threaded by design, store.go:18), scaled by rows to 1M")
+              f"1 thread (the reference scan is single-threaded by design, store.go:18), scaled by rows to {N_KEYS}")
     return qps_full, dt * 1e3, rows, sample
 
 
@@ -189,7 +198,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     sharded = ShardedStore(ops, rank, world) if world > 1 else None
     if sharded:
         sharded.key_len = DIM
-        ops.init_native_comm(rank, world)     # scan + ncclAllGather + merge become one library call
+        if args.exchange != "torch":            # scan + ncclAllGather + merge become one library call
+            ops.init_native_comm(rank, world, shared=(args.exchange == "native"))
 
     Q = gen_queries()
     ctx = ops.ctx
@@ -270,7 +280,8 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         pass
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json")))["dram_bytes_per_launch"]
+        if args.workload == "c2" and world == 1:     # the ncu capture was taken on exactly this launch shape
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
 
@@ -317,6 +328,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "keys": N_KEYS, "dim": DIM, "topk": TOPK, "queries_per_step": 1,
                        "path": "normalized", "rows_per_gpu": rows_local, "finds_in_flight": in_flight,
+                       "exchange": args.exchange if world > 1 else None,
                        "l2": "inputs larger than L2 (keys %.2f GB per GPU vs 126 MB); no flush" % (algo_bytes / 1e9)
                              if algo_bytes > 4 * 126e6 else "keys per GPU %.0f MB: partly L2-resident" % (algo_bytes / 1e6),
                        "parallelism": "row-sharded x%d, one ncclAllGather of top-k records + device merge per query" % world
@@ -347,7 +359,11 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=["c2", "target"], default="c2")
+    ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="torch",
+                    help="N>1: all-gather through torch.distributed, or inside libtfpstore (one call per query)")
     args = ap.parse_args()
+    select_workload(args.workload)
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -198,6 +198,9 @@ int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk,
  *   tfp_find_ctx_download_merged wait and copy the merged answer to the host. */
 int tfp_nccl_unique_id(void* out_id, size_t out_bytes);
 int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int world);
+/* Let `c` use the communicator `owner` created (both contexts of one store).  NCCL then orders
+ * their collectives one after the other; `owner` must outlive `c`'s last sharded launch. */
+int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner);
 int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk);
 int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard,
                                 int** d_index, int** d_n);

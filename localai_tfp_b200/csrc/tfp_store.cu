@@ -187,6 +187,7 @@ struct tfp_find_ctx {
     PinBuf h_status;
     // sharded finds: communicator, gathered records, merged answer
     void* nccl_comm = nullptr;
+    bool comm_owned = false;
     int comm_rank = 0, comm_world = 0;
     DevBuf gathered, merged;
     int merged_topk = 0;
@@ -650,7 +651,8 @@ static void ctx_destroy(tfp_find_ctx* c) {
     if (!c) return;
     tfp_store* s = c->st;
     if (c->stream) cudaStreamSynchronize(c->stream);
-    if (c->nccl_comm && g_nccl.CommDestroy) { g_nccl.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+    if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+    c->nccl_comm = nullptr;
     if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
                       &c->cub_tmp, &c->out_block, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
@@ -1302,12 +1304,24 @@ extern "C" int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, in
     if (!c || !unique_id || world < 1 || rank < 0 || rank >= world) return fail(2, "tfp_find_ctx_comm_init: bad argument");
     if (nccl_api()) return -5;
     if (set_device(c->st)) return -1;
-    if (c->nccl_comm) { g_nccl.CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+    if (c->nccl_comm && c->comm_owned) g_nccl.CommDestroy(c->nccl_comm);
+    c->nccl_comm = nullptr;
     NcclId id;
     memcpy(&id, unique_id, sizeof(id));
     NCCL_OK(g_nccl.CommInitRank(&c->nccl_comm, world, id, rank));
+    c->comm_owned = true;
     c->comm_rank = rank;
     c->comm_world = world;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner) {
+    if (!c || !owner || !owner->nccl_comm || c->st != owner->st) return fail(2, "tfp_find_ctx_comm_share: bad argument");
+    if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
+    c->nccl_comm = owner->nccl_comm;
+    c->comm_owned = false;
+    c->comm_rank = owner->comm_rank;
+    c->comm_world = owner->comm_world;
     return 0;
 }
 

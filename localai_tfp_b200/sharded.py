@@ -156,10 +156,14 @@ class CudaShardOps:
         for lane in self.lanes:
             lane.ctx.upload(qs)
 
-    def init_native_comm(self, rank: int, world: int, group=None):
-        """One NCCL communicator per lane, created inside libtfpstore (the id travels over
-        torch.distributed).  After this, find_merged() does scan + all-gather + merge in ONE call."""
-        for lane in self.lanes:
+    def init_native_comm(self, rank: int, world: int, group=None, shared: bool = True):
+        """NCCL communicator(s) created inside libtfpstore (the id travels over torch.distributed): one
+        shared by all lanes (NCCL orders their all-gathers) or one per lane.  After this, find_merged()
+        does scan + all-gather + merge in ONE library call."""
+        for i, lane in enumerate(self.lanes):
+            if shared and i > 0:
+                lane.ctx.comm_share(self.lanes[0].ctx)
+                continue
             box = [nccl_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(box, src=0, group=group)
             lane.ctx.comm_init(box[0], rank, world)

@@ -279,6 +279,9 @@ class FindContext:
         buf = C.create_string_buffer(unique_id, 128)
         self.store._check(self._L.tfp_find_ctx_comm_init(self._h, buf, rank, world))
 
+    def comm_share(self, owner: "FindContext"):
+        self.store._check(self._L.tfp_find_ctx_comm_share(self._h, owner._h))
+
     def launch_sharded(self, qi: int, topk: int):
         self.store._check(self._L.tfp_find_ctx_launch_sharded(self._h, qi, topk))
         self._topk = topk
