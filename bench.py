@@ -199,7 +199,12 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     if sharded:
         sharded.key_len = DIM
         if args.exchange != "torch":            # scan + ncclAllGather + merge become one library call
-            ops.init_native_comm(rank, world, shared=(args.exchange == "native"))
+            try:
+                ops.init_native_comm(rank, world, shared=(args.exchange == "native"))
+            except Exception as e:              # NCCL not resolvable by dlopen: same exchange through torch.distributed
+                if rank == 0:
+                    print(f"bench: native exchange unavailable ({e}); using torch.distributed", file=sys.stderr)
+                args.exchange = "torch"
 
     Q = gen_queries()
     ctx = ops.ctx
@@ -360,7 +365,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=["c2", "target"], default="c2")
-    ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="torch",
+    ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="native",
                     help="N>1: all-gather through torch.distributed, or inside libtfpstore (one call per query)")
     args = ap.parse_args()
     select_workload(args.workload)
