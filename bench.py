@@ -32,6 +32,7 @@ N_KEYS = 1_000_000
 DIM = 768
 TOPK = 10
 N_QUERIES = 64
+QUERIES_PER_STEP = 1
 BLOCK_ROWS = 62_500            # generation granularity: 16 blocks, so 1/2/4/8 shards align with blocks
 SEED = 0x5EED0002
 WORKLOAD = "C2 (BASELINE.json configs[1]): 1M keys x 768-d fp32, single-query top-10, normalised-key fast path"
@@ -42,9 +43,15 @@ def select_workload(name: str):
     """`c2` is the bench contract's workload.  `target` is the north star's stated target shape
     (10M keys x 1024-d, top-10, batch 1: 41 GB, strong-scaled over the GPUs) for extra evidence."""
     global N_KEYS, DIM, WORKLOAD, SEED
+    global TOPK, QUERIES_PER_STEP, METRIC
     if name == "target":
         N_KEYS, DIM, SEED = 10_000_000, 1024, 0x5EED0003
         WORKLOAD = "north-star target: 10M keys x 1024-d fp32, single-query top-10, normalised-key fast path"
+    if name == "c3":
+        N_KEYS, DIM, SEED, TOPK, QUERIES_PER_STEP = 10_000_000, 1024, 0x5EED0003, 100, 256
+        METRIC = "StoresFind queries/sec (top-100, batch 256)"
+        WORKLOAD = ("C3 (BASELINE.json configs[2]): 10M keys x 1024-d fp32, batch-256 queries top-100 on the "
+                    "tensor-core path (tcgen05 3xTF32 filter + exact re-score)")
 
 
 # ----------------------------------------------------------------------------- inputs
@@ -58,7 +65,7 @@ def gen_block_torch(block: int, device):
 
 def gen_queries() -> np.ndarray:
     rng = np.random.default_rng(SEED + 1)
-    q = rng.standard_normal((N_QUERIES, DIM)).astype(np.float32)
+    q = rng.standard_normal((max(N_QUERIES, QUERIES_PER_STEP), DIM)).astype(np.float32)
     q /= np.linalg.norm(q.astype(np.float64), axis=1, keepdims=True).astype(np.float32)
     return np.ascontiguousarray(q.astype(np.float32))
 
@@ -214,14 +221,21 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     # Two finds are kept in flight (two find-contexts, alternating): the next query's CTAs fill the
     # SMs that the previous query's tail and merge leave idle and, at N > 1, its scan overlaps the
     # previous query's all-gather.  Every query is still its own scan (batch 1).
-    in_flight = 2
+    in_flight = 2 if QUERIES_PER_STEP == 1 else 1
     ctx_b = ops.lanes[1].ctx
     ctx_b.upload(Q)
     ctx_b.sync()
     stream_b = ops.lanes[1].stream
 
+    batched = QUERIES_PER_STEP > 1
+
     def step_device(i: int):
-        if world == 1:
+        if batched:          # one batch of QUERIES_PER_STEP queries per step (tensor-core path)
+            if world == 1:
+                ctx.launch(0, QUERIES_PER_STEP, TOPK)
+            else:
+                ctx.launch_sharded(0, TOPK, count=QUERIES_PER_STEP)
+        elif world == 1:
             (ctx if i % 2 == 0 else ctx_b).launch(i % N_QUERIES, 1, TOPK)
         else:
             sharded.find_device(i % N_QUERIES, TOPK, with_keys=False, lane=i % 2)
@@ -262,7 +276,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total = float(t.item())
     ms_per_step = ms_total / args.steps
-    qps = 1e3 / ms_per_step
+    qps = 1e3 / ms_per_step * QUERIES_PER_STEP
 
     # ---- the scan kernel alone for the roofline: back to back on ONE stream, nothing overlapping it
     with torch.cuda.stream(stream):
@@ -271,7 +285,10 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         torch.cuda.synchronize(device)
         s0.record(stream)
         for i in range(k):
-            ctx.launch(i % N_QUERIES, 1, TOPK)
+            if batched:
+                ctx.launch(0, QUERIES_PER_STEP, TOPK)
+            else:
+                ctx.launch(i % N_QUERIES, 1, TOPK)
         s1.record(stream)
         torch.cuda.synchronize(device)
         scan_ms = s0.elapsed_time(s1) / k
@@ -283,6 +300,17 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
     except Exception:
         pass
+    roof_bound, roof_unit, roof_kernel = "hbm", "GB/s", "scan_tma_kernel<1,fp32,fused>"
+    if batched:
+        # tensor-bound: credited flops = 2 * Q * rows * D per batch (the 3xTF32 scheme issues 3x that)
+        roof_bound, roof_unit, roof_kernel = "tensor", "TFLOP/s", "mma_scan_kernel (tcgen05.mma kind::tf32)"
+        achieved = 2.0 * QUERIES_PER_STEP * rows_local * DIM / (scan_ms * 1e-3) / 1e12
+        peak, peak_src = 1590.0 / 2, "fallback (B200_PROFILING.md bf16 1.59 PFLOP/s, halved for TF32)"
+        try:
+            peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"]) / 2
+            peak_src = "derived: half of the measured bf16 burst peak (MEASURED_PEAKS.json bf16_tflops); TF32 dense runs at half the bf16 rate"
+        except Exception:
+            pass
     traffic = None
     try:
         if args.workload == "c2" and world == 1:     # the ncu capture was taken on exactly this launch shape
@@ -293,7 +321,25 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     # ---- end to end through the public call: host query in, host (ids, sims, keys) out, every step
     e2e_steps = args.steps
     barrier()
-    if world == 1:
+    if batched:
+        e2e_steps = min(args.steps, 20)
+        qb = Q[:QUERIES_PER_STEP]
+
+        def e2e_once():
+            if world == 1:
+                return store.find_batch(qb, TOPK)[0][1]
+            ctx.upload(qb)
+            ctx.launch_sharded(0, TOPK, count=QUERIES_PER_STEP)
+            return ctx.download_merged()[0][1]
+        e2e_once()
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            sims = e2e_once()
+        torch.cuda.synchronize(device)
+        e2e_dt = time.perf_counter() - t0
+        ctx.upload(Q)
+    elif world == 1:
         for i in range(min(args.warmup, 5)):
             store.StoresFind(Q[i % N_QUERIES], TOPK)
         barrier()
@@ -314,10 +360,10 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     t = torch.tensor([e2e_dt], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_qps = e2e_steps / float(t.item())
+    e2e_qps = e2e_steps * QUERIES_PER_STEP / float(t.item())
     assert len(sims) == TOPK and list(sims) == sorted(sims, reverse=True)
-    h2d = DIM * 4 + 16                                   # query + its QInfo record
-    d2h = 4 + TOPK * (8 + 4) + TOPK * DIM * 4            # n, ids, sims, key rows
+    h2d = QUERIES_PER_STEP * (DIM * 4 + 16)              # queries + their QInfo records
+    d2h = QUERIES_PER_STEP * (4 + TOPK * (8 + 4)) + (TOPK * DIM * 4 if not batched else 0)   # n, ids, sims (+ key rows)
 
     # ---- CPU baseline beside it (rank 0, N=1 only)
     cpu = None
@@ -331,7 +377,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "keys": N_KEYS, "dim": DIM, "topk": TOPK, "queries_per_step": 1,
+            "config": {"workload": WORKLOAD, "keys": N_KEYS, "dim": DIM, "topk": TOPK, "queries_per_step": QUERIES_PER_STEP,
                        "path": "normalized", "rows_per_gpu": rows_local, "finds_in_flight": in_flight,
                        "exchange": args.exchange if world > 1 else None,
                        "l2": "inputs larger than L2 (keys %.2f GB per GPU vs 126 MB); no flush" % (algo_bytes / 1e9)
@@ -339,15 +385,18 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                        "parallelism": "row-sharded x%d, one ncclAllGather of top-k records + device merge per query" % world
                                       if world > 1 else "single GPU"},
             "clocks": clk,
+            "tensor_core_path": dict(zip(("passes", "exact_reruns"), ctx.mma_counters())) if batched else None,
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "scan_tma_kernel<1,fp32,fused>",
+            "roofline": {"bound": roof_bound, "achieved": achieved, "peak": peak, "unit": roof_unit, "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "kernel": roof_kernel,
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": scan_ms,
                          "note": "achieved = bytes / duration of one scan launched alone back to back on one stream; "
                                  "`value` overlaps the tail of one scan with the start of the next (finds_in_flight)",
                          "effective_gbs_in_timed_region": algo_bytes / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
-                         "frac_of_nominal_8TBs": achieved / 8000.0},
+                         "frac_of_nominal_8TBs": achieved / 8000.0 if not batched else None,
+                         "issued_tf32_tflops": 3 * achieved if batched else None,
+                         "frac_of_nominal_tf32_1100": 3 * achieved / 1100.0 if batched else None},
         }
         if cpu:
             line["cpu_baseline"] = cpu
@@ -364,7 +413,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--workload", choices=["c2", "target"], default="c2")
+    ap.add_argument("--workload", choices=["c2", "target", "c3"], default="c2")
     ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="native",
                     help="N>1: all-gather through torch.distributed, or inside libtfpstore (one call per query)")
     args = ap.parse_args()

@@ -194,18 +194,29 @@ int tfp_merge_records(const void* d_gathered, int n_shards, int nq, int topk,
  *   tfp_find_ctx_launch_sharded  scan this shard for staged query `qi`, all-gather the
  *                        records, merge.  Returns without waiting.  Every rank must issue
  *                        the same sequence of sharded launches per context.
- *   tfp_find_ctx_merged_results  device pointers of the merged answer ([topk] each, n[1]).
- *   tfp_find_ctx_download_merged wait and copy the merged answer to the host. */
+ *   tfp_find_ctx_merged_results  device pointers of the merged answer ([count x topk] each, n[count]).
+ *   tfp_find_ctx_download_merged wait and copy the merged answer to the host (stride topk per query). */
 int tfp_nccl_unique_id(void* out_id, size_t out_bytes);
 int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int world);
 /* Let `c` use the communicator `owner` created (both contexts of one store).  NCCL then orders
  * their collectives one after the other; `owner` must outlive `c`'s last sharded launch. */
 int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner);
 int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk);
+/* Same for staged queries [first, first+count): one all-gather of count records, one merge CTA per
+ * query.  Batches of >= 32 same-path queries take the tensor-core path on every shard. */
+int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk);
 int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard,
                                 int** d_index, int** d_n);
 int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims,
                                  int* out_shard, int* out_index);
+
+/* ---- pinned host staging (no reference counterpart) --------------------------------
+ * Keys handed to tfp_store_set / queries handed to the find entry points are copied to
+ * the GPU from wherever they are; from ordinary (pageable) memory that copy runs at
+ * ~7 GB/s.  A host that fills its request buffers directly in memory obtained here
+ * (page-locked) gets the full PCIe rate.  Plain malloc/free semantics. */
+void* tfp_host_alloc(size_t bytes);
+void  tfp_host_free(void* p);
 
 /* ---- a find that allocates nothing ----------------------------------------------
  * This entry point has no counterpart in the reference.

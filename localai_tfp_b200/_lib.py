@@ -55,8 +55,11 @@ PROTOTYPES = {
     "tfp_find_ctx_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int]),
     "tfp_find_ctx_comm_share": (C.c_int, [vp, vp]),
     "tfp_find_ctx_launch_sharded": (C.c_int, [vp, C.c_int, C.c_int]),
+    "tfp_find_ctx_launch_sharded_batch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
     "tfp_find_ctx_merged_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "tfp_find_ctx_download_merged": (C.c_int, [vp, i32p, i64p, fp, i32p, i32p]),
+    "tfp_host_alloc": (vp, [C.c_size_t]),
+    "tfp_host_free": (None, [vp]),
     "tfp_scan_topk_noalloc": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp]),
     "tfp_version": (C.c_char_p, []),
 }

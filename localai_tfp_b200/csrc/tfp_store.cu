@@ -190,7 +190,7 @@ struct tfp_find_ctx {
     bool comm_owned = false;
     int comm_rank = 0, comm_world = 0;
     DevBuf gathered, merged;
-    int merged_topk = 0;
+    int merged_topk = 0, merged_count = 0;
     int64_t mma_passes = 0, mma_fallbacks = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
@@ -1325,47 +1325,52 @@ extern "C" int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner) {
     return 0;
 }
 
-// merged buffer layout: sims[topk] f32 | ids[topk] i64 | shard[topk] i32 | index[topk] i32 | n i32 (each 16-aligned)
-struct MergedLayout {
+struct MergedLayout {   // [count x topk] sims f32 | ids i64 | shard i32 | index i32 | n[count] i32 (each 16-aligned)
     size_t sims, ids, shard, index, n, total;
-    explicit MergedLayout(int k) {
+    MergedLayout(int k, int count) {
         auto up = [](size_t v) { return (v + 15) & ~(size_t)15; };
-        sims = 0; ids = up((size_t)k * 4); shard = ids + (size_t)k * 8; index = up(shard + (size_t)k * 4);
-        n = up(index + (size_t)k * 4); total = n + 16;
+        const size_t e = (size_t)k * count;
+        sims = 0; ids = up(e * 4); shard = ids + e * 8; index = up(shard + e * 4);
+        n = up(index + e * 4); total = up(n + (size_t)count * 4);
     }
 };
 
-extern "C" int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk) {
+extern "C" int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk) {
     if (!c) return fail(2, "tfp_find_ctx_launch_sharded: ctx is NULL");
     if (!c->nccl_comm) return fail(2, "tfp_find_ctx_launch_sharded: call tfp_find_ctx_comm_init first");
     std::shared_lock<std::shared_mutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
-    int rc = ctx_launch_locked(c, qi, 1, topk);
+    int rc = ctx_launch_locked(c, first, count, topk);
     if (rc) return rc;
-    const size_t rb = record_bytes(c->last_topk);
-    const int world = c->comm_world;
-    if ((int64_t)world * c->last_topk > 16384) return fail(2, "sharded find: world x topk = %lld exceeds 16384", (long long)world * c->last_topk);
-    MergedLayout L(c->last_topk);
-    if (c->gathered.reserve(rb * world) || c->merged.reserve(L.total)) return -1;
-    NCCL_OK(g_nccl.AllGather(c->out_rec, c->gathered.p, rb, /*ncclUint8*/ 1, c->nccl_comm, c->stream));
-    uint8_t* m = c->merged.as<uint8_t>();
     const int k = c->last_topk;
+    const size_t rb = record_bytes(k);
+    const int world = c->comm_world;
+    if ((int64_t)world * k > 16384) return fail(2, "sharded find: world x topk = %lld exceeds 16384", (long long)world * k);
+    MergedLayout L(k, count);
+    if (c->gathered.reserve(rb * count * world) || c->merged.reserve(L.total)) return -1;
+    NCCL_OK(g_nccl.AllGather(c->out_rec, c->gathered.p, rb * count, /*ncclUint8*/ 1, c->nccl_comm, c->stream));
+    uint8_t* m = c->merged.as<uint8_t>();
     int P = next_pow2(std::max(world * k, 2));
     if ((size_t)P * 8 > 48 * 1024)
         CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
-    merge_records_kernel<<<1, 256, (size_t)P * 8, c->stream>>>(c->gathered.as<uint8_t>(), (int)rb, world, 1, k, P,
-                                                              (float*)(m + L.sims), (int64_t*)(m + L.ids),
-                                                              (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n));
+    merge_records_kernel<<<count, 256, (size_t)P * 8, c->stream>>>(c->gathered.as<uint8_t>(), (int)rb, world, count, k, P,
+                                                                  (float*)(m + L.sims), (int64_t*)(m + L.ids),
+                                                                  (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n));
     CU_OK(cudaGetLastError());
     c->launches++;
     c->merged_topk = k;
+    c->merged_count = count;
     return 0;
+}
+
+extern "C" int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk) {
+    return tfp_find_ctx_launch_sharded_batch(c, qi, 1, topk);
 }
 
 extern "C" int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard, int** d_index,
                                            int** d_n) {
     if (!c || c->merged_topk <= 0) return fail(2, "tfp_find_ctx_merged_results: no sharded launch on this context");
-    MergedLayout L(c->merged_topk);
+    MergedLayout L(c->merged_topk, c->merged_count);
     uint8_t* m = c->merged.as<uint8_t>();
     if (d_sims) *d_sims = (float*)(m + L.sims);
     if (d_ids) *d_ids = (int64_t*)(m + L.ids);
@@ -1379,17 +1384,31 @@ extern "C" int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t
                                             int* out_index) {
     if (!c || c->merged_topk <= 0) return fail(2, "tfp_find_ctx_download_merged: no sharded launch on this context");
     if (set_device(c->st)) return -1;
-    const int k = c->merged_topk;
-    MergedLayout L(k);
+    const int k = c->merged_topk, count = c->merged_count;
+    MergedLayout L(k, count);
     if (c->h_out.reserve(L.total)) return -1;
     uint8_t* h = (uint8_t*)c->h_out.p;
     CU_OK(cudaMemcpyAsync(h, c->merged.p, L.total, cudaMemcpyDeviceToHost, c->stream));
     CU_OK(cudaStreamSynchronize(c->stream));
-    const int m = *(const int*)(h + L.n);
-    if (out_n) *out_n = m;
-    if (out_ids) memcpy(out_ids, h + L.ids, (size_t)m * 8);
-    if (out_sims) memcpy(out_sims, h + L.sims, (size_t)m * 4);
-    if (out_shard) memcpy(out_shard, h + L.shard, (size_t)m * 4);
-    if (out_index) memcpy(out_index, h + L.index, (size_t)m * 4);
+    for (int q = 0; q < count; q++) {
+        const int m = ((const int*)(h + L.n))[q];
+        const size_t o = (size_t)q * k;
+        if (out_n) out_n[q] = m;
+        if (out_ids) memcpy(out_ids + o, h + L.ids + o * 8, (size_t)m * 8);
+        if (out_sims) memcpy(out_sims + o, h + L.sims + o * 4, (size_t)m * 4);
+        if (out_shard) memcpy(out_shard + o, h + L.shard + o * 4, (size_t)m * 4);
+        if (out_index) memcpy(out_index + o, h + L.index + o * 4, (size_t)m * 4);
+    }
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// pinned host staging
+// ---------------------------------------------------------------------------
+extern "C" void* tfp_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) { fail(-1, "cudaMallocHost(%zu) failed: %s", bytes, cudaGetErrorString(e)); return nullptr; }
+    return p;
+}
+extern "C" void tfp_host_free(void* p) { if (p) cudaFreeHost(p); }

@@ -282,9 +282,10 @@ class FindContext:
     def comm_share(self, owner: "FindContext"):
         self.store._check(self._L.tfp_find_ctx_comm_share(self._h, owner._h))
 
-    def launch_sharded(self, qi: int, topk: int):
-        self.store._check(self._L.tfp_find_ctx_launch_sharded(self._h, qi, topk))
+    def launch_sharded(self, qi: int, topk: int, count: int = 1):
+        self.store._check(self._L.tfp_find_ctx_launch_sharded_batch(self._h, qi, count, topk))
         self._topk = topk
+        self._count = count
 
     def merged_results(self):
         """Device addresses (sims, ids, shard, index, n) of the last sharded launch's merged answer."""
@@ -293,14 +294,17 @@ class FindContext:
         return tuple(x.value for x in p)
 
     def download_merged(self):
-        k = self._topk
-        n = C.c_int()
-        ids = np.empty(k, np.int64); sims = np.empty(k, np.float32)
-        shard = np.empty(k, np.int32); index = np.empty(k, np.int32)
-        self.store._check(self._L.tfp_find_ctx_download_merged(self._h, C.byref(n), _p(ids, i64p), _p(sims, fp),
+        k, cnt = self._topk, self._count
+        n = np.empty(cnt, np.int32)
+        ids = np.empty((cnt, k), np.int64); sims = np.empty((cnt, k), np.float32)
+        shard = np.empty((cnt, k), np.int32); index = np.empty((cnt, k), np.int32)
+        self.store._check(self._L.tfp_find_ctx_download_merged(self._h, _p(n, i32p), _p(ids, i64p), _p(sims, fp),
                                                                _p(shard, i32p), _p(index, i32p)))
-        m = n.value
-        return ids[:m].copy(), sims[:m].copy(), shard[:m].copy(), index[:m].copy()
+        if cnt == 1:
+            m = int(n[0])
+            return ids[0, :m].copy(), sims[0, :m].copy(), shard[0, :m].copy(), index[0, :m].copy()
+        return [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy(), shard[i, :n[i]].copy(), index[i, :n[i]].copy())
+                for i in range(cnt)]
 
     def mma_counters(self):
         """(tensor-core passes, queries re-run on the exact kernel) so far on this context."""
