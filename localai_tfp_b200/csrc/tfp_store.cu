@@ -144,6 +144,106 @@ static NcclApi g_nccl;
 static std::once_flag g_nccl_once;
 
 // ---------------------------------------------------------------------------
+// Growable HBM arrays on CUDA virtual memory management: a large virtual range is reserved once,
+// physical memory is mapped behind it as the store grows.  The base address never changes, no
+// row is ever copied to grow, and the peak footprint is the data itself -- what lets one shard
+// approach the 180 GB of a B200 (a realloc-and-copy array would need twice its size to grow).
+// Driver entry points are resolved at run time (no -lcuda link).
+// ---------------------------------------------------------------------------
+struct VmmApi {
+    CUresult (*AddressReserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*AddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*Create)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long) = nullptr;
+    CUresult (*Release)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*Map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*Unmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*SetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t) = nullptr;
+    CUresult (*GetGranularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags) = nullptr;
+    bool ok = false;
+};
+static VmmApi g_vmm;
+static std::once_flag g_vmm_once;
+static bool vmm_api() {
+    std::call_once(g_vmm_once, [] {
+        auto get = [](const char* name) -> void* {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint(name, &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) return nullptr;
+            return fn;
+        };
+        g_vmm.AddressReserve = (decltype(g_vmm.AddressReserve))get("cuMemAddressReserve");
+        g_vmm.AddressFree = (decltype(g_vmm.AddressFree))get("cuMemAddressFree");
+        g_vmm.Create = (decltype(g_vmm.Create))get("cuMemCreate");
+        g_vmm.Release = (decltype(g_vmm.Release))get("cuMemRelease");
+        g_vmm.Map = (decltype(g_vmm.Map))get("cuMemMap");
+        g_vmm.Unmap = (decltype(g_vmm.Unmap))get("cuMemUnmap");
+        g_vmm.SetAccess = (decltype(g_vmm.SetAccess))get("cuMemSetAccess");
+        g_vmm.GetGranularity = (decltype(g_vmm.GetGranularity))get("cuMemGetAllocationGranularity");
+        g_vmm.ok = g_vmm.AddressReserve && g_vmm.AddressFree && g_vmm.Create && g_vmm.Release && g_vmm.Map &&
+                   g_vmm.Unmap && g_vmm.SetAccess && g_vmm.GetGranularity && getenv("TFP_DISABLE_VMM") == nullptr;
+    });
+    return g_vmm.ok;
+}
+
+struct VmmArray {
+    CUdeviceptr base = 0;
+    size_t reserved = 0, mapped = 0, gran = 0;
+    int device = 0;
+    std::vector<std::pair<CUmemGenericAllocationHandle, size_t>> chunks;
+
+    bool active() const { return base != 0; }
+    // Reserve `bytes` of address space (no memory yet).
+    int reserve(int dev, size_t bytes) {
+        device = dev;
+        CUmemAllocationProp prop;
+        memset(&prop, 0, sizeof(prop));
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = dev;
+        if (g_vmm.GetGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) != CUDA_SUCCESS || gran == 0)
+            return fail(-6, "cuMemGetAllocationGranularity failed");
+        reserved = (bytes + gran - 1) / gran * gran;
+        CUresult r = g_vmm.AddressReserve(&base, reserved, 0, 0, 0);
+        if (r != CUDA_SUCCESS) { base = 0; return fail(-6, "cuMemAddressReserve(%zu) failed with CUresult %d", reserved, (int)r); }
+        return 0;
+    }
+    // Make at least `bytes` from the base usable.
+    int grow(size_t bytes) {
+        if (bytes <= mapped) return 0;
+        if (bytes > reserved) return fail(-6, "store array would exceed its reserved address range (%zu > %zu)", bytes, reserved);
+        size_t want = (bytes - mapped + gran - 1) / gran * gran;
+        CUmemAllocationProp prop;
+        memset(&prop, 0, sizeof(prop));
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = device;
+        CUmemGenericAllocationHandle h;
+        CUresult r = g_vmm.Create(&h, want, &prop, 0);
+        if (r != CUDA_SUCCESS) return fail(-6, "cuMemCreate(%zu) failed with CUresult %d (out of HBM?)", want, (int)r);
+        r = g_vmm.Map(base + mapped, want, 0, h, 0);
+        if (r != CUDA_SUCCESS) { g_vmm.Release(h); return fail(-6, "cuMemMap failed with CUresult %d", (int)r); }
+        CUmemAccessDesc acc;
+        memset(&acc, 0, sizeof(acc));
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = device;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        r = g_vmm.SetAccess(base + mapped, want, &acc, 1);
+        if (r != CUDA_SUCCESS) { g_vmm.Unmap(base + mapped, want); g_vmm.Release(h); return fail(-6, "cuMemSetAccess failed with CUresult %d", (int)r); }
+        chunks.emplace_back(h, want);
+        mapped += want;
+        return 0;
+    }
+    void release() {
+        if (!base) return;
+        size_t off = 0;
+        for (auto& c : chunks) { g_vmm.Unmap(base + off, c.second); g_vmm.Release(c.first); off += c.second; }
+        chunks.clear();
+        g_vmm.AddressFree(base, reserved);
+        base = 0; reserved = mapped = 0;
+    }
+};
+
+// ---------------------------------------------------------------------------
 // the store
 // ---------------------------------------------------------------------------
 struct tfp_find_ctx;
@@ -155,6 +255,7 @@ struct tfp_store {
     bool normalized = true;    // store.go:27,43 keysAreNormalized (sticky)
     int64_t n = 0, cap = 0, cap_hint = 0;
     int64_t next_id = 0;
+    VmmArray vm_keys, vm_ids, vm_knorm;   // backing of the three arrays when virtual memory management is available
     float* d_keys = nullptr;
     int64_t* d_ids = nullptr;
     double* d_knorm = nullptr;
@@ -233,8 +334,36 @@ static int encode_tmap(tfp_store* s) {
 // Grow the HBM arrays to hold `rows` rows (dim must be latched).
 static int ensure_capacity(tfp_store* s, int64_t rows) {
     if (rows <= s->cap) return 0;
+    if (rows > 0xFFFFFFF0ll) return fail(-3, "store shard would exceed 2^32 rows");
+    const size_t row_bytes = (size_t)s->dim * 4;
+    if (vmm_api()) {
+        // virtual memory: map more physical memory behind fixed addresses; nothing is copied
+        if (!s->vm_keys.active()) {
+            size_t free_b = 0, total_b = 0;
+            CU_OK(cudaMemGetInfo(&free_b, &total_b));
+            int64_t max_rows = (int64_t)std::min<size_t>((size_t)0xFFFFFFF0ull, total_b / row_bytes + 1);
+            if (s->vm_keys.reserve(s->device, (size_t)max_rows * row_bytes + 4096) ||
+                s->vm_ids.reserve(s->device, (size_t)max_rows * 8) || s->vm_knorm.reserve(s->device, (size_t)max_rows * 8))
+                return -6;
+            s->d_keys = (float*)s->vm_keys.base;
+            s->d_ids = (int64_t*)s->vm_ids.base;
+            s->d_knorm = (double*)s->vm_knorm.base;
+        }
+        int64_t ncap = std::max<int64_t>({rows, s->cap + s->cap / 4, s->cap_hint, (int64_t)1024});
+        ncap = std::min<int64_t>(ncap, 0xFFFFFFF0ll);
+        if (s->vm_keys.grow((size_t)ncap * row_bytes + 256) || s->vm_ids.grow((size_t)ncap * 8) || s->vm_knorm.grow((size_t)ncap * 8)) {
+            // the generous step did not fit: take exactly what is needed
+            ncap = rows;
+            if (s->vm_keys.grow((size_t)ncap * row_bytes + 256) || s->vm_ids.grow((size_t)ncap * 8) || s->vm_knorm.grow((size_t)ncap * 8))
+                return -6;
+        }
+        // whatever the mapping granularity added is usable too
+        int64_t by_map = (int64_t)std::min({(s->vm_keys.mapped - 256) / row_bytes, s->vm_ids.mapped / 8, s->vm_knorm.mapped / 8});
+        s->cap = std::min<int64_t>(std::max(ncap, by_map), 0xFFFFFFF0ll);
+        return encode_tmap(s);
+    }
+    // no virtual memory management: reallocate and copy
     int64_t ncap = std::max<int64_t>({rows, s->cap * 2, s->cap_hint, (int64_t)1024});
-    if (ncap > 0xFFFFFFF0ll) return fail(-3, "store shard would exceed 2^32 rows");
     float* nk = nullptr; int64_t* ni = nullptr; double* nn = nullptr;
     CU_OK(cudaMalloc(&nk, (size_t)ncap * s->dim * 4 + 256));
     CU_OK(cudaMalloc(&ni, (size_t)ncap * 8));
@@ -320,9 +449,13 @@ extern "C" void tfp_store_close(tfp_store* s) {
     cudaDeviceSynchronize();
     std::vector<tfp_find_ctx*> ctxs = s->ctxs;
     for (tfp_find_ctx* c : ctxs) ctx_destroy(c);
-    if (s->d_keys) cudaFree(s->d_keys);
-    if (s->d_ids) cudaFree(s->d_ids);
-    if (s->d_knorm) cudaFree(s->d_knorm);
+    if (s->vm_keys.active()) {
+        s->vm_keys.release(); s->vm_ids.release(); s->vm_knorm.release();
+    } else {
+        if (s->d_keys) cudaFree(s->d_keys);
+        if (s->d_ids) cudaFree(s->d_ids);
+        if (s->d_knorm) cudaFree(s->d_knorm);
+    }
     DevBuf* bufs[] = {&s->st_rows, &s->st_hash, &s->st_knorm, &s->st_isnorm, &s->st_pair_row,
                       &s->st_pair_slot, &s->st_pair_eq, &s->st_src, &s->st_dst, &s->st_ids};
     for (DevBuf* b : bufs) b->release();
@@ -335,7 +468,8 @@ extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
     std::shared_lock<std::shared_mutex> lk(s->rw);
     out->rows = s->n;
     out->capacity_rows = s->cap;
-    out->hbm_bytes = s->cap * ((int64_t)(s->dim > 0 ? s->dim : 0) * 4 + 16);
+    out->hbm_bytes = s->vm_keys.active() ? (int64_t)(s->vm_keys.mapped + s->vm_ids.mapped + s->vm_knorm.mapped)
+                                         : s->cap * ((int64_t)(s->dim > 0 ? s->dim : 0) * 4 + 16);
     out->dim = s->dim;
     out->keys_are_normalized = s->normalized ? 1 : 0;
     out->device = s->device;
