@@ -121,6 +121,14 @@ typedef struct {
 } tfp_stats;
 int tfp_store_stats(tfp_store* s, tfp_stats* out);
 
+/* ---- snapshot / restore ----------------------------------------------
+ * The reference keeps the store in process memory only (Load is a no-op, store.go:101-103): a
+ * watchdog kill or a respawn loses everything.  tfp_store_save writes rows, ids, key length, the
+ * sticky flag and the id counter to `path`; tfp_store_load fills an EMPTY store from such a file
+ * (hashes and norms are recomputed on the device).  Values stay with the host, keyed by id. */
+int tfp_store_save(tfp_store* s, const char* path);
+int tfp_store_load(tfp_store* s, const char* path);
+
 /* A shard of a logical multi-GPU store is told that another shard has seen a key that
  * is not unit length: the sticky flag (store.go:27,126-127) is a property of the whole
  * store, so every shard must leave the normalised path together. */

@@ -36,6 +36,8 @@ PROTOTYPES = {
     "tfp_store_find": (C.c_int, [vp, fp, C.c_int, C.c_int, i32p, i64p, fp, fp, i32p]),
     "tfp_store_find_batch": (C.c_int, [vp, fp, C.c_int, C.c_int, C.c_int, i32p, i64p, fp, fp]),
     "tfp_store_stats": (C.c_int, [vp, C.POINTER(TfpStats)]),
+    "tfp_store_save": (C.c_int, [vp, C.c_char_p]),
+    "tfp_store_load": (C.c_int, [vp, C.c_char_p]),
     "tfp_store_mark_not_normalized": (C.c_int, [vp]),
     "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_destroy": (None, [vp]),

@@ -769,6 +769,99 @@ extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int 
 }
 
 // ---------------------------------------------------------------------------
+// snapshot / restore
+// ---------------------------------------------------------------------------
+struct SnapHeader {
+    char magic[8];        // "TFPSTOR1"
+    int32_t dim;
+    int32_t normalized;
+    int64_t rows;
+    int64_t next_id;
+};
+
+extern "C" int tfp_store_save(tfp_store* s, const char* path) {
+    if (!s || !path) return fail(2, "tfp_store_save: NULL argument");
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (set_device(s) || quiesce_finds(s)) return -1;
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(2, "tfp_store_save: cannot open %s", path);
+    SnapHeader h;
+    memcpy(h.magic, "TFPSTOR1", 8);
+    h.dim = s->dim; h.normalized = s->normalized ? 1 : 0; h.rows = s->n; h.next_id = s->next_id;
+    bool ok = fwrite(&h, sizeof(h), 1, f) == 1;
+    const size_t chunk = (size_t)64 << 20;
+    PinBuf pin;
+    if (ok && s->n > 0 && pin.reserve(chunk)) { fclose(f); return -1; }
+    auto dump = [&](const void* dptr, size_t bytes) -> int {
+        for (size_t off = 0; ok && off < bytes; off += chunk) {
+            size_t m = std::min(chunk, bytes - off);
+            CU_OK(cudaMemcpy(pin.p, (const uint8_t*)dptr + off, m, cudaMemcpyDeviceToHost));
+            ok = fwrite(pin.p, 1, m, f) == m;
+        }
+        return 0;
+    };
+    if (s->n > 0) {
+        if (dump(s->d_keys, (size_t)s->n * s->dim * 4) || dump(s->d_ids, (size_t)s->n * 8)) { fclose(f); pin.release(); return -1; }
+    }
+    pin.release();
+    ok = (fclose(f) == 0) && ok;
+    return ok ? 0 : fail(2, "tfp_store_save: short write to %s", path);
+}
+
+extern "C" int tfp_store_load(tfp_store* s, const char* path) {
+    if (!s || !path) return fail(2, "tfp_store_load: NULL argument");
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (s->n != 0 || s->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
+    if (set_device(s)) return -1;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(2, "tfp_store_load: cannot open %s", path);
+    SnapHeader h;
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "TFPSTOR1", 8) != 0 || h.rows < 0 || h.rows > 0xFFFFFFF0ll ||
+        (h.rows > 0 && h.dim <= 0)) {
+        fclose(f);
+        return fail(2, "tfp_store_load: %s is not a store snapshot", path);
+    }
+    s->dim = h.dim;
+    s->next_id = h.next_id;
+    s->normalized = h.normalized != 0;
+    if (h.rows == 0) { fclose(f); return 0; }
+    if (ensure_capacity(s, h.rows)) { fclose(f); return -1; }
+    const size_t chunk = (size_t)64 << 20;
+    PinBuf pin;
+    if (pin.reserve(chunk)) { fclose(f); return -1; }
+    bool ok = true;
+    auto fill = [&](void* dptr, size_t bytes) -> int {
+        for (size_t off = 0; ok && off < bytes; off += chunk) {
+            size_t m = std::min(chunk, bytes - off);
+            ok = fread(pin.p, 1, m, f) == m;
+            if (ok) CU_OK(cudaMemcpy((uint8_t*)dptr + off, pin.p, m, cudaMemcpyHostToDevice));
+        }
+        return 0;
+    };
+    int rc = fill(s->d_keys, (size_t)h.rows * h.dim * 4);
+    if (!rc) rc = fill(s->d_ids, (size_t)h.rows * 8);
+    fclose(f);
+    pin.release();
+    if (rc) return rc;
+    if (!ok) { s->dim = -1; s->normalized = true; s->next_id = 0; return fail(2, "tfp_store_load: %s is truncated", path); }
+    // recompute row hashes and norms on the device, rebuild the host index and mirrors
+    const int64_t n = h.rows;
+    if (s->st_hash.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
+    row_stats_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->s_mut>>>(s->d_keys, n, s->dim, s->st_hash.as<uint64_t>(),
+                                                                        s->d_knorm, s->st_isnorm.as<uint8_t>());
+    CU_OK(cudaGetLastError());
+    s->slot_hash.resize((size_t)n);
+    s->slot_id.resize((size_t)n);
+    CU_OK(cudaMemcpyAsync(s->slot_hash.data(), s->st_hash.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
+    CU_OK(cudaMemcpyAsync(s->slot_id.data(), s->d_ids, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
+    CU_OK(cudaStreamSynchronize(s->s_mut));
+    s->index.reserve((size_t)n);
+    for (int64_t i = 0; i < n; i++) s->index.insert(s->slot_hash[(size_t)i], (uint32_t)i);
+    s->n = n;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
 // find contexts
 // ---------------------------------------------------------------------------
 static int ctx_create(tfp_store* s, tfp_find_ctx** out) {

@@ -13,6 +13,8 @@ The reference serialises RPCs with a mutex (base.SingleThread); so does this ser
 from __future__ import annotations
 
 import argparse
+import os
+import signal
 import threading
 from concurrent import futures
 
@@ -30,8 +32,11 @@ def _ident(b):
 
 
 class Backend:
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, snapshot: str | None = None):
         self.store = Store(device=device)
+        self.snapshot = snapshot
+        if snapshot and os.path.exists(snapshot) and os.path.exists(snapshot + ".values"):
+            self.store.load(snapshot)             # survive a watchdog kill / respawn
         self.lock = threading.Lock()          # base.SingleThread (pkg/grpc/base/singlethread.go:13-29)
         self.busy = False
 
@@ -80,8 +85,8 @@ class Backend:
         return wire.enc_find_result(ks, vs, sims)
 
 
-def make_server(addr: str, device: int = 0, workers: int = 8):
-    backend = Backend(device)
+def make_server(addr: str, device: int = 0, workers: int = 8, snapshot: str | None = None):
+    backend = Backend(device, snapshot)
     methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,
                                                          response_serializer=_ident)
                for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}
@@ -134,8 +139,18 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--addr", default="localhost:50051", help="the address to connect to")   # main.go:14-16
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--snapshot", default=os.environ.get("TFP_STORE_SNAPSHOT"),
+                    help="file to restore the store from at start and to save it to on SIGTERM")
     args = ap.parse_args()
-    server, _, _ = make_server(args.addr, args.device)
+    server, backend, _ = make_server(args.addr, args.device, snapshot=args.snapshot)
+
+    def on_term(signum, frame):
+        if backend.snapshot:
+            with backend.lock:
+                backend.store.save(backend.snapshot)
+        server.stop(grace=1)
+
+    signal.signal(signal.SIGTERM, on_term)
     server.start()
     server.wait_for_termination()
 

@@ -14,6 +14,7 @@ Method names and argument meaning follow store.go:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Sequence, Tuple
 
 import numpy as np
@@ -202,6 +203,21 @@ class Store:
                                                  _p(outk, fp) if with_keys else None))
         res = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy()) for i in range(nq)]
         return (res, outk) if with_keys else res
+
+    # -- snapshot / restore ---------------------------------------------------------
+    def save(self, path: str):
+        """Write the store to `path` (keys, ids, flags: the library) and `path + ".values"` (id -> bytes: the host)."""
+        import pickle
+        self._check(self._L.tfp_store_save(self._h, os.fsencode(path)))
+        with open(path + ".values", "wb") as f:
+            pickle.dump(self.values, f, protocol=4)
+
+    def load(self, path: str):
+        """Fill this (empty) store from a snapshot written by save()."""
+        import pickle
+        self._check(self._L.tfp_store_load(self._h, os.fsencode(path)))
+        with open(path + ".values", "rb") as f:
+            self.values = pickle.load(f)
 
     def mark_not_normalized(self):
         self._check(self._L.tfp_store_mark_not_normalized(self._h))

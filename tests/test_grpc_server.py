@@ -105,3 +105,32 @@ def test_c1_shape_over_grpc(client, oracle):             # BASELINE.json configs
     for _ in range(50):
         client.find(q, 10)
     print(f"C1 over loopback gRPC: {(time.perf_counter() - t0) / 50 * 1e6:.0f} us per StoresFind")
+
+
+def test_snapshot_survives_a_respawn(tfp, tmp_path):
+    """The reference loses the store when LocalAI's watchdog kills the backend; with
+    --snapshot the respawned process answers as before."""
+    from localai_tfp_b200.server import Client
+    snap = str(tmp_path / "store.snap")
+
+    def spawn():
+        s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+        addr = f"127.0.0.1:{port}"
+        proc = subprocess.Popen([sys.executable, "-m", "localai_tfp_b200.server", "--addr", addr, "--snapshot", snap])
+        c = Client(addr)
+        for attempt in range(60):
+            try:
+                if c.health() == b"OK":
+                    return proc, c
+            except grpc.RpcError:
+                time.sleep(0.5)
+        raise RuntimeError("backend did not become healthy")
+
+    proc, c = spawn()
+    c.set([[0.5, 0.5, 0.5], [0.6, 0.6, -0.6], [0.7, -0.7, -0.7]], [b"test1", b"test2", b"test3"])
+    before = c.find([0.1, 0.3, 0.5], 2)
+    c.close(); proc.terminate(); proc.wait(timeout=30)
+    proc, c = spawn()
+    after = c.find([0.1, 0.3, 0.5], 2)
+    assert after[1] == before[1] == [b"test1", b"test2"] and np.array_equal(after[2], before[2])
+    c.close(); proc.terminate(); proc.wait(timeout=30)

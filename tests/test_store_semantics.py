@@ -240,3 +240,29 @@ def test_random_mutation_stream_matches_oracle(pair):
             a, b = both(pair, "StoresFind", ks[0], int(rng.integers(1, 12)))
             same_find(a, b)
         assert len(gpu) == len(orc)
+
+
+def test_snapshot_and_restore(tfp, oracle, tmp_path):
+    """a saved store answers like the original after a restart (new process state = new Store)."""
+    from conftest import make_keys
+    K = make_keys(3000, 96, seed=3, normalized=True)
+    vals = [b"v%d" % i for i in range(len(K))]
+    a = tfp.Store()
+    a.StoresSet(K, vals)
+    a.StoresDelete(K[100:300])
+    a.StoresSet([(K[0] * f32(2)).astype(f32)], [b"big"])       # flips the sticky flag
+    a.StoresDelete([(K[0] * f32(2)).astype(f32)])
+    path = str(tmp_path / "store.snap")
+    a.save(path)
+    b = tfp.Store()
+    b.load(path)
+    assert len(b) == len(a) == 2800 and b.key_len == 96 and not b.keys_are_normalized
+    for q in (K[5], K[2999], K[150]):
+        ra, rb = a.StoresFind(q, 10), b.StoresFind(q, 10)
+        assert np.array_equal(ra[2], rb[2]) and ra[1] == rb[1]
+    assert b.StoresGet(K[[7, 150, 2000]])[1] == [b"v7", b"v2000"] or b.StoresGet(K[[7, 150, 2000]])[1] == [b"v2000", b"v7"]
+    b.StoresSet(K[100:110], [b"again"] * 10)                    # ids continue after the restored counter
+    assert len(b) == 2810 and len(set(b.values)) == 2810
+    with pytest.raises(tfp.StoreError):
+        b.load(path)                                            # only an empty store can be restored into
+    a.close(); b.close()
