@@ -5,23 +5,34 @@
 // reference loop (backend/go/stores/store.go:378-389 / :441-452) -- the reference has no
 // batched path at all.
 //
-// Numerics: tensor cores only FILTER.  Each fp32 operand is split into a TF32 "hi" part and a
-// TF32 "lo" remainder (a = hi + lo up to 2^-22); S ~= hi.hi + hi.lo + lo.hi (3xTF32, fp32
-// accumulation in TMEM), good to ~1e-6.  Per query the rows whose approximate score clears a
-// proven lower bound of its 148th best score are kept as candidates; finalize (below) takes the
-// best k+48 of them and RE-SCORES them in the reference's exact arithmetic (index-order fp32
-// dot, or fp64-accumulated cosine), so the similarities returned are bit-identical to the Go
-// code, exactly as on the single-query path.  A query whose candidate list overflowed or came
-// out short is flagged and re-run by the host on the exact scan kernel -- still on the GPU.
+// Numerics: tensor cores only FILTER; finalize (below) RE-SCORES the surviving rows in the
+// reference's exact arithmetic (index-order fp32 dot, or fp64-accumulated cosine), so the
+// similarities returned are bit-identical to the Go code, exactly as on the single-query path.
+// Two filters (template TERMS):
+//   TERMS = 1  one TF32 MMA per K-step on the raw fp32 operands.  TF32 keeps 10 mantissa bits, so
+//              each operand is off by < 2^-10 relative and |approx - exact| <= eps with
+//              eps = (2^-9 + D 2^-23) |q| |k| (Cauchy-Schwarz; the D term covers the reference's
+//              own fp32 rounding).  Every row within 2 eps of the k-th best approximate score is
+//              re-scored: a row outside that band provably cannot be in the exact top-k.  The scan
+//              is then HBM-bound like the single-query path (one MMA per 12 KB of operands).
+//   TERMS = 3  each operand split into TF32 hi + lo (a = hi + lo to 2^-22), S ~= hi.hi + hi.lo +
+//              lo.hi, error ~1e-6; the best k+48 candidates are re-scored and the query is re-run on
+//              the exact kernel if the first row not re-scored is too close to call.  3x the MMAs
+//              and twice the query traffic: shared-memory-bandwidth bound at half the tensor peak.
+// Per query, candidates are the rows whose approximate score clears a proven lower bound of the
+// 148th best score (minus 2 eps).  A query whose candidate list overflowed or came out short is
+// flagged and re-run by the host on the exact scan kernel -- still on the GPU.
 //
 // Kernel anatomy (one persistent CTA per SM, 12 warps):
 //   warp 0      TMA producer: per 16-column chunk one key box [128 rows x 64 B] (HBM, read once)
-//               and two query boxes [nq x 64 B] (hi and lo parts, L2-resident), 64-B swizzle,
-//               into a ring of 4 stages of 48 KiB (at nq = 256);
+//               and the query box(es) [nq x 64 B] (L2-resident), 64-B swizzle, into a ring of
+//               8 stages of 24 KiB (TERMS = 1) or 4 of 48 KiB (TERMS = 3) at nq = 256.  (Sharing one
+//               query box between two key tiles was tried: it costs the second accumulator buffer,
+//               and the lost MMA/epilogue overlap outweighed the saved L2 traffic.)
 //   warps 8-11  converters: split the landed key tile into hi (in place) and lo (second tile),
 //               fence.proxy.async so the tensor core sees the generic-proxy writes;
 //   warp 1      MMA issuer: one elected thread issues tcgen05.mma.kind::tf32 (M=128, N=nq, K=8),
-//               3 per K-step, accumulating in one of two TMEM buffers; tcgen05.commit releases
+//               TERMS per K-step, accumulating in one of two TMEM buffers; tcgen05.commit releases
 //               the shared-memory stage and, after the last chunk, hands the accumulator over;
 //   warps 4-7   epilogue: tcgen05.ld the finished accumulator (thread = key row, registers =
 //               queries), scale by 1/|k| on the cosine path, compare against the per-query
@@ -35,13 +46,18 @@
 namespace tfp {
 
 constexpr int kMmaThreads = 384;
-constexpr int kMmaStages = 4;
+constexpr int kMmaStages3 = 4;          // TERMS = 3: stages of 48 KiB at nq = 256
+constexpr int kMmaStages1 = 8;          // TERMS = 1: stages of 24 KiB
+constexpr int kMmaStagesMax = 8;
+constexpr int kMmaHitQueue = 256;       // per epilogue warp: hits staged in shared memory, flushed once per tile
+constexpr int kMmaRescoreMax = 1024;    // TERMS = 1: rows re-scored per query at most (else exact re-run)
 constexpr int kMmaBoxCols = 16;         // floats per row per stage (64 B, 64-byte swizzle): small stages, deep ring
 constexpr int kMmaMaxNQ = 256;         // queries per pass == UMMA N (multiple of 16)
 constexpr int kMmaCandCap = 16384;     // candidate words per query
 constexpr int kMmaMargin = 48;         // candidates re-scored beyond k
 constexpr int kMmaMaxTopK = 100;       // k + margin must stay within the 148 rows the bound guarantees
-constexpr int kMmaATile = kRowsPerTile * kMmaBoxCols * 4;   // 8 KiB
+constexpr int kMmaRows = kRowsPerTile;                       // key rows per stage == one 128-row MMA tile
+constexpr int kMmaATile = kMmaRows * kMmaBoxCols * 4;        // 8 KiB
 constexpr int kMmaRowBytes = kMmaBoxCols * 4;                // 64
 
 struct MmaParams {
@@ -55,6 +71,8 @@ struct MmaParams {
     uint64_t* cand;              // [nq x kMmaCandCap]
     unsigned int* cand_cnt;      // [nq]
     int refresh_ns;
+    const float* eps;            // [nq] error bound of the approximate score (0 for TERMS = 3)
+    int debug;                   // development only: 1 = skip the epilogue's per-element work, 2 = issue no MMAs
 };
 
 // ---- tcgen05 wrappers ---------------------------------------------------------------------
@@ -103,6 +121,15 @@ __device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t smem_addr) {
 __host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
+// 16-byte shared load that is re-issued every time (other warps update these words)
+__device__ __forceinline__ float4 __uint4_as_float4(uint4 u) {
+    return make_float4(__uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z), __uint_as_float(u.w));
+}
+__device__ __forceinline__ uint4 lds_volatile_v4(const unsigned int* p) {
+    uint4 v;
+    asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)));
+    return v;
+}
 constexpr uint32_t kTf32Mask = 0xFFFFE000u;   // sign, exponent, 10 mantissa bits
 __device__ __forceinline__ void tf32_split(float a, float& hi, float& lo) {
     hi = __uint_as_float(__float_as_uint(a) & kTf32Mask);
@@ -121,34 +148,45 @@ __global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int 
     }
 }
 
-__host__ __device__ inline size_t mma_smem_bytes(int nqp) {
-    size_t stage = 2 * (size_t)kMmaATile + 2 * (size_t)nqp * kMmaRowBytes;
-    return kMmaStages * stage + (3 * kMmaStages + 4) * 8 + 16 + 2 * kMmaMaxNQ * 4 + 1024;
+__host__ __device__ inline size_t mma_stage_bytes(int nqp, int terms) {
+    return terms == 3 ? 2 * (size_t)kMmaATile + 2 * (size_t)nqp * kMmaRowBytes : (size_t)kMmaATile + (size_t)nqp * kMmaRowBytes;
+}
+__host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms) {
+    const int stages = terms == 3 ? kMmaStages3 : kMmaStages1;
+    return stages * mma_stage_bytes(nqp, terms) + (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 +
+           4 * (size_t)kMmaHitQueue * 16 + 16;
 }
 
+template <int TERMS>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_q, const MmaParams p) {
+    constexpr int kMmaStages = TERMS == 3 ? kMmaStages3 : kMmaStages1;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const size_t b_bytes = (size_t)p.nqp * kMmaRowBytes;
-    const size_t stage_bytes = 2 * (size_t)kMmaATile + 2 * b_bytes;
+    const size_t stage_bytes = mma_stage_bytes(p.nqp, TERMS);
+    // TERMS = 3: [a_hi | a_lo | b_hi | b_lo];  TERMS = 1: [a | b]
     auto a_hi = [&](int s) { return base + s * stage_bytes; };
     auto a_lo = [&](int s) { return base + s * stage_bytes + kMmaATile; };
-    auto b_hi = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile; };
+    auto b_hi = [&](int s) { return base + s * stage_bytes + (TERMS == 3 ? 2 : 1) * kMmaATile; };
     auto b_lo = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile + b_bytes; };
     uint8_t* tail = base + kMmaStages * stage_bytes;
     uint64_t* full = (uint64_t*)tail;            // [stages] TMA landed
-    uint64_t* conv = full + kMmaStages;          // [stages] hi/lo tiles ready
-    uint64_t* empty = conv + kMmaStages;         // [stages] stage consumed by the tensor core
-    uint64_t* acc_full = empty + kMmaStages;     // [2] accumulator complete
+    uint64_t* conv = full + kMmaStagesMax;       // [stages] hi/lo tiles ready (TERMS = 3)
+    uint64_t* empty = conv + kMmaStagesMax;      // [stages] stage consumed by the tensor core
+    uint64_t* acc_full = empty + kMmaStagesMax;  // [2] accumulator complete
     uint64_t* acc_empty = acc_full + 2;          // [2] accumulator drained
     uint32_t* tmem_base_s = (uint32_t*)(acc_empty + 2);
     volatile int* flags = (volatile int*)(tmem_base_s + 1);   // [0] done, [1] thresholds ready
     unsigned int* tau = (unsigned int*)(tmem_base_s + 4);     // [kMmaMaxNQ] admission thresholds (orderable words)
     unsigned int* lb = tau + kMmaMaxNQ;                       // [kMmaMaxNQ] this CTA's best score per query
+    float* tau_f = (float*)(lb + kMmaMaxNQ);                  // [kMmaMaxNQ] tau as a float (-inf = admit everything)
+    float* lb_f = tau_f + kMmaMaxNQ;                          // [kMmaMaxNQ] lb as a float (may lag behind lb: only a hint)
+    uint4* hitq = (uint4*)(lb_f + kMmaMaxNQ);                 // [4][kMmaHitQueue] (query, row, score bits): staged hits
+    int* hitn = (int*)(hitq + 4 * kMmaHitQueue);              // [4] entries staged per epilogue warp
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t n_tiles_all = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+    const uint32_t n_tiles_all = (p.n_rows + kMmaRows - 1) / kMmaRows;
     const uint32_t n_tiles = p.mode == 0 ? (n_tiles_all < gridDim.x ? n_tiles_all : gridDim.x) : n_tiles_all;
     const uint32_t tmem_cols = 2 * p.nqp <= 32 ? 32 : (2 * p.nqp <= 64 ? 64 : (2 * p.nqp <= 128 ? 128 : (2 * p.nqp <= 256 ? 256 : 512)));
 
@@ -165,11 +203,14 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         fence_mbar_init();
         flags[0] = 0;
         flags[1] = p.mode == 0 ? 1 : 0;    // the bound-only pass needs no thresholds
+        hitn[0] = hitn[1] = hitn[2] = hitn[3] = 0;
     }
     for (int i = tid; i < kMmaMaxNQ; i += kMmaThreads) {
         tau[i] = 0u;
+        tau_f[i] = -INFINITY;
         // the full pass continues from what the bound-only pass published for this CTA
         lb[i] = p.mode == 1 ? p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + i] : 0u;
+        lb_f[i] = lb[i] ? order_to_score(lb[i]) : -INFINITY;
     }
     if (warp == 1) tmem_alloc(tmem_base_s, tmem_cols);
     tc_fence_before();
@@ -188,10 +229,11 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
             for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int c = 0; c < p.n_chunks; c++) {
                     mbar_wait(empty + stage, phase ^ 1u);
-                    mbar_arrive_expect_tx(full + stage, (uint32_t)(kMmaATile + 2 * b_bytes));
-                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kMmaBoxCols, (int)(tile * kRowsPerTile), pol_stream);
+                    mbar_arrive_expect_tx(full + stage, (uint32_t)(kMmaATile + (TERMS == 3 ? 2 : 1) * b_bytes));
+                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kMmaBoxCols, (int)(tile * kMmaRows), pol_stream);
                     tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * kMmaBoxCols, 0, pol_keep);
-                    tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kMmaBoxCols, p.nqp, pol_keep);
+                    if constexpr (TERMS == 3)
+                        tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kMmaBoxCols, p.nqp, pol_keep);
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -207,17 +249,20 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.nqp);
                 for (int c = 0; c < p.n_chunks; c++) {
-                    mbar_wait(full + stage, phase);             // query boxes landed (keys are covered by conv)
-                    mbar_wait(conv + stage, phase);             // hi / lo key tiles written and fenced
+                    mbar_wait(full + stage, phase);             // key and query boxes landed
+                    if constexpr (TERMS == 3) mbar_wait(conv + stage, phase);   // hi / lo key tiles written and fenced
                     tc_fence_after();
-                    const uint32_t ah = smem_u32(a_hi(stage)), al = smem_u32(a_lo(stage));
-                    const uint32_t bh = smem_u32(b_hi(stage)), bl = smem_u32(b_lo(stage));
+                    const uint32_t ah = smem_u32(a_hi(stage)), bh = smem_u32(b_hi(stage));
 #pragma unroll
                     for (int k = 0; k < kMmaBoxCols / 8; k++) { // UMMA K = 8 TF32 = 32 bytes along the swizzled row
+                        if (p.debug & 2) break;
                         const uint32_t off = (uint32_t)k * 32u;
                         umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bh + off), idesc, (c | k) != 0);
-                        umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bl + off), idesc, 1u);
-                        umma_tf32(d_tmem, umma_desc_sw64(al + off), umma_desc_sw64(bh + off), idesc, 1u);
+                        if constexpr (TERMS == 3) {
+                            const uint32_t al = smem_u32(a_lo(stage)), bl = smem_u32(b_lo(stage));
+                            umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bl + off), idesc, 1u);
+                            umma_tf32(d_tmem, umma_desc_sw64(al + off), umma_desc_sw64(bh + off), idesc, 1u);
+                        }
                     }
                     umma_commit(empty + stage);                 // stage is free once these MMAs retire
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
@@ -240,7 +285,13 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                         unsigned int v = ((volatile unsigned int*)p.lbest)[(size_t)b * kMmaMaxNQ + q];
                         m = v < m ? v : m;
                     }
-                    if (m > tau[q]) ((volatile unsigned int*)tau)[q] = m;
+                    // admit everything within 2 eps below the bound (eps = 0 when the filter is 3xTF32)
+                    const float e2 = p.eps ? 2.0f * p.eps[q] : 0.0f;
+                    if (e2 > 0.0f && m != 0u && m != 0xFFFFFFFFu) m = score_to_order(order_to_score(m) - e2);
+                    if (m != 0xFFFFFFFFu && m > tau[q]) {
+                        ((volatile unsigned int*)tau)[q] = m;
+                        ((volatile float*)tau_f)[q] = order_to_score(m);
+                    }
                 }
                 __syncwarp();
                 if (lane == 0) flags[1] = 1;
@@ -262,7 +313,7 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         }
         int acc = 0; uint32_t acc_phase = 0;
         for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            const uint32_t row = tile * kRowsPerTile + (uint32_t)row_in_tile;
+            const uint32_t row = tile * kMmaRows + (uint32_t)row_in_tile;
             const bool valid = row < p.n_rows;
             const float inv = (p.f64 && valid) ? (float)(1.0 / __ldg(p.knorm + row)) : 1.0f;
             mbar_wait(acc_full + acc, acc_phase);
@@ -270,17 +321,41 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
             for (int col0 = 0; col0 < p.nqp; col0 += 32) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(acc * p.nqp + col0), v);
-                if (valid) {
+                // Thresholds and bests of these 32 queries as floats: 16 vector loads up front, then two float
+                // compares per element.  Only an element that passes one of them (rare) takes the slow path,
+                // which works on the exact orderable words.  A stale float is harmless: a lower threshold or
+                // best only sends a few more elements down the slow path.
+                float4 tq[8], bq[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    tq[i] = __uint4_as_float4(lds_volatile_v4((const unsigned int*)tau_f + col0 + 4 * i));
+                    bq[i] = __uint4_as_float4(lds_volatile_v4((const unsigned int*)lb_f + col0 + 4 * i));
+                }
+                if (valid && !(p.debug & 1)) {
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
-                        const int q = col0 + j;
-                        if (q < p.nq) {
-                            const float s = __uint_as_float(v[j]) * inv;
-                            const unsigned int o = score_to_order(s);
-                            if (o > ((volatile unsigned int*)lb)[q]) atomicMax(lb + q, o);
-                            if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
-                                const unsigned int pos = atomicAdd(p.cand_cnt + q, 1u);
-                                if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)q * kMmaCandCap + pos] = pack_cand(s, row);
+                        const float tj = j % 4 == 0 ? tq[j / 4].x : (j % 4 == 1 ? tq[j / 4].y : (j % 4 == 2 ? tq[j / 4].z : tq[j / 4].w));
+                        const float bj = j % 4 == 0 ? bq[j / 4].x : (j % 4 == 1 ? bq[j / 4].y : (j % 4 == 2 ? bq[j / 4].z : bq[j / 4].w));
+                        const float s = __uint_as_float(v[j]) * inv;
+                        if (s >= tj || s > bj) {                     // false for NaN
+                            const int q = col0 + j;
+                            if (q < p.nq) {
+                                const unsigned int o = score_to_order(s);
+                                if (o > ((volatile unsigned int*)lb)[q]) {
+                                    const unsigned int old = atomicMax(lb + q, o);
+                                    ((volatile float*)lb_f)[q] = order_to_score(old > o ? old : o);
+                                }
+                                if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
+                                    // A global atomic per hit would stall the warp ~1 us each time (its result
+                                    // is needed for the store): stage the hit, flush all of them after the tile.
+                                    const int hp = atomicAdd(hitn + wq, 1);
+                                    if (hp < kMmaHitQueue) {
+                                        hitq[wq * kMmaHitQueue + hp] = make_uint4((unsigned)q, row, __float_as_uint(s), 0u);
+                                    } else {   // queue full (thresholds still loose): the slow path, rare
+                                        const unsigned int pos = atomicAdd(p.cand_cnt + q, 1u);
+                                        if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)q * kMmaCandCap + pos] = pack_cand(s, row);
+                                    }
+                                }
                             }
                         }
                     }
@@ -288,15 +363,28 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(acc_empty + acc);
+            if (lane == 0) mbar_arrive(acc_empty + acc);        // the tensor core may refill this accumulator now
             if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+            // flush the staged hits: 32 global atomics in flight at a time instead of one
+            {
+                int nh = *((volatile int*)(hitn + wq));
+                nh = nh < kMmaHitQueue ? nh : kMmaHitQueue;
+                for (int i = lane; i < nh; i += 32) {
+                    const uint4 e = hitq[wq * kMmaHitQueue + i];
+                    const unsigned int pos = atomicAdd(p.cand_cnt + e.x, 1u);
+                    if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)e.x * kMmaCandCap + pos] = pack_cand(__uint_as_float(e.z), e.y);
+                }
+                __syncwarp();
+                if (lane == 0) hitn[wq] = 0;
+                __syncwarp();
+            }
         }
         // publish this CTA's bests (the bound-only pass exists to produce exactly this)
         named_bar_sync(2, 128);
         for (int q = tid - 128; q < p.nq; q += 128) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
         if (tid == 128) flags[0] = 1;
-    } else if (warp >= 8) {
-        // ============================ converters ============================
+    } else if (TERMS == 3 && warp >= 8) {
+        // ============================ converters (3xTF32 only) ============================
         const int ct = tid - 256;                               // 0..127
         int stage = 0; uint32_t phase = 0;
         for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -339,6 +427,7 @@ struct FinalizeParams {
     uint64_t* out_cand; int64_t* out_ids; float* out_sims; uint32_t* out_slots; int* out_n;
     uint8_t* out_rec; int rec_bytes; int rec_topk;
     int* status;                                         // [nq] 0 ok, else the host re-runs the query exactly
+    const float* eps;                                    // [nq] error bound of the approximate scores (TERMS = 1)
 };
 
 __device__ __forceinline__ void block_sort_desc(uint64_t* buf, int P, int tid, int nthreads) {
@@ -355,11 +444,12 @@ __device__ __forceinline__ void block_sort_desc(uint64_t* buf, int P, int tid, i
     }
 }
 
-template <bool F64>
+template <bool F64, int TERMS>
 __global__ void __launch_bounds__(512, 1)
 mma_finalize_kernel(const FinalizeParams p) {
-    extern __shared__ uint64_t fbuf[];                   // [P] candidate words, then reused for the exact words
-    __shared__ uint64_t exact[256];
+    extern __shared__ uint64_t fbuf[];                   // [P] candidate words (approximate score, slot)
+    __shared__ uint64_t exact[kMmaRescoreMax];           // exact words of the re-scored rows
+    __shared__ int s_C;
     const int q = blockIdx.x, tid = threadIdx.x;
     const unsigned int cnt = p.cand_cnt[q];
     const int n = cnt < (unsigned)kMmaCandCap ? (int)cnt : kMmaCandCap;
@@ -369,28 +459,49 @@ mma_finalize_kernel(const FinalizeParams p) {
     __syncthreads();
     block_sort_desc(fbuf, P, tid, blockDim.x);
     const int k = p.topk;
-    const int want = k + kMmaMargin;
-    const int C = n < want ? n : want;                   // <= 148 <= 256
+    const int lim = (uint32_t)k < p.n_rows ? k : (int)p.n_rows;
+    // how many of the best candidates to re-score
+    if (tid == 0) {
+        int C;
+        if (TERMS == 3) {
+            C = n < k + kMmaMargin ? n : k + kMmaMargin;
+        } else if (n <= lim) {
+            C = n;
+        } else {
+            // every row whose approximate score is within 2 eps of the k-th best approximate score:
+            // a row below that band is provably below the k-th exact score
+            const float band = cand_score(fbuf[lim - 1]) - 2.0f * p.eps[q];
+            const uint32_t cut = score_to_order(band);
+            int lo = lim, hi = n;                        // first index whose score word is below the band
+            while (lo < hi) { int mid = (lo + hi) >> 1; if ((uint32_t)(fbuf[mid] >> 32) >= cut) lo = mid + 1; else hi = mid; }
+            C = lo;
+        }
+        s_C = C;
+    }
+    __syncthreads();
+    const int C_all = s_C;
+    const int C = C_all < kMmaRescoreMax ? C_all : kMmaRescoreMax;
     // exact re-score, one thread per candidate row, the reference's arithmetic (scan.cuh Acc<>)
     const float* qv = p.q + (size_t)(p.q_first + q) * p.dim;
     const double mag1 = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
-    if (tid < 256) {
+    for (int t = tid; t < kMmaRescoreMax; t += blockDim.x) {
         uint64_t w = 0ull;
-        if (tid < C) {
-            const uint32_t slot = cand_slot(fbuf[tid]);
+        if (t < C) {
+            const uint32_t slot = cand_slot(fbuf[t]);
             const float* kr = p.keys + (size_t)slot * p.dim;
             Acc<F64> acc;
             acc.zero();
             for (int i = 0; i < p.dim; i++) acc.add(__ldg(qv + i), kr[i]);
             w = pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[slot] : 1.0), slot);
         }
-        exact[tid] = w;
+        exact[t] = w;
     }
     __syncthreads();
-    const uint64_t cut = C > 0 ? fbuf[C - 1] : 0ull;     // approximate word of the last candidate re-scored
+    const uint64_t cut_word = C > 0 ? fbuf[C - 1] : 0ull; // approximate word of the last candidate re-scored
+    int PE = 2;
+    while (PE < C) PE <<= 1;
     __syncthreads();
-    block_sort_desc(exact, 256, tid, blockDim.x);
-    const int lim = (uint32_t)k < p.n_rows ? k : (int)p.n_rows;
+    block_sort_desc(exact, PE, tid, blockDim.x);
     const int m = C < lim ? C : lim;
     const int o = p.out_first + q;
     for (int i = tid; i < k; i += blockDim.x) {
@@ -411,12 +522,13 @@ mma_finalize_kernel(const FinalizeParams p) {
         int st = 0;
         if (cnt > (unsigned)kMmaCandCap) st = 1;                     // candidate list overflowed
         else if (m < lim) st = 2;                                    // came out short
-        else if ((uint32_t)C < p.n_rows && m > 0) {
+        else if (TERMS == 1 && C_all > kMmaRescoreMax) st = 4;       // too many rows inside the error band
+        else if (TERMS == 3 && (uint32_t)C < p.n_rows && m > 0) {
             // Rows that were NOT re-scored all have an approximate score <= `cut` (the last re-scored
             // candidate; rows never listed are below the threshold, which is below it too).  They are
             // irrelevant iff cut + (3xTF32 error) is still below the k-th exact score.
             const float kth = cand_score(exact[m - 1]);
-            const float nxt = cand_score(cut);
+            const float nxt = cand_score(cut_word);
             if (!(nxt + 2e-5f * (fabsf(kth) + 1.0f) < kth)) st = 3;  // too close to call: exact re-run
         }
         p.status[q] = st;

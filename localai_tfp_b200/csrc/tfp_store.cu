@@ -116,6 +116,7 @@ struct Tuning {
     bool disable_lbest = false;
     int mma_min_queries = 32;      // batches at least this large go to the tensor-core path
     int64_t mma_min_rows = 65536;
+    int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
 };
 static const Tuning& tuning() {
     static Tuning t = [] {
@@ -124,6 +125,7 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_DISABLE_LBEST")) x.disable_lbest = atoi(e) != 0;
         if (const char* e = getenv("TFP_MMA_MIN_QUERIES")) x.mma_min_queries = atoi(e);
         if (const char* e = getenv("TFP_MMA_MIN_ROWS")) x.mma_min_rows = atoll(e);
+        if (const char* e = getenv("TFP_MMA_TERMS")) x.mma_terms = atoi(e) == 3 ? 3 : 1;
         return x;
     }();
     return t;
@@ -322,7 +324,7 @@ static int encode_tmap(tfp_store* s) {
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    cuuint32_t box2[2] = {(cuuint32_t)kMmaBoxCols, (cuuint32_t)kRowsPerTile};
+    cuuint32_t box2[2] = {(cuuint32_t)kMmaBoxCols, (cuuint32_t)kMmaRows};
     r = g_encode(&s->tmap_mma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_keys, gdim, gstride, box2, estr,
                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -401,9 +403,12 @@ static int optin_all(int bytes) {
     CU_OK((optin_gen<4, false, false>(bytes))); CU_OK((optin_gen<4, true, false>(bytes)));
     CU_OK((optin_gen<8, false, false>(bytes))); CU_OK((optin_gen<8, true, false>(bytes)));
     CU_OK((optin_gen<1, false, true>(bytes)));  CU_OK((optin_gen<1, true, true>(bytes)));
-    CU_OK(cudaFuncSetAttribute(mma_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    CU_OK(cudaFuncSetAttribute(mma_finalize_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8));
-    CU_OK(cudaFuncSetAttribute(mma_finalize_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8));
+    CU_OK(cudaFuncSetAttribute(mma_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    CU_OK(cudaFuncSetAttribute(mma_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
     return 0;
 }
 
@@ -986,13 +991,26 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     tfp_store* s = c->st;
     const int dim = s->dim;
     const int nqp = (g + 15) & ~15;
-    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 2 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
+    const int terms = tuning().mma_terms;
+    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 3 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
     if (c->mma_qsplit.reserve((size_t)2 * kMmaMaxNQ * dim * 4 + 256) || c->mma_cand.reserve((size_t)kMmaMaxNQ * kMmaCandCap * 8) ||
         c->mma_small.reserve(small_bytes) || c->h_status.reserve(kMmaMaxNQ * 4)) return -1;
     unsigned int* cand_cnt = c->mma_small.as<unsigned int>();
     int* status = (int*)(cand_cnt + kMmaMaxNQ);
-    unsigned int* lbest = (unsigned int*)(status + kMmaMaxNQ);
+    float* eps = (float*)(status + kMmaMaxNQ);
+    unsigned int* lbest = (unsigned int*)(eps + kMmaMaxNQ);
     float* qs = c->mma_qsplit.as<float>();
+    if (terms == 1) {
+        // |approx - exact| <= (2^-9 + D 2^-23) |q| |k|: TF32 drops < 2^-10 of each operand, the D term covers the
+        // reference's own fp32 rounding.  Normalised path: |q|, |k| <= 1.01.  Cosine path: the approximate score
+        // is dot / |k|, so the bound scales with |q| only.  5 % slack on top.
+        if (c->h_status.reserve(kMmaMaxNQ * 8)) return -1;
+        float* he = c->h_status.as<float>() + kMmaMaxNQ;
+        const float unit = (1.0f / 512.0f + (float)dim / 8388608.0f) * 1.05f;
+        for (int j = 0; j < g; j++)
+            he[j] = norm ? unit * 1.0201f : unit * (float)c->qinfo[(size_t)(q0 + j)].mag1;
+        CU_OK(cudaMemcpyAsync(eps, he, (size_t)g * 4, cudaMemcpyHostToDevice, c->stream));
+    }
 
     qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(
         sp.q + (size_t)q0 * dim, g, nqp, dim, qs);
@@ -1015,13 +1033,17 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = (dim + kMmaBoxCols - 1) / kMmaBoxCols;
     mp.nq = g; mp.nqp = nqp; mp.f64 = norm ? 0 : 1;
     mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
-    mp.refresh_ns = 20000;
-    const size_t smem = mma_smem_bytes(nqp);
+    mp.refresh_ns = 5000;
+    mp.eps = terms == 1 ? eps : nullptr;
+    mp.debug = getenv("TFP_MMA_DEBUG") ? atoi(getenv("TFP_MMA_DEBUG")) : 0;
+    const size_t smem = mma_smem_bytes(nqp, terms);
     mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
-    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
     CU_OK(cudaGetLastError());
     mp.mode = 1;
-    mma_scan_kernel<<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
     CU_OK(cudaGetLastError());
 
     FinalizeParams fp;
@@ -1032,8 +1054,15 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     fp.out_cand = sp.out_cand; fp.out_ids = sp.out_ids; fp.out_sims = sp.out_sims; fp.out_slots = sp.out_slots;
     fp.out_n = sp.out_n; fp.out_rec = sp.out_rec; fp.rec_bytes = sp.rec_bytes; fp.rec_topk = sp.rec_topk;
     fp.status = status;
-    if (norm) mma_finalize_kernel<false><<<g, 512, (size_t)kMmaCandCap * 8, c->stream>>>(fp);
-    else      mma_finalize_kernel<true><<<g, 512, (size_t)kMmaCandCap * 8, c->stream>>>(fp);
+    fp.eps = eps;
+    const size_t fsm = (size_t)kMmaCandCap * 8;
+    if (terms == 3) {
+        if (norm) mma_finalize_kernel<false, 3><<<g, 512, fsm, c->stream>>>(fp);
+        else      mma_finalize_kernel<true, 3><<<g, 512, fsm, c->stream>>>(fp);
+    } else {
+        if (norm) mma_finalize_kernel<false, 1><<<g, 512, fsm, c->stream>>>(fp);
+        else      mma_finalize_kernel<true, 1><<<g, 512, fsm, c->stream>>>(fp);
+    }
     CU_OK(cudaGetLastError());
     c->launches += 4;
     c->mma_passes++;
@@ -1042,7 +1071,7 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     CU_OK(cudaStreamSynchronize(c->stream));
     const int* hs = c->h_status.as<int>();
     for (int j = 0; j < g; j++) {
-        if (hs[j] != 0) {
+        if (hs[j] != 0 && !mp.debug) {   // (development timing runs skip the exact re-run)
             c->mma_fallbacks++;
             int rc = exact_one(q0 + j, o0 + j);
             if (rc) return rc;
@@ -1177,7 +1206,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     // relies on counts one row per CTA, so k + margin must not exceed the grid.
     const bool mma_ok = fused && s->tmap_ok && ksel <= kMmaMaxTopK && grid >= ksel + kMmaMargin &&
                         n >= tuning().mma_min_rows && tuning().mma_min_queries > 0 &&
-                        mma_smem_bytes(kMmaMaxNQ) <= (size_t)s->max_smem;
+                        mma_smem_bytes(kMmaMaxNQ, 3) <= (size_t)s->max_smem;
     int i = 0;
     while (i < count) {
         const bool norm = path_of(first + i);

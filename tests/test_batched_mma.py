@@ -47,16 +47,31 @@ def test_mma_path_ragged_dim_and_partial_tile(tfp, oracle):
     run_batch(tfp, oracle, K, Q, 10, True)
 
 
-def test_mma_path_near_ties_fall_back_to_exact(tfp, oracle):
-    """Rows that differ by less than the 3xTF32 error around the k-th place: the filter cannot order
-    them, the status check must notice and the exact kernel must decide."""
+def test_mma_path_near_ties_are_decided_exactly(tfp, oracle):
+    """400 rows that differ by less than the filter's error around the k-th place: the filter cannot
+    order them.  The single-TF32 filter re-scores the whole error band; the 3xTF32 filter must notice
+    that the cut is too close to call and hand the query to the exact kernel."""
     rng = np.random.default_rng(9)
     base = normalize_rows(rng.standard_normal((1, 64)).astype(f32))[0]
     K = make_keys(70000, 64, seed=11, normalized=True)
     K[:400] = normalize_rows(base[None, :] + rng.standard_normal((400, 64)).astype(f32) * f32(2e-7))
     Q = np.repeat(base[None, :], 32, axis=0) + rng.standard_normal((32, 64)).astype(f32) * f32(1e-3)
     Q = normalize_rows(Q)
+    import os
     passes, reruns = run_batch(tfp, oracle, K, Q, 50, True)
+    if os.environ.get("TFP_MMA_TERMS") == "3":
+        assert reruns >= 1
+
+
+def test_mma_path_band_wider_than_the_rescore_budget_reruns_exactly(tfp, oracle):
+    """More near-duplicates of the query than the filter may re-score (1024): the query is flagged and
+    the exact kernel answers it."""
+    rng = np.random.default_rng(10)
+    base = normalize_rows(rng.standard_normal((1, 64)).astype(f32))[0]
+    K = make_keys(70000, 64, seed=12, normalized=True)
+    K[:3000] = normalize_rows(base[None, :] + rng.standard_normal((3000, 64)).astype(f32) * f32(1e-5))
+    Q = normalize_rows(np.repeat(base[None, :], 32, axis=0) + rng.standard_normal((32, 64)).astype(f32) * f32(1e-4))
+    passes, reruns = run_batch(tfp, oracle, K, Q, 20, True)
     assert reruns >= 1
 
 
