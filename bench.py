@@ -33,6 +33,7 @@ DIM = 768
 TOPK = 10
 N_QUERIES = 64
 QUERIES_PER_STEP = 1
+MMA_TERMS = 3 if os.environ.get("TFP_MMA_TERMS") == "3" else 1   # tensor-core filter: TF32 MMAs per K-step
 BLOCK_ROWS = 62_500            # generation granularity: 16 blocks, so 1/2/4/8 shards align with blocks
 SEED = 0x5EED0002
 WORKLOAD = "C2 (BASELINE.json configs[1]): 1M keys x 768-d fp32, single-query top-10, normalised-key fast path"
@@ -51,7 +52,7 @@ def select_workload(name: str):
         N_KEYS, DIM, SEED, TOPK, QUERIES_PER_STEP = 10_000_000, 1024, 0x5EED0003, 100, 256
         METRIC = "StoresFind queries/sec (top-100, batch 256)"
         WORKLOAD = ("C3 (BASELINE.json configs[2]): 10M keys x 1024-d fp32, batch-256 queries top-100 on the "
-                    "tensor-core path (tcgen05 3xTF32 filter + exact re-score)")
+                    "tensor-core path (tcgen05 %dxTF32 filter + exact re-score)" % MMA_TERMS)
 
 
 # ----------------------------------------------------------------------------- inputs
@@ -302,7 +303,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         pass
     roof_bound, roof_unit, roof_kernel = "hbm", "GB/s", "scan_tma_kernel<1,fp32,fused>"
     if batched:
-        # tensor-bound: credited flops = 2 * Q * rows * D per batch (the 3xTF32 scheme issues 3x that)
+        # credited flops = 2 * Q * rows * D per batch (the filter issues MMA_TERMS times that)
         roof_bound, roof_unit, roof_kernel = "tensor", "TFLOP/s", "mma_scan_kernel (tcgen05.mma kind::tf32)"
         achieved = 2.0 * QUERIES_PER_STEP * rows_local * DIM / (scan_ms * 1e-3) / 1e12
         peak, peak_src = 1590.0 / 2, "fallback (B200_PROFILING.md bf16 1.59 PFLOP/s, halved for TF32)"
@@ -395,8 +396,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                                  "`value` overlaps the tail of one scan with the start of the next (finds_in_flight)",
                          "effective_gbs_in_timed_region": algo_bytes / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
                          "frac_of_nominal_8TBs": achieved / 8000.0 if not batched else None,
-                         "issued_tf32_tflops": 3 * achieved if batched else None,
-                         "frac_of_nominal_tf32_1100": 3 * achieved / 1100.0 if batched else None},
+                         "tf32_terms": MMA_TERMS if batched else None,
+                         "issued_tf32_tflops": MMA_TERMS * achieved if batched else None,
+                         "frac_of_nominal_tf32_1100": MMA_TERMS * achieved / 1100.0 if batched else None},
         }
         if cpu:
             line["cpu_baseline"] = cpu
