@@ -47,6 +47,7 @@ struct ScanParams {
     int topk;                 // <= TFP_FUSED_TOPK_MAX on the fused path
     int cap;                  // selection buffer entries per query (power of two)
     int evict_first;          // stream keys through L2 with evict-first
+    unsigned long long* dbg_times;   // development only: [grid x 4] globaltimer stamps (start, scan end, epilogue end, tiles), or nullptr
     const float* q;           // [nq_total x dim] staged queries
     const QInfo* qinfo;       // [nq_total]
     int q_first;              // first staged query of this launch group
@@ -59,7 +60,8 @@ struct ScanParams {
     unsigned int* tile_counter; // [1] dynamic tile scheduler: next tile = gridDim.x + counter++
     unsigned long long* lbest; // [kMaxNQ x lbest_stride] per-CTA "m-th best so far" (0 = not published)
     int lbest_stride;
-    int m_local;              // ceil(topk / grid)
+    int m_local;              // m = ceil(topk / grid): which of its bests every CTA publishes
+    int r_local;              // r = ceil(topk / m): the r-th largest published value is the bound
     int refresh_ns;           // refresher warp's poll period; 0 = no refresher
     uint64_t* all_cand;       // big-k path: [kMaxNQ? no: 1 x n_rows] every row's candidate word
     // outputs, indexed by out_first + query
@@ -114,6 +116,7 @@ struct ScanSmem {
     unsigned long long* ext;     // NQ: grid-wide bound kept fresh by the refresher warp
     unsigned long long* lmax;    // NQ: best word this CTA has seen (published as lbest when m == 1)
     int* done;                   // 1: consumers are finished, refresher may exit
+    unsigned long long* lstage;  // kMaxGrid: the refresher warp's copy of the per-CTA bests
 };
 // Packed per-query record: int32 n; int32 reserved; int64 ids[topk]; float sims[topk]; padded to 16.
 __host__ __device__ inline size_t record_bytes(int topk) {
@@ -131,8 +134,13 @@ __host__ __device__ inline size_t scan_smem_bytes(int n_stages, int nq, int dpad
     b += (size_t)nq * cap * 8;
     b += (size_t)(2 * n_stages + 1) * 8;
     b += (size_t)nq * 8 + (size_t)nq * 4 + 16 + (size_t)(kMaxGrid + 1) * 4 + (size_t)kMaxStages * 4;
-    b += (size_t)nq * 16 + 16;
+    b += (size_t)nq * 16 + 16 + (size_t)kMaxGrid * 8 + 8;
     return b + 1024;  // slack for the 1024-byte alignment of the stage ring
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
 }
 __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int nq, int dpad, int cap) {
     ScanSmem s;
@@ -152,24 +160,38 @@ __device__ __forceinline__ ScanSmem scan_carve(uint8_t* raw, int n_stages, int n
     s.flag = (int*)p; p += 4;
     s.pref = (int*)p; p += (size_t)(kMaxGrid + 1) * 4;
     s.tile_id = (uint32_t*)p; p += (size_t)kMaxStages * 4;
-    s.done = (int*)p;
+    s.done = (int*)p; p += 4;
+    p += (8u - (smem_u32(p) & 7u)) & 7u;
+    s.lstage = (unsigned long long*)p;
     return s;
 }
 
-// min over the CTAs of the published "m-th best so far" words for query q, by one warp.
-// 0 while any CTA has not published yet (then it is no bound at all).
-__device__ __forceinline__ unsigned long long lbest_min(const ScanParams& p, int q, int lane) {
-    unsigned long long v = ~0ull;
+// The grid-wide bound from the per-CTA "m-th best so far" words of query q, by one warp: the r-th
+// largest of them (r = ceil(k / m)).  r CTAs each hold m rows at least that good, so r*m >= k rows
+// of the store reach it: it is a lower bound of the global k-th best.  For k <= #CTAs this is simply
+// the k-th largest of the CTAs' best rows -- within a few ranks of the true k-th best, so almost
+// nothing but the answer survives to the final merge.  `stage`: shared scratch for gridDim.x words.
+// Returns 0 while fewer than r CTAs have published (then there is no bound yet).
+__device__ __forceinline__ unsigned long long lbest_rth(const ScanParams& p, int q, int lane,
+                                                        unsigned long long* stage) {
+    const int G = (int)gridDim.x;
     const volatile unsigned long long* a = p.lbest + (size_t)q * p.lbest_stride;
-    for (int b = lane; b < (int)gridDim.x; b += 32) {
-        unsigned long long u = a[b];
-        v = u < v ? u : v;
+    for (int b = lane; b < G; b += 32) stage[b] = a[b];
+    __syncwarp();
+    unsigned long long found = 0ull;
+    for (int b = lane; b < G; b += 32) {
+        const unsigned long long v = stage[b];
+        if (v == 0ull) continue;
+        int above = 0;
+        for (int j = 0; j < G; j++) above += (stage[j] > v) ? 1 : 0;
+        if (above == p.r_local - 1) found = v;      // words are unique: at most one lane hits
     }
     for (int d = 16; d > 0; d >>= 1) {
-        unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, v, d);
-        v = o < v ? o : v;
+        unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, found, d);
+        found = o > found ? o : found;
     }
-    return v;
+    __syncwarp();
+    return found;
 }
 
 // ---- epilogue shared by the TMA and the generic kernel -----------------------
@@ -179,21 +201,61 @@ template <int NQ>
 __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel, int* flag, int* pref, int tid,
                                               uint64_t* big_buf, int big_cap) {
     const int k = p.topk;
-    // 1. final local prune, then publish this CTA's survivors
+    // 1. publish this CTA's survivors: the buffered words that reach the bound.  With the grid-wide
+    // bound in place that is a handful of words, so the usual case needs no sort at all: count them,
+    // and if they fit (<= k) copy them out unsorted (the last CTA orders everything anyway).
     for (int q = 0; q < NQ; q++) {
-        sel_prune(sel[q], tid, true);
-        int m = *sel[q].cnt;
-        unsigned long long bound = *sel[q].tau;   // includes the grid-wide bounds seen so far
         uint64_t* dst = p.part + ((size_t)blockIdx.x * kMaxNQ + q) * k;
-        // survivors are sorted descending, so those >= bound form a prefix
-        for (int i = tid; i < m; i += kSelThreads) {
-            uint64_t c = sel[q].buf[i];
-            if (c >= bound) dst[i] = c;
+        bool fast = sel[q].m_local == 1;      // larger m publishes its m-th best from the sorted buffer
+        if (fast) {
+            const int n = *sel[q].cnt;
+            const unsigned long long bound = *sel[q].tau;
+            if (tid == 0) *flag = 0;
+            named_bar_sync(kSelBarrier, kSelThreads);
+            int mine = 0;
+            for (int i = tid; i < n; i += kSelThreads) mine += (sel[q].buf[i] >= bound) ? 1 : 0;
+            if (mine) atomicAdd(flag, mine);
+            named_bar_sync(kSelBarrier, kSelThreads);
+            const int total = *((volatile int*)flag);
+            named_bar_sync(kSelBarrier, kSelThreads);
+            if (total <= k) {
+                if (tid == 0) *flag = 0;
+                named_bar_sync(kSelBarrier, kSelThreads);
+                for (int i = tid; i < n; i += kSelThreads) {
+                    const uint64_t c = sel[q].buf[i];
+                    if (c >= bound) dst[atomicAdd(flag, 1)] = c;
+                }
+                named_bar_sync(kSelBarrier, kSelThreads);
+                if (tid == 0) p.part_cnt[blockIdx.x * kMaxNQ + q] = total;
+                // the last CTA continues from its own buffer: compact it the same way
+                if (tid == 0) *flag = 0;
+                named_bar_sync(kSelBarrier, kSelThreads);
+                uint64_t keep[16];   // cap / kSelThreads <= 16 entries per thread
+                int nk = 0;
+                for (int i = tid; i < n; i += kSelThreads) { const uint64_t c = sel[q].buf[i]; if (c >= bound && nk < 16) keep[nk++] = c; }
+                named_bar_sync(kSelBarrier, kSelThreads);
+                for (int j = 0; j < nk; j++) sel[q].buf[atomicAdd(flag, 1)] = keep[j];
+                named_bar_sync(kSelBarrier, kSelThreads);
+                if (tid == 0) *sel[q].cnt = total;
+                named_bar_sync(kSelBarrier, kSelThreads);
+            } else {
+                fast = false;
+            }
         }
-        if (tid == 0) {
-            int lo = 0, hi = m;   // first index with buf[i] < bound
-            while (lo < hi) { int mid = (lo + hi) >> 1; if (sel[q].buf[mid] >= bound) lo = mid + 1; else hi = mid; }
-            p.part_cnt[blockIdx.x * kMaxNQ + q] = lo;
+        if (!fast) {
+            sel_prune(sel[q], tid, true);
+            int m = *sel[q].cnt;
+            unsigned long long bound = *sel[q].tau;   // includes the grid-wide bounds seen so far
+            // survivors are sorted descending, so those >= bound form a prefix
+            for (int i = tid; i < m; i += kSelThreads) {
+                uint64_t c = sel[q].buf[i];
+                if (c >= bound) dst[i] = c;
+            }
+            if (tid == 0) {
+                int lo = 0, hi = m;   // first index with buf[i] < bound
+                while (lo < hi) { int mid = (lo + hi) >> 1; if (sel[q].buf[mid] >= bound) lo = mid + 1; else hi = mid; }
+                p.part_cnt[blockIdx.x * kMaxNQ + q] = lo;
+            }
         }
     }
     __threadfence();
@@ -211,9 +273,9 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
     // (it travelled through gtau / lbest), and that row is part of the answer: admit words
     // >= tau, i.e. > tau - 1.  No word is offered twice (own rows are not re-offered), so
     // equality can only be that one row.
-    if (p.lbest && tid < 32) {
+    if (p.lbest && tid < 32 && big_buf && big_cap >= (int)gridDim.x) {
         for (int q = 0; q < NQ; q++) {
-            unsigned long long v = lbest_min(p, q, tid);
+            unsigned long long v = lbest_rth(p, q, tid, (unsigned long long*)big_buf);
             if (tid == 0 && v > *sel[q].tau) *sel[q].tau = v;
         }
     }
@@ -425,7 +487,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
                 int d = (lane == 0) ? *((volatile int*)sm.done) : 0;
                 if (__shfl_sync(0xFFFFFFFFu, d, 0)) break;
                 for (int q = 0; q < NQ; q++) {
-                    unsigned long long v = p.lbest ? lbest_min(p, q, lane) : 0ull;
+                    unsigned long long v = p.lbest ? lbest_rth(p, q, lane, sm.lstage) : 0ull;
                     if (lane == 0) {
                         unsigned long long g = *((volatile unsigned long long*)(p.gtau + q));
                         *((volatile unsigned long long*)(sm.ext + q)) = g > v ? g : v;
@@ -446,6 +508,8 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
 #pragma unroll
     for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
 
+    if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 0] = globaltimer_ns();
+    unsigned long long dbg_tiles = 0;
     mbar_wait(sm.qbar, 0);
     const uint32_t swz = (uint32_t)(tid & 7);
     const uint32_t row_off = (uint32_t)tid * 128u;
@@ -504,13 +568,16 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
         unsigned long long ext_bound = 0ull;
         if (!SPILL && tid < NQ) ext_bound = *((volatile unsigned long long*)(sm.ext + tid));
         tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, ext_bound, last_pub);
+        dbg_tiles++;
     }
+    if (p.dbg_times && tid == 0) { p.dbg_times[blockIdx.x * 4 + 1] = globaltimer_ns(); p.dbg_times[blockIdx.x * 4 + 3] = dbg_tiles; }
     if (tid == 0) *((volatile int*)sm.done) = 1;   // the refresher warp may leave
     if constexpr (!SPILL) {
         // the stage ring is idle now (every TMA box has landed and been consumed): lend it to the merge
         int big_cap = 1;
         while ((size_t)big_cap * 2 * 8 <= (size_t)p.n_stages * kStageBytes) big_cap <<= 1;
         scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid, (uint64_t*)sm.stages, big_cap);
+        if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 2] = globaltimer_ns();
     }
 }
 

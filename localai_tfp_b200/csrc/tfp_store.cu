@@ -286,6 +286,7 @@ struct tfp_find_ctx {
     PinBuf h_in, h_out;
     DevBuf part, part_cnt, sync_words;   // sync_words: gtau[kMaxNQ] + ticket + tile counter + lbest[kMaxNQ x kMaxGrid]
     DevBuf all_cand, sorted_cand, cub_tmp;
+    DevBuf dbg_times; int dbg_grid = 0;
     DevBuf mma_qsplit, mma_cand, mma_small;   // tensor-core path: split queries, candidate lists, counters/bounds/status
     PinBuf h_status;
     // sharded finds: communicator, gathered records, merged answer
@@ -887,7 +888,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     c->nccl_comm = nullptr;
     if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
-                      &c->cub_tmp, &c->out_block, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
+                      &c->cub_tmp, &c->out_block, &c->dbg_times, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
     for (DevBuf* b : bufs) b->release();
     c->h_in.release();
     c->h_out.release();
@@ -1137,8 +1138,15 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     p.lbest = c->sync_words.as<unsigned long long>() + kMaxNQ + 2;
     p.lbest_stride = kMaxGrid;
     p.m_local = (ksel + grid - 1) / grid;
+    p.r_local = (ksel + p.m_local - 1) / p.m_local;
     p.refresh_ns = tuning().refresh_ns;
     if (tuning().disable_lbest) p.lbest = nullptr;
+    if (getenv("TFP_SCAN_TIMES")) {   // development: per-CTA time stamps of the next scan, printed by tfp_find_ctx_sync
+        if (c->dbg_times.reserve((size_t)kMaxGrid * 4 * 8)) return -1;
+        CU_OK(cudaMemsetAsync(c->dbg_times.p, 0, (size_t)kMaxGrid * 4 * 8, c->stream));
+        p.dbg_times = c->dbg_times.as<unsigned long long>();
+        c->dbg_grid = grid;
+    }
     p.out_cand = c->out_cand; p.out_ids = c->out_ids;
     p.out_sims = c->out_sims; p.out_slots = c->out_slots; p.out_n = c->out_n;
     p.out_rec = c->out_rec; p.rec_bytes = (int)rec_bytes; p.rec_topk = topk;
@@ -1299,6 +1307,25 @@ extern "C" int tfp_find_ctx_sync(tfp_find_ctx* c) {
     if (!c) return fail(2, "tfp_find_ctx_sync: ctx is NULL");
     if (set_device(c->st)) return -1;
     CU_OK(cudaStreamSynchronize(c->stream));
+    if (c->dbg_grid > 0 && c->dbg_times.p) {   // development: timeline of the last scan
+        std::vector<unsigned long long> t((size_t)c->dbg_grid * 4);
+        CU_OK(cudaMemcpy(t.data(), c->dbg_times.p, t.size() * 8, cudaMemcpyDeviceToHost));
+        unsigned long long t0 = ~0ull, s_min = ~0ull, s_max = 0, e_max = 0, start_max = 0;
+        double s_sum = 0;
+        unsigned long long tl_min = ~0ull, tl_max = 0;
+        for (int b = 0; b < c->dbg_grid; b++) {
+            t0 = std::min(t0, t[b * 4]); start_max = std::max(start_max, t[b * 4]);
+        }
+        for (int b = 0; b < c->dbg_grid; b++) {
+            s_min = std::min(s_min, t[b * 4 + 1]); s_max = std::max(s_max, t[b * 4 + 1]); s_sum += (double)(t[b * 4 + 1] - t0);
+            e_max = std::max(e_max, t[b * 4 + 2]); tl_min = std::min(tl_min, t[b * 4 + 3]); tl_max = std::max(tl_max, t[b * 4 + 3]);
+        }
+        fprintf(stderr, "tfp scan timeline (us from first CTA start): last CTA start %.1f | scan end min %.1f avg %.1f max %.1f | "
+                        "kernel end %.1f | tiles per CTA %llu..%llu\n",
+                (start_max - t0) / 1e3, (s_min - t0) / 1e3, s_sum / c->dbg_grid / 1e3, (s_max - t0) / 1e3, (e_max - t0) / 1e3,
+                tl_min, tl_max);
+        c->dbg_grid = 0;
+    }
     return 0;
 }
 extern "C" void* tfp_find_ctx_stream(tfp_find_ctx* c) { return c ? (void*)c->stream : nullptr; }
@@ -1478,6 +1505,7 @@ extern "C" int tfp_scan_topk_noalloc(const float* d_keys, int64_t n_rows, int di
     p.lbest = (unsigned long long*)(base + NoAllocLayout::sync_words + (kMaxNQ + 2) * 8);
     p.lbest_stride = kNoAllocMaxGrid;
     p.m_local = (ksel + grid - 1) / grid;
+    p.r_local = (ksel + p.m_local - 1) / p.m_local;
     p.refresh_ns = tuning().refresh_ns;
     if (tuning().disable_lbest) p.lbest = nullptr;
     p.out_cand = (uint64_t*)(base + NoAllocLayout::out_cand);
