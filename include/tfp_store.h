@@ -142,6 +142,9 @@ int tfp_store_mark_not_normalized(tfp_store* s);
  * scan can be timed with inputs already in HBM.  No reference counterpart:
  * the reference is synchronous and single-threaded (store.go:18).        */
 int  tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out);
+/* The context behind tfp_store_find / tfp_store_find_batch (owned by the store; do not destroy):
+ * lets a host read its counters. */
+tfp_find_ctx* tfp_store_default_ctx(tfp_store* s);
 void tfp_find_ctx_destroy(tfp_find_ctx* c);
 /* Stage nq host queries into HBM (async on the context's stream); computes each
  * query's path and |q| on the host exactly as store.go:313-324,435-439. */

@@ -39,6 +39,7 @@ PROTOTYPES = {
     "tfp_store_save": (C.c_int, [vp, C.c_char_p]),
     "tfp_store_load": (C.c_int, [vp, C.c_char_p]),
     "tfp_store_mark_not_normalized": (C.c_int, [vp]),
+    "tfp_store_default_ctx": (vp, [vp]),
     "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_destroy": (None, [vp]),
     "tfp_find_ctx_upload": (C.c_int, [vp, fp, C.c_int, C.c_int]),

@@ -271,6 +271,7 @@ struct tfp_store {
     DevBuf st_rows, st_hash, st_knorm, st_isnorm, st_pair_row, st_pair_slot, st_pair_eq, st_src, st_dst, st_ids;
     std::vector<tfp_find_ctx*> ctxs;
     tfp_find_ctx* default_ctx = nullptr;
+    std::mutex find_mu;                // the built-in context serves one synchronous find at a time
     int sm_count = 148;
     int max_smem = 0;
 };
@@ -897,6 +898,8 @@ static void ctx_destroy(tfp_find_ctx* c) {
     delete c;
 }
 
+extern "C" tfp_find_ctx* tfp_store_default_ctx(tfp_store* s) { return s ? s->default_ctx : nullptr; }
+
 extern "C" int tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out) {
     if (!s || !out) return fail(2, "tfp_find_ctx_create: NULL argument");
     std::unique_lock<std::shared_mutex> lk(s->rw);
@@ -1357,8 +1360,7 @@ extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int di
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
     if (!q || nq <= 0) return fail(2, "tfp_store_find: q is NULL or nq <= 0");
     if (set_device(s)) return -1;
-    static std::mutex default_ctx_mu;   // the built-in context serves one synchronous find at a time
-    std::lock_guard<std::mutex> g(default_ctx_mu);
+    std::lock_guard<std::mutex> g(s->find_mu);
     tfp_find_ctx* c = s->default_ctx;
     int rc = ctx_upload_locked(c, q, nq, dim);
     if (rc) return rc;

@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import argparse
 import os
+import queue
 import signal
 import threading
 from concurrent import futures
@@ -31,10 +32,75 @@ def _ident(b):
     return b
 
 
+class _FindBatcher:
+    """Concurrent StoresFind requests become ONE batched find ("micro-batcher for concurrent
+    StoresFind").  Whatever has queued up while the previous batch ran is taken together, grouped by
+    top-k; 32 or more same-path queries on a large store ride the tensor-core path.  A lone request is
+    served at once: nothing waits for company."""
+
+    def __init__(self, backend: "Backend", max_batch: int = 256):
+        self.backend = backend
+        self.max_batch = max_batch
+        self.q = queue.Queue()
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+        self.batches = 0
+        self.largest = 0
+
+    def submit(self, key, topk):
+        fut = futures.Future()
+        self.q.put((key, topk, fut))
+        return fut
+
+    def _run(self):
+        while True:
+            items = [self.q.get()]
+            while len(items) < self.max_batch:
+                try:
+                    items.append(self.q.get_nowait())
+                except queue.Empty:
+                    break
+            by_k = {}
+            for it in items:
+                by_k.setdefault(it[1], []).append(it)
+            for topk, group in by_k.items():
+                self._serve(topk, group)
+
+    def _serve(self, topk, group):
+        b = self.backend
+        with b.lock:
+            b.busy = True
+            try:
+                dims = {len(g[0]) for g in group}
+                if len(group) == 1 or len(dims) != 1 or topk < 1 or b.store.key_len != next(iter(dims)) or len(b.store) == 0:
+                    for key, k, fut in group:        # singles and anything that will error: the plain call, per request
+                        try:
+                            fut.set_result(b.store.StoresFind(key, k))
+                        except Exception as e:
+                            fut.set_exception(e)
+                    return
+                import numpy as np
+                qs = np.stack([g[0] for g in group]).astype(np.float32)
+                res, keys = b.store.find_batch(qs, topk, with_keys=True)
+                self.batches += 1
+                self.largest = max(self.largest, len(group))
+                for i, (key, k, fut) in enumerate(group):
+                    ids, sims = res[i]
+                    fut.set_result(([keys[i, j, :].copy() for j in range(len(ids))],
+                                    [b.store.values.get(int(x)) for x in ids], sims))
+            except Exception as e:
+                for _, _, fut in group:
+                    if not fut.done():
+                        fut.set_exception(e)
+            finally:
+                b.busy = False
+
+
 class Backend:
     def __init__(self, device: int = 0, snapshot: str | None = None):
         self.store = Store(device=device)
         self.snapshot = snapshot
+        self.batcher = None
         if snapshot and os.path.exists(snapshot) and os.path.exists(snapshot + ".values"):
             self.store.load(snapshot)             # SURVEY §8f.4: survive a watchdog kill / respawn
         self.lock = threading.Lock()          # base.SingleThread (pkg/grpc/base/singlethread.go:13-29)
@@ -81,12 +147,20 @@ class Backend:
 
     def StoresFind(self, request: bytes, context) -> bytes:
         key, topk = wire.dec_find(request)
-        ks, vs, sims = self._run(context, lambda: self.store.StoresFind(key, topk))
+        if self.batcher is None:
+            ks, vs, sims = self._run(context, lambda: self.store.StoresFind(key, topk))
+        else:
+            try:
+                ks, vs, sims = self.batcher.submit(key, topk).result()
+            except StoreError as e:
+                context.abort(grpc.StatusCode.UNKNOWN, str(e))
         return wire.enc_find_result(ks, vs, sims)
 
 
-def make_server(addr: str, device: int = 0, workers: int = 8, snapshot: str | None = None):
+def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | None = None, batch_finds: bool = True):
     backend = Backend(device, snapshot)
+    if batch_finds:
+        backend.batcher = _FindBatcher(backend)
     methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,
                                                          response_serializer=_ident)
                for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}

@@ -225,6 +225,13 @@ class Store:
     def find_context(self) -> "FindContext":
         return FindContext(self)
 
+    def mma_counters(self):
+        """(tensor-core passes, queries re-run exactly) of the built-in context that serves find_batch."""
+        a, b = C.c_int64(), C.c_int64()
+        ctx = C.c_void_p(self._L.tfp_store_default_ctx(self._h))
+        self._check(self._L.tfp_find_ctx_mma_counters(ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
 
 class FindContext:
     """Asynchronous, device-resident finds (include/tfp_store.h `tfp_find_ctx_*`)."""

@@ -134,3 +134,40 @@ def test_snapshot_survives_a_respawn(tfp, tmp_path):
     after = c.find([0.1, 0.3, 0.5], 2)
     assert after[1] == before[1] == [b"test1", b"test2"] and np.array_equal(after[2], before[2])
     c.close(); proc.terminate(); proc.wait(timeout=30)
+
+
+def test_concurrent_finds_are_batched_onto_the_tensor_cores(tfp, oracle):
+    """64 clients call StoresFind at once against a 70k-row store: the server's micro-batcher must answer
+    each exactly as a lone call would, and batches of >= 32 must have gone through the tensor-core path."""
+    import threading
+    from conftest import make_keys
+    from localai_tfp_b200.server import Client, make_server
+    server, backend, port = make_server("127.0.0.1:0")
+    server.start()
+    try:
+        K = make_keys(70000, 64, seed=41, normalized=True)
+        c0 = Client(f"127.0.0.1:{port}")
+        for lo in range(0, len(K), 10000):
+            c0.set(K[lo:lo + 10000], [b"%d" % i for i in range(lo, min(lo + 10000, len(K)))])
+        Q = make_keys(64, 64, seed=42, normalized=True)
+        want = [oracle.scan_block(K, q, 10, True) for q in Q]
+        got = [None] * len(Q)
+        clients = [Client(f"127.0.0.1:{port}") for _ in Q]
+        for rounds in range(3):                                  # a few rounds so that real batches form
+            gate = threading.Barrier(len(Q))
+
+            def work(i):
+                gate.wait()
+                got[i] = clients[i].find(Q[i], 10)
+            ts = [threading.Thread(target=work, args=(i,)) for i in range(len(Q))]
+            [t.start() for t in ts]; [t.join() for t in ts]
+            for i in range(len(Q)):
+                ks, vs, sims = got[i]
+                assert np.array_equal(sims, want[i][1])
+                assert [int(v) for v in vs] == [int(r) for r in want[i][0]]
+                assert all(np.array_equal(k, K[int(v)]) for k, v in zip(ks, vs))
+        assert backend.batcher.largest >= 32, backend.batcher.largest
+        assert backend.store.mma_counters()[0] >= 1
+        [c.close() for c in clients]; c0.close()
+    finally:
+        server.stop(grace=0)
