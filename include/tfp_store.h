@@ -102,10 +102,13 @@ int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim,
 int tfp_store_find(tfp_store* s, const float* q, int dim, int topk,
                    int* out_n, int64_t* out_ids, float* out_sims, float* out_keys, int* out_path);
 
-/* nq independent finds that share one pass over the keys per group of up to 8
- * queries.  Same per-query results as nq calls of tfp_store_find.  Replaces nq
- * sequential Store.StoresFind calls (the reference has no batch RPC; SURVEY
- * §8f.2).  out_n[nq]; out_ids/out_sims [nq x topk]; out_keys [nq x topk x dim] or NULL. */
+/* nq independent finds that share passes over the keys.  Same per-query results
+ * as nq calls of tfp_store_find (bit-identical similarities).  Up to 4 same-path
+ * queries share one pass of the exact scan kernel; 5 or more on a store of
+ * >= 65536 rows (topk <= 100) go through the tensor cores in groups of up to 256
+ * (TF32 filter + exact re-score, mma_scan.cuh).  Replaces nq sequential
+ * Store.StoresFind calls (the reference has no batch RPC).
+ * out_n[nq]; out_ids/out_sims [nq x topk]; out_keys [nq x topk x dim] or NULL. */
 int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk,
                          int* out_n, int64_t* out_ids, float* out_sims, float* out_keys);
 
@@ -166,8 +169,8 @@ int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d
  * address: [count x stride x dim] floats, stride as returned by
  * tfp_find_ctx_device_results (what StoresFindResult.Keys is built from). */
 int  tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys);
-/* How often this context took the tensor-core path (batches of >= 32 same-path queries on a
- * large store: tcgen05 3xTF32 filter + exact re-score) and how many queries it then had to
+/* How often this context took the tensor-core path (batches of >= 5 same-path queries on a
+ * store of >= 65536 rows: tcgen05 3xTF32 filter + exact re-score) and how many queries it then had to
  * re-run on the exact scan kernel.  Either pointer may be NULL. */
 int  tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64_t* exact_reruns);
 /* Number of kernels the context has launched so far (for bench accounting). */
@@ -214,7 +217,7 @@ int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int
 int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner);
 int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk);
 /* Same for staged queries [first, first+count): one all-gather of count records, one merge CTA per
- * query.  Batches of >= 32 same-path queries take the tensor-core path on every shard. */
+ * query.  Batches of >= 5 same-path queries take the tensor-core path on every shard. */
 int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk);
 int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard,
                                 int** d_index, int** d_n);

@@ -1,6 +1,6 @@
 // mma_scan.cuh -- batched StoresFind on the 5th-generation tensor cores (tcgen05 + TMEM).
 //
-// For >= 32 concurrent queries the scan is a dense contraction S = K . Q^T
+// For batches of queries (5 or more: the measured break-even) the scan is a dense contraction S = K . Q^T
 // (K: [rows x D] keys, Q: [nq x D] queries).  It replaces nq sequential runs of the
 // reference loop (backend/go/stores/store.go:378-389 / :441-452) -- the reference has no
 // batched path at all.
@@ -48,7 +48,7 @@ namespace tfp {
 constexpr int kMmaThreads = 384;
 constexpr int kMmaStages3 = 4;          // TERMS = 3: stages of 48 KiB at nq = 256
 constexpr int kMmaStages1 = 8;          // TERMS = 1: stages of 24 KiB
-constexpr int kMmaStagesMax = 8;
+constexpr int kMmaStagesMax = 24;        // small batches have small query boxes: more key tiles in flight
 constexpr int kMmaHitQueue = 256;       // per epilogue warp: hits staged in shared memory, flushed once per tile
 constexpr int kMmaRescoreMax = 1024;    // TERMS = 1: rows re-scored per query at most (else exact re-run)
 constexpr int kMmaBoxCols = 16;         // floats per row per stage (64 B, 64-byte swizzle): small stages, deep ring
@@ -72,6 +72,8 @@ struct MmaParams {
     unsigned int* cand_cnt;      // [nq]
     int refresh_ns;
     const float* eps;            // [nq] error bound of the approximate score (0 for TERMS = 3)
+    int n_stages;                // ring depth (mma_stage_count)
+    int box_cols;                // floats per row per stage: 16 (64-B swizzle) or 32 (128-B swizzle)
     int debug;                   // development only: 1 = skip the epilogue's per-element work, 2 = issue no MMAs
 };
 
@@ -117,6 +119,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
 __device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (32ull << 32) | (1ull << 46) | (4ull << 61);
 }
+// same with 128-byte rows / 128-byte swizzle: 8-row groups 1024 B apart, SWIZZLE_128B = 2
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, bool wide) {
+    return wide ? umma_desc_sw128(smem_addr) : umma_desc_sw64(smem_addr);
+}
 // kind::tf32, fp32 accumulator, both operands K-major, M = 128, N = n
 __host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -148,28 +157,43 @@ __global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int 
     }
 }
 
+// The single-TF32 filter moves 32 columns per stage (a 16 KiB key box: the per-stage cost of barriers,
+// TMA issue and tcgen05.commit is then paid half as often, which is what small batches are bound by);
+// the 3xTF32 filter, with four tiles per stage, stays at 16 columns to keep four stages.
+__host__ __device__ inline int mma_box_cols(int terms) { return terms == 3 ? 16 : 32; }
 __host__ __device__ inline size_t mma_stage_bytes(int nqp, int terms) {
-    return terms == 3 ? 2 * (size_t)kMmaATile + 2 * (size_t)nqp * kMmaRowBytes : (size_t)kMmaATile + (size_t)nqp * kMmaRowBytes;
+    const size_t row = (size_t)mma_box_cols(terms) * 4;
+    return terms == 3 ? 2 * (size_t)kMmaRows * row + 2 * (size_t)nqp * row : (size_t)kMmaRows * row + (size_t)nqp * row;
 }
-__host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms) {
-    const int stages = terms == 3 ? kMmaStages3 : kMmaStages1;
-    return stages * mma_stage_bytes(nqp, terms) + (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 +
-           4 * (size_t)kMmaHitQueue * 16 + 16;
+__host__ __device__ inline size_t mma_fixed_smem_bytes() {
+    return (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 + 4 * (size_t)kMmaHitQueue * 16 + 16;
+}
+// as many stages as fit (at least the pipeline's nominal depth at nq = 256, at most kMmaStagesMax)
+__host__ __device__ inline int mma_stage_count(int nqp, int terms, size_t max_smem) {
+    const size_t room = max_smem > mma_fixed_smem_bytes() ? max_smem - mma_fixed_smem_bytes() : 0;
+    int n = (int)(room / mma_stage_bytes(nqp, terms));
+    return n > kMmaStagesMax ? kMmaStagesMax : n;
+}
+__host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms, int stages) {
+    return stages * mma_stage_bytes(nqp, terms) + mma_fixed_smem_bytes();
 }
 
 template <int TERMS>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_q, const MmaParams p) {
-    constexpr int kMmaStages = TERMS == 3 ? kMmaStages3 : kMmaStages1;
+    const int kMmaStages = p.n_stages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const size_t b_bytes = (size_t)p.nqp * kMmaRowBytes;
+    const int bc = p.box_cols;                                   // floats per row per stage
+    const size_t a_bytes = (size_t)kMmaRows * bc * 4;
+    const size_t b_bytes = (size_t)p.nqp * bc * 4;
+    const bool wide = bc == 32;
     const size_t stage_bytes = mma_stage_bytes(p.nqp, TERMS);
     // TERMS = 3: [a_hi | a_lo | b_hi | b_lo];  TERMS = 1: [a | b]
     auto a_hi = [&](int s) { return base + s * stage_bytes; };
-    auto a_lo = [&](int s) { return base + s * stage_bytes + kMmaATile; };
-    auto b_hi = [&](int s) { return base + s * stage_bytes + (TERMS == 3 ? 2 : 1) * kMmaATile; };
-    auto b_lo = [&](int s) { return base + s * stage_bytes + 2 * kMmaATile + b_bytes; };
+    auto a_lo = [&](int s) { return base + s * stage_bytes + a_bytes; };
+    auto b_hi = [&](int s) { return base + s * stage_bytes + (TERMS == 3 ? 2 : 1) * a_bytes; };
+    auto b_lo = [&](int s) { return base + s * stage_bytes + 2 * a_bytes + b_bytes; };
     uint8_t* tail = base + kMmaStages * stage_bytes;
     uint64_t* full = (uint64_t*)tail;            // [stages] TMA landed
     uint64_t* conv = full + kMmaStagesMax;       // [stages] hi/lo tiles ready (TERMS = 3)
@@ -229,11 +253,11 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
             for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
                 for (int c = 0; c < p.n_chunks; c++) {
                     mbar_wait(empty + stage, phase ^ 1u);
-                    mbar_arrive_expect_tx(full + stage, (uint32_t)(kMmaATile + (TERMS == 3 ? 2 : 1) * b_bytes));
-                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * kMmaBoxCols, (int)(tile * kMmaRows), pol_stream);
-                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * kMmaBoxCols, 0, pol_keep);
+                    mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + (TERMS == 3 ? 2 : 1) * b_bytes));
+                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * bc, (int)(tile * kMmaRows), pol_stream);
+                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * bc, 0, pol_keep);
                     if constexpr (TERMS == 3)
-                        tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * kMmaBoxCols, p.nqp, pol_keep);
+                        tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * bc, p.nqp, pol_keep);
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -253,15 +277,14 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                     if constexpr (TERMS == 3) mbar_wait(conv + stage, phase);   // hi / lo key tiles written and fenced
                     tc_fence_after();
                     const uint32_t ah = smem_u32(a_hi(stage)), bh = smem_u32(b_hi(stage));
-#pragma unroll
-                    for (int k = 0; k < kMmaBoxCols / 8; k++) { // UMMA K = 8 TF32 = 32 bytes along the swizzled row
+                    for (int k = 0; k < bc / 8; k++) {          // UMMA K = 8 TF32 = 32 bytes along the swizzled row
                         if (p.debug & 2) break;
                         const uint32_t off = (uint32_t)k * 32u;
-                        umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bh + off), idesc, (c | k) != 0);
+                        umma_tf32(d_tmem, umma_desc(ah + off, wide), umma_desc(bh + off, wide), idesc, (c | k) != 0);
                         if constexpr (TERMS == 3) {
                             const uint32_t al = smem_u32(a_lo(stage)), bl = smem_u32(b_lo(stage));
-                            umma_tf32(d_tmem, umma_desc_sw64(ah + off), umma_desc_sw64(bl + off), idesc, 1u);
-                            umma_tf32(d_tmem, umma_desc_sw64(al + off), umma_desc_sw64(bh + off), idesc, 1u);
+                            umma_tf32(d_tmem, umma_desc(ah + off, wide), umma_desc(bl + off, wide), idesc, 1u);
+                            umma_tf32(d_tmem, umma_desc(al + off, wide), umma_desc(bh + off, wide), idesc, 1u);
                         }
                     }
                     umma_commit(empty + stage);                 // stage is free once these MMAs retire
@@ -393,7 +416,7 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                 float4* hi4 = reinterpret_cast<float4*>(a_hi(stage));
                 float4* lo4 = reinterpret_cast<float4*>(a_lo(stage));
 #pragma unroll
-                for (int i = 0; i < kMmaATile / 16 / 128; i++) {   // element-wise: the swizzle does not matter
+                for (int i = 0; i < (int)(a_bytes / 16 / 128); i++) {   // element-wise: the swizzle does not matter
                     float4 a = hi4[ct + i * 128], h, l;
                     tf32_split(a.x, h.x, l.x);
                     tf32_split(a.y, h.y, l.y);

@@ -114,7 +114,7 @@ static int get_encoder() {
 struct Tuning {
     int refresh_ns = 4000;
     bool disable_lbest = false;
-    int mma_min_queries = 32;      // batches at least this large go to the tensor-core path
+    int mma_min_queries = 5;       // batches at least this large go to the tensor-core path (measured break-even)
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
 };
@@ -1025,29 +1025,34 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     CUtensorMap tmap_q;
     cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)(2 * nqp)};
     cuuint64_t gstride[1] = {(cuuint64_t)dim * 4};
-    cuuint32_t box[2] = {(cuuint32_t)kMmaBoxCols, (cuuint32_t)nqp};
+    const int bc = mma_box_cols(terms);
+    cuuint32_t box[2] = {(cuuint32_t)bc, (cuuint32_t)nqp};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(&tmap_q, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, qs, gdim, gstride, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, bc == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(-2, "cuTensorMapEncodeTiled (queries) failed with CUresult %d", (int)r);
 
     MmaParams mp;
     memset(&mp, 0, sizeof(mp));
-    mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = (dim + kMmaBoxCols - 1) / kMmaBoxCols;
+    mp.n_rows = sp.n_rows; mp.dim = dim; mp.n_chunks = (dim + bc - 1) / bc;
+    mp.box_cols = bc;
+    const CUtensorMap& tmap_keys = bc == 32 ? s->tmap : s->tmap_mma;   // the exact scan's [32 x 128] / 128-B-swizzle map serves here too
     mp.nq = g; mp.nqp = nqp; mp.f64 = norm ? 0 : 1;
     mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
     mp.refresh_ns = 5000;
     mp.eps = terms == 1 ? eps : nullptr;
     mp.debug = getenv("TFP_MMA_DEBUG") ? atoi(getenv("TFP_MMA_DEBUG")) : 0;
-    const size_t smem = mma_smem_bytes(nqp, terms);
+    mp.n_stages = mma_stage_count(nqp, terms, (size_t)s->max_smem);
+    if (mp.n_stages < 2) return fail(-4, "internal: tensor-core stages do not fit shared memory");
+    const size_t smem = mma_smem_bytes(nqp, terms, mp.n_stages);
     mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
-    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
-    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
+    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
     CU_OK(cudaGetLastError());
     mp.mode = 1;
-    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
-    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(s->tmap_mma, tmap_q, mp);
+    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
+    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
     CU_OK(cudaGetLastError());
 
     FinalizeParams fp;
@@ -1217,7 +1222,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     // relies on counts one row per CTA, so k + margin must not exceed the grid.
     const bool mma_ok = fused && s->tmap_ok && ksel <= kMmaMaxTopK && grid >= ksel + kMmaMargin &&
                         n >= tuning().mma_min_rows && tuning().mma_min_queries > 0 &&
-                        mma_smem_bytes(kMmaMaxNQ, 3) <= (size_t)s->max_smem;
+                        mma_stage_count(kMmaMaxNQ, 3, (size_t)s->max_smem) >= 3;
     int i = 0;
     while (i < count) {
         const bool norm = path_of(first + i);

@@ -1,5 +1,5 @@
-"""The tensor-core path (>= 32 same-path queries on a large store): tcgen05 3xTF32 filter + exact
-re-score.  Results must be what nq single finds return: similarities bit-identical to the oracle."""
+"""The tensor-core path (5 or more same-path queries on a store of >= 65536 rows): tcgen05 TF32 filter
++ exact re-score.  Results must be what nq single finds return: similarities bit-identical to the oracle."""
 import numpy as np
 import pytest
 
@@ -26,7 +26,7 @@ def run_batch(tfp, oracle, K, Q, k, normalized, expect_mma=True):
     return passes, reruns
 
 
-@pytest.mark.parametrize("nq,d,k", [(32, 256, 10), (64, 768, 10), (200, 128, 100), (256, 64, 100), (300, 96, 7)])
+@pytest.mark.parametrize("nq,d,k", [(5, 64, 10), (17, 160, 3), (32, 256, 10), (64, 768, 10), (200, 128, 100), (256, 64, 100), (300, 96, 7)])
 def test_mma_path_matches_oracle_normalized(tfp, oracle, nq, d, k):
     K = make_keys(70000, d, seed=nq + d, normalized=True)
     Q = make_keys(nq, d, seed=nq + d + 1, normalized=True)
@@ -84,7 +84,7 @@ def test_mma_path_mixed_paths_split_into_runs(tfp, oracle):
 
 def test_small_batches_and_small_stores_stay_on_the_exact_kernel(tfp, oracle):
     K = make_keys(70000, 64, seed=31, normalized=True)
-    Q = make_keys(16, 64, seed=32, normalized=True)
+    Q = make_keys(4, 64, seed=32, normalized=True)
     passes, _ = run_batch(tfp, oracle, K, Q, 10, True, expect_mma=False)
     assert passes == 0
     K = make_keys(5000, 64, seed=33, normalized=True)
