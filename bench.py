@@ -421,6 +421,7 @@ def main():
     args = ap.parse_args()
     select_workload(args.workload)
     args.warmup = max(args.warmup, 3)
+    os.environ.setdefault("NCCL_DEBUG", "WARN")     # keep NCCL's version banner off stdout: ONE JSON line is the contract
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

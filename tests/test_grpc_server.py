@@ -153,14 +153,22 @@ def test_concurrent_finds_are_batched_onto_the_tensor_cores(tfp, oracle):
         want = [oracle.scan_block(K, q, 10, True) for q in Q]
         got = [None] * len(Q)
         clients = [Client(f"127.0.0.1:{port}") for _ in Q]
-        for rounds in range(3):                                  # a few rounds so that real batches form
+        for rounds in range(3):
             gate = threading.Barrier(len(Q))
 
             def work(i):
                 gate.wait()
                 got[i] = clients[i].find(Q[i], 10)
             ts = [threading.Thread(target=work, args=(i,)) for i in range(len(Q))]
-            [t.start() for t in ts]; [t.join() for t in ts]
+            # hold the store briefly so that the requests pile up behind it, as they do behind a busy GPU:
+            # the batcher must then take the backlog as one batch
+            backend.lock.acquire()
+            [t.start() for t in ts]
+            deadline = time.time() + 10
+            while backend.batcher.q.qsize() < len(Q) - 8 and time.time() < deadline:
+                time.sleep(0.01)
+            backend.lock.release()
+            [t.join() for t in ts]
             for i in range(len(Q)):
                 ks, vs, sims = got[i]
                 assert np.array_equal(sims, want[i][1])
