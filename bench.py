@@ -48,6 +48,10 @@ def select_workload(name: str):
     if name == "target":
         N_KEYS, DIM, SEED = 10_000_000, 1024, 0x5EED0003
         WORKLOAD = "north-star target: 10M keys x 1024-d fp32, single-query top-10, normalised-key fast path"
+    if name == "c4":
+        N_KEYS, DIM, SEED = 100_000_000, 384, 0x5EED0004
+        WORKLOAD = ("C4 (BASELINE.json configs[3]): 100M keys x 384-d fp32 (153.6 GB), single-query top-10, "
+                    "sharded by rows, NCCL candidate merge")
     if name == "c3":
         N_KEYS, DIM, SEED, TOPK, QUERIES_PER_STEP = 10_000_000, 1024, 0x5EED0003, 100, 256
         METRIC = "StoresFind queries/sec (top-100, batch 256)"
@@ -204,7 +208,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     torch.cuda.empty_cache()
     assert len(store) == rows_local and store.keys_are_normalized
     sharded = ShardedStore(ops, rank, world) if world > 1 else None
-    if sharded:
+    if sharded is not None:
         sharded.key_len = DIM
         if args.exchange != "torch":            # scan + ncclAllGather + merge become one library call
             try:
@@ -415,7 +419,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--workload", choices=["c2", "target", "c3"], default="c2")
+    ap.add_argument("--workload", choices=["c2", "target", "c3", "c4"], default="c2")
     ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="native",
                     help="N>1: all-gather through torch.distributed, or inside libtfpstore (one call per query)")
     args = ap.parse_args()
