@@ -210,7 +210,18 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     sharded = ShardedStore(ops, rank, world) if world > 1 else None
     if sharded is not None:
         sharded.key_len = DIM
-        if args.exchange != "torch":            # scan + ncclAllGather + merge become one library call
+        if args.exchange == "p2p":              # the scan kernel pushes its records to the peers over NVLink
+            ok = True
+            try:
+                ops.init_p2p(rank, world)
+            except Exception as e:
+                ok = False
+                print(f"bench[{rank}]: peer exchange unavailable ({e})", file=sys.stderr)
+            flags = [None] * world
+            dist.all_gather_object(flags, ok)
+            if not all(flags):                  # every rank must take the same path
+                args.exchange = "native"
+        if args.exchange in ("native", "native-per-lane"):   # scan + ncclAllGather + merge in one library call
             try:
                 ops.init_native_comm(rank, world, shared=(args.exchange == "native"))
             except Exception as e:              # NCCL not resolvable by dlopen: same exchange through torch.distributed
@@ -275,7 +286,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         barrier()
         clk = clocks.stop()
         ms_total = e0.elapsed_time(e1)
-        launches = launches_now() - launches0 + (args.steps if world > 1 else 0)   # + one merge kernel per step
+        launches = launches_now() - launches0 + (args.steps if world > 1 and args.exchange == "torch" else 0)   # torch path: + the merge kernel
     t = torch.tensor([ms_total], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -387,7 +398,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                        "exchange": args.exchange if world > 1 else None,
                        "l2": "inputs larger than L2 (keys %.2f GB per GPU vs 126 MB); no flush" % (algo_bytes / 1e9)
                              if algo_bytes > 4 * 126e6 else "keys per GPU %.0f MB: partly L2-resident" % (algo_bytes / 1e6),
-                       "parallelism": "row-sharded x%d, one ncclAllGather of top-k records + device merge per query" % world
+                       "parallelism": ("row-sharded x%d, " % world) +
+                                      ("top-k records pushed to every peer over NVLink by the scan kernel, stream wait, device merge"
+                                       if args.exchange == "p2p" else "one all-gather of top-k records + device merge per query")
                                       if world > 1 else "single GPU"},
             "clocks": clk,
             "tensor_core_path": dict(zip(("passes", "exact_reruns"), ctx.mma_counters())) if batched else None,
@@ -407,10 +420,10 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
+    ops.close()          # (with the peer exchange this is collective: unmap everywhere, barrier, free)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    ops.close()
 
 
 def main():
@@ -420,8 +433,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=["c2", "target", "c3", "c4"], default="c2")
-    ap.add_argument("--exchange", choices=["torch", "native", "native-per-lane"], default="native",
-                    help="N>1: all-gather through torch.distributed, or inside libtfpstore (one call per query)")
+    ap.add_argument("--exchange", choices=["p2p", "torch", "native", "native-per-lane"], default="p2p",
+                    help="N>1: records pushed to the peers by the scan kernel (p2p), ncclAllGather inside libtfpstore "
+                         "(native), or torch.distributed (torch)")
     args = ap.parse_args()
     select_workload(args.workload)
     args.warmup = max(args.warmup, 3)

@@ -224,6 +224,35 @@ int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids
 int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims,
                                  int* out_shard, int* out_index);
 
+/* ---- sharded find over peer memory (no reference counterpart) ----------
+ * The same exchange without a collective library call: the scan kernel's last CTA writes this
+ * shard's records straight into EVERY rank's gather block over NVLink (peer-mapped memory) and
+ * raises a sequence word there; the receiving context's stream waits for its peers' words with a
+ * stream memory operation (cuStreamWaitValue32 -- no kernel spins) and merges.  One process per
+ * GPU, 2..8 GPUs with peer access (one NVSwitch box).  Set-up, per find context:
+ *   tfp_find_ctx_p2p_export  allocate this rank's gather block (2 parities x world slots of
+ *                        slot_bytes, + world sequence words) and return its 64-byte cudaIpc handle;
+ *   (the host hands every rank's handle to every rank: torch.distributed, MPI, a file)
+ *   tfp_find_ctx_p2p_attach  map the peers' blocks; `handles` = world x 64 bytes in rank order.
+ *                        Every rank must have attached before any rank launches (barrier).
+ * After that tfp_find_ctx_launch_sharded[_batch] uses the peer exchange whenever count records fit
+ * slot_bytes, else the NCCL communicator if one was set.  Every rank must issue the same sequence
+ * of sharded launches per context (a rank that skips one leaves its peers' streams waiting).
+ *   tfp_find_ctx_p2p_detach  unmap the peers' blocks.  Every rank detaches, THEN (barrier) contexts
+ *                        are destroyed: an exported block must not be freed while a peer maps it. */
+int tfp_find_ctx_p2p_export(tfp_find_ctx* c, int world, size_t slot_bytes, void* handle_out, size_t handle_bytes);
+int tfp_find_ctx_p2p_attach(tfp_find_ctx* c, const void* handles, int rank, int world);
+int tfp_find_ctx_p2p_detach(tfp_find_ctx* c);
+/* The same find, with the winning key rows (StoresFindResult.Keys, store.go:399-401): every shard's
+ * top-k rows travel to every rank with the records, the merged answer carries the rows of the global
+ * winners, and tfp_find_ctx_download_merged_keys brings n, ids, sims and rows to the host in ONE copy
+ * (stride topk per query; out_keys [count x topk x dim]).  Peer exchange only; the slot must hold
+ * tfp_p2p_slot_bytes_with_keys(count, topk, dim) bytes. */
+size_t tfp_p2p_slot_bytes_with_keys(int count, int topk, int dim);
+int tfp_find_ctx_launch_sharded_keys(tfp_find_ctx* c, int first, int count, int topk);
+int tfp_find_ctx_download_merged_keys(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims,
+                                      float* out_keys);
+
 /* ---- pinned host staging (no reference counterpart) --------------------------------
  * Keys handed to tfp_store_set / queries handed to the find entry points are copied to
  * the GPU from wherever they are; from ordinary (pageable) memory that copy runs at

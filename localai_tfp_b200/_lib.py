@@ -61,6 +61,12 @@ PROTOTYPES = {
     "tfp_find_ctx_launch_sharded_batch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
     "tfp_find_ctx_merged_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "tfp_find_ctx_download_merged": (C.c_int, [vp, i32p, i64p, fp, i32p, i32p]),
+    "tfp_find_ctx_p2p_export": (C.c_int, [vp, C.c_int, C.c_size_t, vp, C.c_size_t]),
+    "tfp_find_ctx_p2p_attach": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+    "tfp_find_ctx_p2p_detach": (C.c_int, [vp]),
+    "tfp_p2p_slot_bytes_with_keys": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "tfp_find_ctx_launch_sharded_keys": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
+    "tfp_find_ctx_download_merged_keys": (C.c_int, [vp, i32p, i64p, fp, fp]),
     "tfp_host_alloc": (vp, [C.c_size_t]),
     "tfp_host_free": (None, [vp]),
     "tfp_scan_topk_noalloc": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp]),

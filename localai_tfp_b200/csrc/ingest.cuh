@@ -120,21 +120,22 @@ __global__ void gather_rows_kernel(const float* __restrict__ keys, int dim, cons
 
 // Cross-shard merge: one CTA per query, bitonic sort of
 // n_shards x topk words (sim order, then lower shard, then position).  Input is the
-// all-gathered block of packed records, [n_shards x nq] records of rec_bytes each.
-__global__ void merge_records_kernel(const uint8_t* __restrict__ g, int rec_bytes, int n_shards, int nq, int topk, int P,
+// gathered block of packed records: shard sh's nq records (rec_bytes each) start at sh * shard_stride
+// bytes.  Read with ld.cg: with the peer exchange the records were written by other GPUs over NVLink.
+__global__ void merge_records_kernel(const uint8_t* g, int rec_bytes, size_t shard_stride, int n_shards, int nq, int topk, int P,
                                      float* __restrict__ o_sims, int64_t* __restrict__ o_ids,
                                      int* __restrict__ o_shard, int* __restrict__ o_index, int* __restrict__ o_n) {
     extern __shared__ uint64_t mbuf[];
     const int q = blockIdx.x;
     const int total = n_shards * topk;
-    auto rec = [&](int sh) { return g + ((size_t)sh * nq + q) * rec_bytes; };
+    auto rec = [&](int sh) { return g + (size_t)sh * shard_stride + (size_t)q * rec_bytes; };
     for (int i = threadIdx.x; i < P; i += blockDim.x) {
         uint64_t w = 0ull;
         if (i < total) {
             int sh = i / topk, j = i - sh * topk;
             const uint8_t* r = rec(sh);
-            if (j < *(const int*)r) {
-                float s = ((const float*)(r + 8 + (size_t)topk * 8))[j];
+            if (j < __ldcg((const int*)r)) {
+                float s = __ldcg((const float*)(r + 8 + (size_t)topk * 8) + j);
                 // low word: earlier (shard, position) ranks higher among equal scores
                 w = ((uint64_t)score_to_order(s) << 32) | (uint64_t)(0xFFFFFFFFu - (uint32_t)i);
             }
@@ -155,7 +156,7 @@ __global__ void merge_records_kernel(const uint8_t* __restrict__ g, int rec_byte
     }
     int valid = 0;
     for (int sh = 0; sh < n_shards; sh++) {
-        int c = *(const int*)rec(sh);
+        int c = __ldcg((const int*)rec(sh));
         valid += c < topk ? c : topk;
     }
     const int m = valid < topk ? valid : topk;
@@ -165,8 +166,8 @@ __global__ void merge_records_kernel(const uint8_t* __restrict__ g, int rec_byte
             uint32_t pos = 0xFFFFFFFFu - (uint32_t)mbuf[i];
             int sh = (int)(pos / (uint32_t)topk), j = (int)(pos - (uint32_t)sh * topk);
             const uint8_t* r = rec(sh);
-            o_sims[at] = ((const float*)(r + 8 + (size_t)topk * 8))[j];
-            o_ids[at] = ((const int64_t*)(r + 8))[j];
+            o_sims[at] = __ldcg((const float*)(r + 8 + (size_t)topk * 8) + j);
+            o_ids[at] = __ldcg((const long long*)(r + 8) + j);
             o_shard[at] = sh;
             o_index[at] = j;
         } else {

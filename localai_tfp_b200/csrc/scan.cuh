@@ -36,6 +36,19 @@ struct QInfo {        // per staged query, filled on the host (exact reference a
     int pad;
 };
 
+// Peer exchange of result records over NVLink: the CTA that finishes a find writes
+// this shard's packed records straight into every rank's gather buffer (peer-mapped memory) and
+// then raises a sequence word there; the receiving rank's stream waits on that word (a stream
+// memory operation, no kernel spins) before its merge kernel runs.  world == 0: no exchange.
+constexpr int kXchgMaxWorld = 8;
+struct XchgParams {
+    uint8_t* slot[kXchgMaxWorld];        // where THIS rank's records land on rank r (r == me: the local buffer)
+    unsigned int* flag[kXchgMaxWorld];   // rank r's "records from rank `me` have landed" word
+    int world, me;
+    unsigned int seq;                    // value to raise the words to (monotonic per find context)
+    int raise;                           // this launch completes the find: raise the words after the copy
+};
+
 struct ScanParams {
     const float* keys;        // [capacity x dim] row-major
     const int64_t* ids;       // [capacity]
@@ -73,7 +86,63 @@ struct ScanParams {
     uint8_t* out_rec;         // [*] packed records (include/tfp_store.h), rec_bytes each, rec_topk slots
     int rec_bytes;
     int rec_topk;
+    XchgParams xchg;          // fused push of the finished records to the peer ranks (world == 0: off)
 };
+
+// Copy `bytes` (a multiple of 16) of finished records from local memory to the same offset of this
+// rank's slot on every rank, then make the copies visible system-wide.  All `nthreads` threads call it;
+// the caller puts a CTA barrier between this and xchg_raise.
+__device__ __forceinline__ void xchg_copy(const XchgParams& x, const uint8_t* src, size_t off, size_t bytes, int tid,
+                                          int nthreads) {
+    const size_t words = bytes >> 4;
+    const uint4* s = (const uint4*)src;
+    for (size_t i = (size_t)tid; i < words * (size_t)x.world; i += (size_t)nthreads) {
+        const int r = (int)(i / words);
+        const size_t w = i - (size_t)r * words;
+        const uint4 v = __ldcg(s + w);
+        uint4* d = (uint4*)(x.slot[r] + off) + w;
+        asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(d), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+    __threadfence_system();
+}
+__device__ __forceinline__ void xchg_raise(const XchgParams& x, int tid) {
+    if (x.raise && tid < x.world && tid != x.me)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(x.flag[tid]), "r"(x.seq) : "memory");
+}
+// Stand-alone push for the paths whose records are written by other kernels (tensor-core finalize,
+// big-k decode, multi-launch batches, empty shards).
+__global__ void push_records_kernel(const __grid_constant__ XchgParams x, const uint8_t* src, size_t bytes) {
+    xchg_copy(x, src, 0, bytes, (int)threadIdx.x, (int)blockDim.x);
+    __syncthreads();
+    xchg_raise(x, (int)threadIdx.x);
+}
+// Winning key rows of a sharded find, from the store straight into every rank's slot: CTA (i, q) copies
+// row out_slots[q][i] to byte offset keys_off + (q * topk + i) * dim * 4 of this rank's slot everywhere.
+// The words are raised by the push_records_kernel that follows in the stream.
+__global__ void push_rows_kernel(const __grid_constant__ XchgParams x, const float* __restrict__ keys, int dim,
+                                 const uint32_t* __restrict__ out_slots, const int* __restrict__ out_n, int stride, int topk,
+                                 size_t keys_off) {
+    const int i = blockIdx.x, q = blockIdx.y;
+    if (i >= out_n[q]) return;
+    const float* src = keys + (size_t)out_slots[(size_t)q * stride + i] * dim;
+    const size_t off = keys_off + ((size_t)q * topk + i) * (size_t)dim * 4;
+    for (int t = threadIdx.x; t < dim * x.world; t += blockDim.x) {
+        const int r = t / dim, cidx = t - r * dim;
+        ((float*)(x.slot[r] + off))[cidx] = src[cidx];
+    }
+    __threadfence_system();
+}
+// After the merge: winner i of query q sits in shard[q][i]'s slot at position index[q][i].
+__global__ void gather_merged_rows_kernel(const uint8_t* block, size_t shard_stride, size_t keys_off, int dim, int topk,
+                                          const int* __restrict__ shard, const int* __restrict__ index,
+                                          const int* __restrict__ n, float* __restrict__ out) {
+    const int i = blockIdx.x, q = blockIdx.y;
+    if (i >= n[q]) return;
+    const size_t at = (size_t)q * topk + i;
+    const float* src = (const float*)(block + (size_t)shard[at] * shard_stride + keys_off) + ((size_t)q * topk + index[at]) * dim;
+    float* dst = out + at * dim;
+    for (int t = threadIdx.x; t < dim; t += blockDim.x) dst[t] = __ldcg(src + t);
+}
 
 // ---- per-row arithmetic ----------------------------------------------------
 template <bool F64> struct Acc;
@@ -359,6 +428,13 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         named_bar_sync(kSelBarrier, kSelThreads);
     }
     if (tid == 0) { *p.ticket = 0u; *p.tile_counter = 0u; }
+    if (p.xchg.world > 0) {
+        // this launch's records are final (the loop above ended on a barrier): push them to the peers
+        const size_t off = (size_t)p.out_first * p.rec_bytes;
+        xchg_copy(p.xchg, p.out_rec + off, off, (size_t)NQ * p.rec_bytes, tid, kSelThreads);
+        named_bar_sync(kSelBarrier, kSelThreads);
+        xchg_raise(p.xchg, tid);
+    }
 }
 
 template <int NQ>
@@ -413,7 +489,7 @@ __device__ __forceinline__ void tile_offer(const ScanParams& p, SelState* sel, c
 // ---- the TMA kernel -----------------------------------------------------------
 template <int NQ, bool F64, bool SPILL>
 __global__ void __launch_bounds__(kScanThreads, 1)
-scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
+scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ ScanParams p) {
     extern __shared__ uint8_t smem_raw[];
     const int dpad = p.n_chunks * kBoxCols;
     ScanSmem sm = scan_carve(smem_raw, p.n_stages, NQ, dpad, p.cap);
@@ -586,7 +662,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const ScanParams p) {
 // from global memory, one thread per row, so it is correct but not tuned. -------
 template <int NQ, bool F64, bool SPILL>
 __global__ void __launch_bounds__(kSelThreads, 4)
-scan_generic_kernel(const ScanParams p) {
+scan_generic_kernel(const __grid_constant__ ScanParams p) {
     extern __shared__ uint8_t smem_raw[];
     ScanSmem sm;  // no stages, no staged query: only the selection state
     uint8_t* base = smem_raw + ((16u - (smem_u32(smem_raw) & 15u)) & 15u);

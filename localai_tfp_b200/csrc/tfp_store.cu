@@ -296,6 +296,16 @@ struct tfp_find_ctx {
     int comm_rank = 0, comm_world = 0;
     DevBuf gathered, merged;
     int merged_topk = 0, merged_count = 0;
+    int merged_keys_dim = 0;             // > 0: the merged block carries the winners' key rows after its fixed part
+    // sharded finds over peer memory (tfp_find_ctx_p2p_*): this rank's gather block
+    // [2 parities][world][x_slot bytes] + [world] sequence words, and every rank's block mapped here
+    DevBuf xbuf;
+    size_t x_slot = 0;
+    uint8_t* x_peer[kXchgMaxWorld] = {nullptr};
+    int x_world = 0, x_me = 0;
+    unsigned int x_seq = 0;
+    bool x_ready = false;
+    bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
     int64_t mma_passes = 0, mma_fallbacks = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
@@ -887,6 +897,9 @@ static void ctx_destroy(tfp_find_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     c->nccl_comm = nullptr;
+    for (int r = 0; r < kXchgMaxWorld; r++)
+        if (c->x_peer[r] && r != c->x_me) cudaIpcCloseMemHandle(c->x_peer[r]);
+    c->xbuf.release();
     if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
                       &c->cub_tmp, &c->out_block, &c->dbg_times, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
@@ -1090,8 +1103,11 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
 }
 
 // Enqueue the scan(s) for staged queries [first, first+count).  Caller holds the shared lock.
-static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
+// xchg: push the finished records to the peer ranks from inside the scan kernel when the find is
+// made of exact fused scans only (c->x_pushed tells the caller whether that happened).
+static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, const XchgParams* xchg = nullptr) {
     tfp_store* s = c->st;
+    c->x_pushed = false;
     if (c->dim != s->dim)                                                            // store.go:480-482
         return fail(1, "Try to find key with length %d when existing length is %d", c->dim, s->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
@@ -1191,6 +1207,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
         p.n_stages = n_stages;
         p.q_first = qf;
         p.out_first = of;
+        p.xchg.raise = (of + g == count) ? 1 : 0;   // the launch that finishes the find raises the peers' words
         int rc;
         if (fused) rc = norm ? launch_scan_nq<false, false>(c, g, p, use_tma, grid, smem)
                              : launch_scan_nq<true, false>(c, g, p, use_tma, grid, smem);
@@ -1223,6 +1240,10 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk) {
     const bool mma_ok = fused && s->tmap_ok && ksel <= kMmaMaxTopK && grid >= ksel + kMmaMargin &&
                         n >= tuning().mma_min_rows && tuning().mma_min_queries > 0 &&
                         mma_stage_count(kMmaMaxNQ, 3, (size_t)s->max_smem) >= 3;
+    if (xchg && fused && !(mma_ok && count >= tuning().mma_min_queries)) {
+        p.xchg = *xchg;     // every launch below is an exact fused scan: each pushes its own records
+        c->x_pushed = true;
+    }
     int i = 0;
     while (i < count) {
         const bool norm = path_of(first + i);
@@ -1405,7 +1426,8 @@ extern "C" int tfp_merge_records(const void* d_gathered, int n_shards, int nq, i
     if ((size_t)P * 8 > 48 * 1024)
         CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
     merge_records_kernel<<<nq, 256, (size_t)P * 8, (cudaStream_t)stream>>>((const uint8_t*)d_gathered,
-                                                                           (int)record_bytes(topk), n_shards, nq, topk, P,
+                                                                           (int)record_bytes(topk),
+                                                                           record_bytes(topk) * (size_t)nq, n_shards, nq, topk, P,
                                                                            o_sims, o_ids, o_shard, o_index, o_n);
     CU_OK(cudaGetLastError());
     return 0;
@@ -1616,6 +1638,98 @@ extern "C" int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------
+// Peer exchange for sharded finds: the scan kernel itself writes this shard's records into every
+// rank's gather block over NVLink (cudaIpc-mapped peer memory) and raises a sequence word there; the
+// receiving stream waits on its words with a stream memory operation, then merges.  No collective
+// library call and no extra kernel per find.  Buffer reuse is safe with two parities: a rank pushes
+// find s+2 only after its own wait for find s+1, and a peer's word s+1 is raised by its scan s+1,
+// which its stream runs after its merge of find s -- the last reader of the parity being overwritten.
+// ---------------------------------------------------------------------------
+typedef CUresult (*PFN_streamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static PFN_streamWaitValue32 g_wait32 = nullptr;
+static std::once_flag g_wait32_once;
+static int wait32_api() {
+    std::call_once(g_wait32_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            g_wait32 = (PFN_streamWaitValue32)fn;
+    });
+    return g_wait32 ? 0 : fail(-7, "cuStreamWaitValue32 is not available from the CUDA driver");
+}
+
+static size_t xbuf_flags_offset(int world, size_t slot) { return ((size_t)2 * world * slot + 255) & ~(size_t)255; }
+
+static void p2p_detach(tfp_find_ctx* c) {
+    for (int r = 0; r < kXchgMaxWorld; r++) {
+        if (c->x_peer[r] && r != c->x_me) cudaIpcCloseMemHandle(c->x_peer[r]);
+        c->x_peer[r] = nullptr;
+    }
+    c->x_ready = false;
+}
+
+extern "C" int tfp_find_ctx_p2p_export(tfp_find_ctx* c, int world, size_t slot_bytes, void* handle_out, size_t handle_bytes) {
+    if (!c || !handle_out || handle_bytes < sizeof(cudaIpcMemHandle_t)) return fail(2, "tfp_find_ctx_p2p_export: bad argument");
+    if (world < 2 || world > kXchgMaxWorld) return fail(2, "tfp_find_ctx_p2p_export: world = %d outside [2, %d]", world, kXchgMaxWorld);
+    if (slot_bytes < 256 || slot_bytes > ((size_t)64 << 20)) return fail(2, "tfp_find_ctx_p2p_export: slot_bytes outside [256, 64 MiB]");
+    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st) || wait32_api()) return -1;
+    CU_OK(cudaStreamSynchronize(c->stream));
+    p2p_detach(c);
+    slot_bytes = (slot_bytes + 255) & ~(size_t)255;
+    const size_t total = xbuf_flags_offset(world, slot_bytes) + 256;
+    c->xbuf.release();                      // a fresh allocation: an exported block is never resized in place
+    if (c->xbuf.reserve(total)) return -1;
+    CU_OK(cudaMemset(c->xbuf.p, 0, total));  // the sequence words start at 0, before anybody can see the handle
+    c->x_slot = slot_bytes;
+    c->x_world = world;
+    c->x_seq = 0;
+    cudaIpcMemHandle_t h;
+    CU_OK(cudaIpcGetMemHandle(&h, c->xbuf.p));
+    memcpy(handle_out, &h, sizeof(h));
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_p2p_attach(tfp_find_ctx* c, const void* handles, int rank, int world) {
+    if (!c || !handles) return fail(2, "tfp_find_ctx_p2p_attach: NULL argument");
+    if (!c->xbuf.p || world != c->x_world || rank < 0 || rank >= world)
+        return fail(2, "tfp_find_ctx_p2p_attach: call tfp_find_ctx_p2p_export with the same world first");
+    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st) || wait32_api()) return -1;
+    c->x_me = rank;
+    for (int r = 0; r < world; r++) {
+        if (r == rank) { c->x_peer[r] = c->xbuf.as<uint8_t>(); continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const uint8_t*)handles + (size_t)r * sizeof(h), sizeof(h));
+        void* ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            p2p_detach(c);
+            return fail(-7, "cudaIpcOpenMemHandle for rank %d failed: %s (no peer access between these GPUs?)", r, cudaGetErrorString(e));
+        }
+        c->x_peer[r] = (uint8_t*)ptr;
+    }
+    // prove that this stream accepts the wait operation before any find depends on it (0 >= 0: passes at once)
+    unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + xbuf_flags_offset(world, c->x_slot));
+    CUresult r = g_wait32((CUstream)c->stream, (CUdeviceptr)(words + rank), 0u, CU_STREAM_WAIT_VALUE_GEQ);
+    if (r != CUDA_SUCCESS) { p2p_detach(c); return fail(-7, "cuStreamWaitValue32 failed with CUresult %d", (int)r); }
+    CU_OK(cudaStreamSynchronize(c->stream));
+    c->x_ready = true;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_p2p_detach(tfp_find_ctx* c) {
+    if (!c) return fail(2, "tfp_find_ctx_p2p_detach: ctx is NULL");
+    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    CU_OK(cudaStreamSynchronize(c->stream));
+    p2p_detach(c);
+    return 0;
+}
+
 struct MergedLayout {   // [count x topk] sims f32 | ids i64 | shard i32 | index i32 | n[count] i32 (each 16-aligned)
     size_t sims, ids, shard, index, n, total;
     MergedLayout(int k, int count) {
@@ -1626,25 +1740,14 @@ struct MergedLayout {   // [count x topk] sims f32 | ids i64 | shard i32 | index
     }
 };
 
-extern "C" int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk) {
-    if (!c) return fail(2, "tfp_find_ctx_launch_sharded: ctx is NULL");
-    if (!c->nccl_comm) return fail(2, "tfp_find_ctx_launch_sharded: call tfp_find_ctx_comm_init first");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
-    if (set_device(c->st)) return -1;
-    int rc = ctx_launch_locked(c, first, count, topk);
-    if (rc) return rc;
-    const int k = c->last_topk;
-    const size_t rb = record_bytes(k);
-    const int world = c->comm_world;
-    if ((int64_t)world * k > 16384) return fail(2, "sharded find: world x topk = %lld exceeds 16384", (long long)world * k);
+static int launch_merge(tfp_find_ctx* c, const uint8_t* gathered, size_t shard_stride, size_t rb, int world, int count, int k) {
     MergedLayout L(k, count);
-    if (c->gathered.reserve(rb * count * world) || c->merged.reserve(L.total)) return -1;
-    NCCL_OK(g_nccl.AllGather(c->out_rec, c->gathered.p, rb * count, /*ncclUint8*/ 1, c->nccl_comm, c->stream));
+    if (c->merged.reserve(L.total)) return -1;
     uint8_t* m = c->merged.as<uint8_t>();
     int P = next_pow2(std::max(world * k, 2));
     if ((size_t)P * 8 > 48 * 1024)
         CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
-    merge_records_kernel<<<count, 256, (size_t)P * 8, c->stream>>>(c->gathered.as<uint8_t>(), (int)rb, world, count, k, P,
+    merge_records_kernel<<<count, 256, (size_t)P * 8, c->stream>>>(gathered, (int)rb, shard_stride, world, count, k, P,
                                                                   (float*)(m + L.sims), (int64_t*)(m + L.ids),
                                                                   (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n));
     CU_OK(cudaGetLastError());
@@ -1652,6 +1755,114 @@ extern "C" int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int
     c->merged_topk = k;
     c->merged_count = count;
     return 0;
+}
+
+// Peer exchange of one sharded find (see the block comment above tfp_find_ctx_p2p_export).
+// with_keys: the winning key rows travel too, so that the merged answer carries StoresFindResult.Keys.
+static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bool with_keys) {
+    tfp_store* s = c->st;
+    const unsigned int seq = c->x_seq + 1;
+    const size_t par_off = (size_t)(seq & 1u) * c->x_world * c->x_slot;
+    const size_t flags_off = xbuf_flags_offset(c->x_world, c->x_slot);
+    XchgParams x;
+    memset(&x, 0, sizeof(x));
+    x.world = c->x_world; x.me = c->x_me; x.seq = seq; x.raise = 1;
+    for (int r = 0; r < c->x_world; r++) {
+        x.slot[r] = c->x_peer[r] + par_off + (size_t)c->x_me * c->x_slot;
+        x.flag[r] = (unsigned int*)(c->x_peer[r] + flags_off) + c->x_me;
+    }
+    // records travel inside the scan kernel when nothing else has to be pushed before the words are raised
+    int rc = ctx_launch_locked(c, first, count, topk, with_keys ? nullptr : &x);
+    if (rc) return rc;     // argument errors: nothing was enqueued and seq was not consumed (same on every rank)
+    c->x_seq = seq;
+    const int k = c->last_topk, dim = s->dim;
+    const size_t rb = record_bytes(k);
+    const size_t keys_off = (rb * count + 255) & ~(size_t)255;
+    if (with_keys && s->n > 0) {
+        // winning rows go from the store straight into every rank's slot (stride topk, whatever this shard holds)
+        dim3 grid((unsigned)c->last_stride, (unsigned)count);
+        push_rows_kernel<<<grid, 256, 0, c->stream>>>(x, s->d_keys, dim, c->out_slots, c->out_n, c->last_stride, k, keys_off);
+        CU_OK(cudaGetLastError());
+        c->launches++;
+    }
+    if (!c->x_pushed) {
+        push_records_kernel<<<1, 256, 0, c->stream>>>(x, c->out_rec, rb * count);
+        CU_OK(cudaGetLastError());
+        c->launches++;
+    }
+    unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + flags_off);
+    for (int r = 0; r < c->x_world; r++) {
+        if (r == c->x_me) continue;
+        CUresult wr = g_wait32((CUstream)c->stream, (CUdeviceptr)(words + r), seq, CU_STREAM_WAIT_VALUE_GEQ);
+        if (wr != CUDA_SUCCESS) return fail(-7, "cuStreamWaitValue32 failed with CUresult %d", (int)wr);
+    }
+    const uint8_t* block = c->xbuf.as<uint8_t>() + par_off;
+    MergedLayout L(k, count);
+    const size_t want = L.total + (with_keys ? (size_t)count * k * dim * 4 : 0);
+    if (c->merged.reserve(want)) return -1;
+    rc = launch_merge(c, block, c->x_slot, rb, c->x_world, count, k);
+    if (rc) return rc;
+    c->merged_keys_dim = 0;
+    if (with_keys) {
+        uint8_t* m = c->merged.as<uint8_t>();
+        dim3 grid((unsigned)k, (unsigned)count);
+        gather_merged_rows_kernel<<<grid, 256, 0, c->stream>>>(block, c->x_slot, keys_off, dim, k, (const int*)(m + L.shard),
+                                                              (const int*)(m + L.index), (const int*)(m + L.n),
+                                                              (float*)(m + L.total));
+        CU_OK(cudaGetLastError());
+        c->launches++;
+        c->merged_keys_dim = dim;
+    }
+    return 0;
+}
+
+static int sharded_check(tfp_find_ctx* c, int topk, int world) {
+    // sizes depend on the arguments only, so every rank takes the same branch
+    const int64_t kk = std::min<int64_t>(std::max(topk, 1), (int64_t)1 << 26);
+    if ((int64_t)world * kk > 16384) return fail(2, "sharded find: world x topk = %lld exceeds 16384", (long long)world * kk);
+    (void)c;
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk) {
+    if (!c) return fail(2, "tfp_find_ctx_launch_sharded: ctx is NULL");
+    if (!c->nccl_comm && !c->x_ready)
+        return fail(2, "tfp_find_ctx_launch_sharded: call tfp_find_ctx_p2p_attach or tfp_find_ctx_comm_init first");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    const int world = c->x_ready ? c->x_world : c->comm_world;
+    if (sharded_check(c, topk, world)) return 2;
+    const size_t rb_want = record_bytes(std::max(topk, 1));
+    const bool p2p = c->x_ready && count > 0 && rb_want * (size_t)count <= c->x_slot;
+    if (!p2p && !c->nccl_comm)
+        return fail(2, "sharded find: %d records of %zu bytes exceed the peer-exchange slot (%zu bytes) and no NCCL communicator is set",
+                    count, rb_want, c->x_slot);
+    if (p2p) return p2p_launch_locked(c, first, count, topk, false);
+    int rc = ctx_launch_locked(c, first, count, topk);
+    if (rc) return rc;
+    const int k = c->last_topk;
+    const size_t rb = record_bytes(k);
+    if (c->gathered.reserve(rb * count * world)) return -1;
+    NCCL_OK(g_nccl.AllGather(c->out_rec, c->gathered.p, rb * count, /*ncclUint8*/ 1, c->nccl_comm, c->stream));
+    c->merged_keys_dim = 0;
+    return launch_merge(c, c->gathered.as<uint8_t>(), rb * count, rb, world, count, k);
+}
+
+extern "C" size_t tfp_p2p_slot_bytes_with_keys(int count, int topk, int dim) {
+    if (count < 1 || topk < 1 || dim < 1) return 0;
+    return ((record_bytes(topk) * (size_t)count + 255) & ~(size_t)255) + (size_t)count * topk * dim * 4;
+}
+
+extern "C" int tfp_find_ctx_launch_sharded_keys(tfp_find_ctx* c, int first, int count, int topk) {
+    if (!c) return fail(2, "tfp_find_ctx_launch_sharded_keys: ctx is NULL");
+    if (!c->x_ready) return fail(2, "tfp_find_ctx_launch_sharded_keys: call tfp_find_ctx_p2p_attach first");
+    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    if (set_device(c->st)) return -1;
+    if (sharded_check(c, topk, c->x_world)) return 2;
+    if (count < 1 || c->st->dim < 1 || tfp_p2p_slot_bytes_with_keys(count, std::max(topk, 1), c->st->dim) > c->x_slot)
+        return fail(2, "sharded find with keys: %d queries x top-%d x %d floats exceed the peer-exchange slot (%zu bytes)",
+                    count, topk, c->st->dim, c->x_slot);
+    return p2p_launch_locked(c, first, count, topk, true);
 }
 
 extern "C" int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk) {
@@ -1689,6 +1900,29 @@ extern "C" int tfp_find_ctx_download_merged(tfp_find_ctx* c, int* out_n, int64_t
         if (out_sims) memcpy(out_sims + o, h + L.sims + o * 4, (size_t)m * 4);
         if (out_shard) memcpy(out_shard + o, h + L.shard + o * 4, (size_t)m * 4);
         if (out_index) memcpy(out_index + o, h + L.index + o * 4, (size_t)m * 4);
+    }
+    return 0;
+}
+
+extern "C" int tfp_find_ctx_download_merged_keys(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims,
+                                                 float* out_keys) {
+    if (!c || c->merged_topk <= 0 || c->merged_keys_dim <= 0)
+        return fail(2, "tfp_find_ctx_download_merged_keys: no sharded launch with keys on this context");
+    if (set_device(c->st)) return -1;
+    const int k = c->merged_topk, count = c->merged_count, dim = c->merged_keys_dim;
+    MergedLayout L(k, count);
+    const size_t total = L.total + (size_t)count * k * dim * 4;
+    if (c->h_out.reserve(total)) return -1;
+    uint8_t* h = (uint8_t*)c->h_out.p;
+    CU_OK(cudaMemcpyAsync(h, c->merged.p, total, cudaMemcpyDeviceToHost, c->stream));   // ONE copy: n, ids, sims, rows
+    CU_OK(cudaStreamSynchronize(c->stream));
+    for (int q = 0; q < count; q++) {
+        const int m = ((const int*)(h + L.n))[q];
+        const size_t o = (size_t)q * k;
+        if (out_n) out_n[q] = m;
+        if (out_ids) memcpy(out_ids + o, h + L.ids + o * 8, (size_t)m * 8);
+        if (out_sims) memcpy(out_sims + o, h + L.sims + o * 4, (size_t)m * 4);
+        if (out_keys) memcpy(out_keys + o * dim, h + L.total + o * dim * 4, (size_t)m * dim * 4);
     }
     return 0;
 }

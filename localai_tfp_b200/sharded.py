@@ -103,6 +103,8 @@ class CudaShardOps:
         self.lanes = [_Lane(self.store, self.device) for _ in range(max(1, lanes))]
         self.ctx = self.lanes[0].ctx
         self.native = False
+        self.p2p = False
+        self._p2p_group = None
 
     def stream(self, lane: int = 0):
         """Everything a find enqueues (scan, collective, merge) is ordered on its lane's stream."""
@@ -169,6 +171,33 @@ class CudaShardOps:
             lane.ctx.comm_init(box[0], rank, world)
         self.native = True
 
+    def init_p2p(self, rank: int, world: int, group=None, slot_bytes: int = 1 << 20):
+        """Peer exchange: every lane's gather block is mapped into every rank (cudaIpc handles travel
+        over torch.distributed); after this find_merged() is ONE library call whose scan kernel pushes
+        the records to the peers over NVLink -- no collective call, no extra kernel per find."""
+        for lane in self.lanes:
+            mine = lane.ctx.p2p_export(world, slot_bytes)
+            handles = [None] * world
+            dist.all_gather_object(handles, mine, group=group)
+            lane.ctx.p2p_attach(b"".join(handles), rank, world)
+        dist.barrier(group=group)      # nobody launches before everybody has attached
+        self.native = True
+        self.p2p = True
+        self._p2p_group = group
+        self._p2p_slot = (slot_bytes + 255) & ~255
+
+    def find_host(self, q: np.ndarray, topk: int):
+        """One StoresFind end to end over the peer exchange: host query in, (ids, sims, key rows) out.
+        Returns None when the answer does not fit the exchange slot (the caller takes the general path)."""
+        if not self.p2p or self.store.key_len < 1:
+            return None
+        if self._L.tfp_p2p_slot_bytes_with_keys(1, topk, self.store.key_len) > self._p2p_slot:
+            return None
+        ctx = self.lanes[0].ctx
+        ctx.upload(q[None, :])
+        ctx.launch_sharded_keys(0, topk)
+        return ctx.download_merged_keys(self.store.key_len)
+
     def find_merged(self, qi: int, topk: int, lane: int = 0):
         """Native path: returns device tensors (sims, ids, shard, index, n) aliasing the lane's merged buffers."""
         ln = self.lanes[lane]
@@ -217,6 +246,13 @@ class CudaShardOps:
         return o_sims, o_ids, o_shard, o_index, o_n
 
     def close(self):
+        if self.p2p:
+            # unmap the peers' blocks everywhere, THEN free: an exported block must outlive its mappings
+            for ln in self.lanes:
+                ln.ctx.p2p_detach()
+            if dist.is_initialized():
+                dist.barrier(group=self._p2p_group)
+            self.p2p = False
         for ln in self.lanes:
             ln.alias.clear(); ln.bufs.clear()
             ln.ctx.close()
@@ -328,6 +364,11 @@ class ShardedStore:
             raise StoreError(f"Try to find key with length {len(q)} when existing length is {self.key_len}")
         if topk < 1:
             raise StoreError(f"opts.TopK = {topk}, must be >= 1")
+        if with_keys and self.world * int(topk) <= 16384 and hasattr(self.ops, "find_host"):
+            got = self.ops.find_host(q, int(topk))     # peer exchange: three library calls, one D2H copy
+            if got is not None:
+                ids_h, sims_h, keys_h = got
+                return [r.copy() for r in keys_h], [self.values.get(int(i)) for i in ids_h], sims_h
         self.ops.stage_queries(q[None, :])
         sims, ids, shard, index, n, g_keys = self.find_device(0, int(topk), with_keys)
         with self.ops.stream():

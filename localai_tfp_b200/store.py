@@ -305,6 +305,40 @@ class FindContext:
     def comm_share(self, owner: "FindContext"):
         self.store._check(self._L.tfp_find_ctx_comm_share(self._h, owner._h))
 
+    # -- sharded finds over peer memory (records pushed by the scan kernel itself) ---------------------
+    def p2p_export(self, world: int, slot_bytes: int) -> bytes:
+        """Allocate this rank's gather block; returns its 64-byte cudaIpc handle for the other ranks."""
+        buf = C.create_string_buffer(64)
+        self.store._check(self._L.tfp_find_ctx_p2p_export(self._h, world, slot_bytes, buf, 64))
+        return buf.raw
+
+    def p2p_attach(self, handles: bytes, rank: int, world: int):
+        """Map every rank's gather block (`handles`: world x 64 bytes, rank order)."""
+        assert len(handles) == 64 * world
+        buf = C.create_string_buffer(handles, len(handles))
+        self.store._check(self._L.tfp_find_ctx_p2p_attach(self._h, buf, rank, world))
+
+    def p2p_detach(self):
+        if self._h:
+            self.store._check(self._L.tfp_find_ctx_p2p_detach(self._h))
+
+    def launch_sharded_keys(self, qi: int, topk: int, count: int = 1):
+        """Sharded find whose merged answer carries the winners' key rows (peer exchange only)."""
+        self.store._check(self._L.tfp_find_ctx_launch_sharded_keys(self._h, qi, count, topk))
+        self._topk = topk
+        self._count = count
+
+    def download_merged_keys(self, dim: int):
+        """(ids, sims, keys) of a single-query launch_sharded_keys, or a list of them for a batch."""
+        k, cnt = self._topk, self._count
+        n = np.empty(cnt, np.int32)
+        ids = np.empty((cnt, k), np.int64); sims = np.empty((cnt, k), np.float32)
+        keys = np.empty((cnt, k, dim), np.float32)
+        self.store._check(self._L.tfp_find_ctx_download_merged_keys(self._h, _p(n, i32p), _p(ids, i64p), _p(sims, fp),
+                                                                    _p(keys, fp)))
+        out = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy(), keys[i, :n[i]].copy()) for i in range(cnt)]
+        return out[0] if cnt == 1 else out
+
     def launch_sharded(self, qi: int, topk: int, count: int = 1):
         self.store._check(self._L.tfp_find_ctx_launch_sharded_batch(self._h, qi, count, topk))
         self._topk = topk

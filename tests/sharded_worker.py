@@ -88,6 +88,95 @@ def native_path_matches(store, single, rank, world):
         assert np.array_equal(got_sims, want[2])
 
 
+def p2p_path_matches(single, rank, world):
+    """Sharded finds over peer memory (records pushed by the scan kernel, stream waits, merge) on a
+    store that never had an NCCL communicator inside the library: a result at all proves the peer
+    path ran; it must equal the torch.distributed path bit for bit, on both lanes, find after find."""
+    from conftest import make_keys
+    from localai_tfp_b200.sharded import CudaShardOps, ShardedStore
+    ops = CudaShardOps(rank, rank, lanes=2)
+    store = ShardedStore(ops, rank, world)
+    K = make_keys(400, 48, seed=5, normalized=True)
+    store.StoresSet(K[:300], [b"v%d" % i for i in range(300)])
+    ref_store = __import__("oracle.oracle", fromlist=["x"]).OracleStore()
+    ref_store.StoresSet(K[:300], [b"v%d" % i for i in range(300)])
+    Q = np.ascontiguousarray(np.concatenate([K[[1, 7, 150, 299, 33, 34, 350]], (K[5:6] * np.float32(2)).astype(np.float32)]))
+    ops.stage_queries(Q)
+
+    def torch_path(qi, k, lane):
+        sims, ids, shard, index, n, _ = store.find_device(qi, k, with_keys=False, lane=lane)
+        torch.cuda.synchronize()
+        m = int(n.item())
+        return tuple(t[:m].cpu().numpy().copy() for t in (ids, sims, shard, index))
+
+    ref = {(qi, k): torch_path(qi, k, 0) for qi in range(len(Q)) for k in (10, 1, 300)}
+    assert not ops.native
+    ops.init_p2p(rank, world, slot_bytes=64 << 10)
+    for rep in range(3):                      # parity buffers are reused every second find
+        for lane in (0, 1):
+            ctx = ops.lanes[lane].ctx
+            for qi in range(len(Q)):
+                for k in (10, 1, 300):
+                    ctx.launch_sharded(qi, k)
+                    got = ctx.download_merged()
+                    for a, b in zip(got, ref[(qi, k)]):
+                        assert np.array_equal(a, b), (rank, rep, lane, qi, k, a, b)
+    want = ref_store.StoresFind(Q[2], 10)
+    assert np.array_equal(ref[(2, 10)][1], want[2])
+    # the whole StoresFind (keys, values, similarities) through the peer exchange, against the oracle;
+    # k = 500 does not fit the 64 KiB slot with its key rows and takes the general path
+    for rep in range(2):
+        for qi in (0, 2, 6, 7):
+            for k in (10, 1, 300, 500):
+                a = store.StoresFind(Q[qi], k); b = ref_store.StoresFind(Q[qi], k)
+                assert np.array_equal(a[2], b[2]), (rank, qi, k, a[2], b[2])
+                assert a[1] == b[1], (rank, qi, k)
+                assert len(a[0]) == len(b[0]) and all(np.array_equal(x, y) for x, y in zip(a[0], b[0])), (rank, qi, k)
+    ops.stage_queries(Q)
+    # batches: 7 unit queries then one non-unit one (two paths -> several launches, the last one raises the words)
+    ctx = ops.lanes[0].ctx
+    for first, count in ((0, 8), (0, 3), (2, 5), (7, 1)):
+        ctx.launch_sharded(first, 10, count=count)
+        got = ctx.download_merged()
+        got = [got] if count == 1 else got
+        for j in range(count):
+            for a, b in zip(got[j], ref[(first + j, 10)]):
+                assert np.array_equal(a, b), (rank, first, count, j)
+    # both lanes in flight at once, no host wait in between
+    for i in range(20):
+        ops.lanes[i % 2].ctx.launch_sharded(i % len(Q), 10)
+    for lane, qi in ((0, 18 % len(Q)), (1, 19 % len(Q))):
+        got = ops.lanes[lane].ctx.download_merged()
+        for a, b in zip(got, ref[(qi, 10)]):
+            assert np.array_equal(a, b), (rank, lane, qi)
+    # a record too large for the slot and no NCCL communicator: a clean error on every rank, nothing enqueued
+    from localai_tfp_b200 import StoreError
+    try:
+        ctx.launch_sharded(0, 8000)
+        raise AssertionError("no error")
+    except StoreError as e:
+        assert "exceed the peer-exchange slot" in str(e), str(e)
+    ctx.launch_sharded(1, 10)                  # and the context still works
+    for a, b in zip(ctx.download_merged(), ref[(1, 10)]):
+        assert np.array_equal(a, b)
+    # a shard with no rows pushes its (empty) records through the stand-alone push kernel
+    store.StoresDelete(K[:300])
+    store.StoresSet(K[310:311], [b"one"])
+    ops.stage_queries(Q)
+    ctx.launch_sharded(0, 10)
+    ids, sims, shard, index = ctx.download_merged()
+    assert len(ids) == 1 and sims[0] == np.float32(ref_one(K[310], Q[0]))
+    store.close()
+
+
+def ref_one(k, q):
+    """fp32 index-order dot (store.go:327-339)."""
+    acc = np.float32(0)
+    for a, b in zip(k, q):
+        acc = np.float32(acc + np.float32(a * b))
+    return acc
+
+
 def run(rank, world, port, backend):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -108,6 +197,8 @@ def run(rank, world, port, backend):
         if backend == "nccl":
             native_path_matches(store, single, rank, world)
         store.close()
+        if backend == "nccl":
+            p2p_path_matches(single, rank, world)
         dist.barrier()
     finally:
         dist.destroy_process_group()
