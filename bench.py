@@ -198,7 +198,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     n_blocks = N_KEYS // BLOCK_ROWS
     b0, b1 = rank * n_blocks // world, (rank + 1) * n_blocks // world
     rows_local = (b1 - b0) * BLOCK_ROWS
-    ops = CudaShardOps(rank, local_rank, capacity_rows=rows_local, lanes=2)
+    ops = CudaShardOps(rank, local_rank, capacity_rows=rows_local, lanes=max(2, args.lanes))
     store = ops.store
     for b in range(b0, b1):
         blk = gen_block_torch(b, device)
@@ -237,11 +237,12 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     # Two finds are kept in flight (two find-contexts, alternating): the next query's CTAs fill the
     # SMs that the previous query's tail and merge leave idle and, at N > 1, its scan overlaps the
     # previous query's all-gather.  Every query is still its own scan (batch 1).
-    in_flight = 2 if QUERIES_PER_STEP == 1 else 1
-    ctx_b = ops.lanes[1].ctx
-    ctx_b.upload(Q)
-    ctx_b.sync()
-    stream_b = ops.lanes[1].stream
+    in_flight = max(2, args.lanes) if QUERIES_PER_STEP == 1 else 1
+    for ln in ops.lanes[1:]:
+        ln.ctx.upload(Q)
+        ln.ctx.sync()
+    lane_ctx = [ln.ctx for ln in ops.lanes]
+    side_streams = [ln.stream for ln in ops.lanes[1:]]
 
     batched = QUERIES_PER_STEP > 1
 
@@ -252,9 +253,9 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             else:
                 ctx.launch_sharded(0, TOPK, count=QUERIES_PER_STEP)
         elif world == 1:
-            (ctx if i % 2 == 0 else ctx_b).launch(i % N_QUERIES, 1, TOPK)
+            lane_ctx[i % in_flight].launch(i % N_QUERIES, 1, TOPK)
         else:
-            sharded.find_device(i % N_QUERIES, TOPK, with_keys=False, lane=i % 2)
+            sharded.find_device(i % N_QUERIES, TOPK, with_keys=False, lane=i % in_flight)
 
     def barrier():
         if world > 1:
@@ -262,7 +263,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         torch.cuda.synchronize(device)
 
     def launches_now():
-        return ctx.launch_count + (ctx_b.launch_count if ctx_b else 0)
+        return sum(c.launch_count for c in lane_ctx)
 
     # ---- device-resident throughput (`value`)
     with torch.cuda.stream(stream):
@@ -272,16 +273,16 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         launches0 = launches_now()
         clocks = ClockSampler(local_rank)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        eb = torch.cuda.Event()
         clocks.start()
         e0.record(stream)
-        if stream_b is not None:
-            stream_b.wait_event(e0)          # both streams start after e0 ...
+        for sb in side_streams:
+            sb.wait_event(e0)                # every lane's stream starts after e0 ...
         for i in range(args.steps):
             step_device(i)
-        if stream_b is not None:
-            eb.record(stream_b)
-            stream.wait_event(eb)            # ... and e1 follows the last kernel of either stream
+        for sb in side_streams:
+            eb = torch.cuda.Event()
+            eb.record(sb)
+            stream.wait_event(eb)            # ... and e1 follows the last kernel of every lane
         e1.record(stream)
         barrier()
         clk = clocks.stop()
@@ -433,12 +434,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=["c2", "target", "c3", "c4"], default="c2")
+    ap.add_argument("--lanes", type=int, default=0,
+                    help="single-query finds kept in flight per GPU (find contexts); default 2 on one GPU, 4 on several "
+                         "(a sharded find waits for its slowest peer: more finds in flight absorb the skew between ranks)")
     ap.add_argument("--exchange", choices=["p2p", "torch", "native", "native-per-lane"], default="p2p",
                     help="N>1: records pushed to the peers by the scan kernel (p2p), ncclAllGather inside libtfpstore "
                          "(native), or torch.distributed (torch)")
     args = ap.parse_args()
     select_workload(args.workload)
     args.warmup = max(args.warmup, 3)
+    if args.lanes <= 0:
+        args.lanes = 4 if int(os.environ.get("WORLD_SIZE", "1")) > 1 else 2
     os.environ.setdefault("NCCL_DEBUG", "WARN")     # keep NCCL's version banner off stdout: ONE JSON line is the contract
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
