@@ -156,6 +156,33 @@ class Backend:
                 context.abort(grpc.StatusCode.UNKNOWN, str(e))
         return wire.enc_find_result(ks, vs, sims)
 
+    def StoresFindBatch(self, request: bytes, context) -> bytes:
+        """Extension: many queries, one top-k, one reply.  Result i is exactly what
+        StoresFind(Keys[i], TopK) returns, errors included (the first failing key aborts the call)."""
+        keys, topk = wire.dec_find_batch(request)
+
+        def serve():
+            import numpy as np
+            st = self.store
+            if not keys:
+                raise StoreError("no keys to find")
+            for k in keys:                                             # store.go:480-486, per key
+                if len(k) != st.key_len:
+                    raise StoreError(f"Try to find key with length {len(k)} when existing length is {st.key_len}")
+            if topk < 1:
+                raise StoreError(f"opts.TopK = {topk}, must be >= 1")
+            if len(st) == 0:
+                return [([], [], np.zeros(0, np.float32)) for _ in keys]
+            out = []
+            for lo in range(0, len(keys), 256):                        # one library call per 256 queries
+                qs = np.stack(keys[lo:lo + 256]).astype(np.float32)
+                res, rows = st.find_batch(qs, topk, with_keys=True)
+                for i, (ids, sims) in enumerate(res):
+                    out.append(([rows[i, j, :].copy() for j in range(len(ids))],
+                                [st.values.get(int(x)) for x in ids], sims))
+            return out
+        return wire.enc_find_batch_result(self._run(context, serve))
+
 
 def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | None = None, batch_finds: bool = True):
     backend = Backend(device, snapshot)
@@ -163,7 +190,8 @@ def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | N
         backend.batcher = _FindBatcher(backend)
     methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,
                                                          response_serializer=_ident)
-               for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}
+               for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind",
+                            "StoresFindBatch")}
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=workers),
                          options=[("grpc.max_receive_message_length", wire.MAX_MESSAGE),
                                   ("grpc.max_send_message_length", wire.MAX_MESSAGE)])
@@ -182,7 +210,8 @@ class Client:
                                                        ("grpc.max_send_message_length", wire.MAX_MESSAGE)])
         self._m = {name: self.ch.unary_unary(f"/{SERVICE}/{name}", request_serializer=_ident,
                                              response_deserializer=_ident)
-                   for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind")}
+                   for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind",
+                                "StoresFindBatch")}
 
     def health(self) -> bytes:
         return wire.dec_reply(self._m["Health"](b"", timeout=10))
@@ -204,6 +233,9 @@ class Client:
 
     def find(self, key, topk: int):
         return wire.dec_find_result(self._m["StoresFind"](wire.enc_find(key, topk)))
+
+    def find_batch(self, keys, topk: int):
+        return wire.dec_find_batch_result(self._m["StoresFindBatch"](wire.enc_find_batch(keys, topk)))
 
     def close(self):
         self.ch.close()

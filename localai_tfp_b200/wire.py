@@ -4,6 +4,11 @@ Messages follow /root/reference/backend/backend.proto (proto3):
     StoresKey :69-71, StoresValue :73-75, StoresSetOptions :77-80, StoresDeleteOptions :82-84,
     StoresGetOptions :86-88, StoresGetResult :90-93, StoresFindOptions :95-98,
     StoresFindResult :100-104, Result :260-263, Reply :159-165, StatusResponse :360-369.
+One extension the reference does not have ("batch Find on the wire"):
+    message StoresFindBatchOptions { repeated StoresKey Keys = 1; int32 TopK = 2; }
+    message StoresFindBatchResult  { repeated StoresFindResult Results = 1; }
+    rpc StoresFindBatch(StoresFindBatchOptions) returns (StoresFindBatchResult) {}
+Result i is what StoresFind(Keys[i], TopK) returns; one client can feed the tensor-core path directly.
 `repeated float` is packed (one length-delimited run of little-endian fp32), which numpy reads and
 writes without a per-element loop; unpacked floats (legal on the wire) are accepted too.
 Unknown fields are skipped, as a protobuf decoder must.
@@ -147,6 +152,25 @@ def dec_find(data: bytes) -> Tuple[np.ndarray, int]:
     return key, topk
 
 
+def enc_find_batch(keys, topk: int) -> bytes:
+    out = b"".join(_ld(1, enc_key(k)) for k in keys)
+    if topk:
+        out += _varint((2 << 3) | 0) + _varint(int(topk))
+    return out
+
+
+def dec_find_batch(data: bytes) -> Tuple[List[np.ndarray], int]:
+    keys, topk = [], 0
+    for field, wt, v in _fields(memoryview(data)):
+        if field == 1 and wt == 2:
+            keys.append(dec_key(v))
+        elif field == 2 and wt == 0:
+            topk = v & 0xFFFFFFFF
+            if topk & 0x80000000:
+                topk -= 1 << 32      # int32
+    return keys, topk
+
+
 # ---- replies --------------------------------------------------------------------------------
 def enc_get_result(keys, values) -> bytes:
     return enc_set(keys, values)        # same field layout (Keys = 1, Values = 2)
@@ -176,6 +200,15 @@ def dec_find_result(data: bytes):
             sims.append(np.frombuffer(v, dtype="<f4"))
     s = np.concatenate(sims).astype(np.float32) if sims else np.zeros(0, np.float32)
     return keys, values, s
+
+
+def enc_find_batch_result(results) -> bytes:
+    """results: one (keys, values, sims) triple per query, in request order."""
+    return b"".join(_ld(1, enc_find_result(k, v, s)) for k, v, s in results)
+
+
+def dec_find_batch_result(data: bytes):
+    return [dec_find_result(bytes(v)) for field, wt, v in _fields(memoryview(data)) if field == 1 and wt == 2]
 
 
 def enc_result(message: str, success: bool) -> bytes:

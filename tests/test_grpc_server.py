@@ -179,3 +179,22 @@ def test_concurrent_finds_are_batched_onto_the_tensor_cores(tfp, oracle):
         [c.close() for c in clients]; c0.close()
     finally:
         server.stop(grace=0)
+
+
+def test_find_batch_rpc_equals_single_finds(client):
+    """StoresFindBatch: result i is exactly StoresFind(Keys[i], TopK), errors keep the reference's texts."""
+    from conftest import make_keys
+    K = make_keys(3000, 64, seed=21, normalized=True)
+    client.set(list(K), [b"v%d" % i for i in range(len(K))])
+    Q = [K[i] for i in (0, 5, 77, 1500, 2999)] + [(K[9] * f32(2)).astype(f32)]      # the last one takes the cosine path
+    for topk in (1, 10):
+        got = client.find_batch(Q, topk)
+        assert len(got) == len(Q)
+        for q, (ks, vs, sims) in zip(Q, got):
+            k1, v1, s1 = client.find(q, topk)
+            assert vs == v1 and np.array_equal(sims, s1) and all(np.array_equal(a, b) for a, b in zip(ks, k1))
+    for keys, topk, text in (([], 3, "no keys to find"), ([K[0][:5]], 3, "Try to find key with length 5 when existing length is 64"),
+                             ([K[0]], 0, "opts.TopK = 0, must be >= 1")):
+        with pytest.raises(grpc.RpcError) as e:
+            client.find_batch(keys, topk)
+        assert e.value.code() == grpc.StatusCode.UNKNOWN and e.value.details() == text

@@ -32,6 +32,9 @@ def build_messages():
     msg("StoresFindOptions", ("Key", 1, F.TYPE_MESSAGE, O, "StoresKey"), ("TopK", 2, F.TYPE_INT32, O, None))
     msg("StoresFindResult", ("Keys", 1, F.TYPE_MESSAGE, R, "StoresKey"), ("Values", 2, F.TYPE_MESSAGE, R, "StoresValue"),
         ("Similarities", 3, F.TYPE_FLOAT, R, None))
+    # the batch-find extension (not in the reference proto)
+    msg("StoresFindBatchOptions", ("Keys", 1, F.TYPE_MESSAGE, R, "StoresKey"), ("TopK", 2, F.TYPE_INT32, O, None))
+    msg("StoresFindBatchResult", ("Results", 1, F.TYPE_MESSAGE, R, "StoresFindResult"))
     msg("Result", ("message", 1, F.TYPE_STRING, O, None), ("success", 2, F.TYPE_BOOL, O, None))   # :260-263
     msg("Reply", ("message", 1, F.TYPE_BYTES, O, None), ("tokens", 2, F.TYPE_INT32, O, None))     # :159-165
     pool = descriptor_pool.DescriptorPool()
@@ -82,6 +85,25 @@ def test_find_result_and_get_result():
     assert list(parsed.Similarities) == [float(x) for x in sims] and [x.Bytes for x in parsed.Values] == VALS
     ref = PB["StoresGetResult"](Keys=[pb_key(k) for k in KEYS[:2]], Values=[PB["StoresValue"](Bytes=v) for v in VALS[:2]])
     assert wire.enc_get_result(KEYS[:2], VALS[:2]) == ref.SerializeToString()
+
+
+@pytest.mark.parametrize("topk", [1, 100, 0, -1])
+def test_find_batch_messages(topk):
+    ref = PB["StoresFindBatchOptions"](Keys=[pb_key(k) for k in KEYS], TopK=topk)
+    assert wire.enc_find_batch(KEYS, topk) == ref.SerializeToString()
+    keys, t = wire.dec_find_batch(ref.SerializeToString())
+    assert t == topk and all(np.array_equal(a, b) for a, b in zip(keys, KEYS))
+    sims = [np.array([1.0, 0.5], np.float32), np.zeros(0, np.float32), np.array([-1.0], np.float32)]
+    triples = [(KEYS[:2], VALS[:2], sims[0]), ([], [], sims[1]), (KEYS[4:5], VALS[4:5], sims[2])]
+    ref = PB["StoresFindBatchResult"](Results=[
+        PB["StoresFindResult"](Keys=[pb_key(k) for k in ks], Values=[PB["StoresValue"](Bytes=v) for v in vs],
+                               Similarities=[float(x) for x in sm]) for ks, vs, sm in triples])
+    data = wire.enc_find_batch_result(triples)
+    assert data == ref.SerializeToString()
+    back = wire.dec_find_batch_result(data)
+    assert len(back) == 3 and back[1][0] == [] and back[1][1] == [] and len(back[1][2]) == 0
+    for (ks, vs, sm), (k2, v2, s2) in zip(triples, back):
+        assert v2 == list(vs) and np.array_equal(s2, sm) and all(np.array_equal(a, b) for a, b in zip(k2, ks))
 
 
 def test_empty_messages():
