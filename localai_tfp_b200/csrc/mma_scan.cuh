@@ -49,7 +49,7 @@ constexpr int kMmaThreads = 384;
 constexpr int kMmaStages3 = 4;          // TERMS = 3: stages of 48 KiB at nq = 256
 constexpr int kMmaStages1 = 8;          // TERMS = 1: stages of 24 KiB
 constexpr int kMmaStagesMax = 24;        // small batches have small query boxes: more key tiles in flight
-constexpr int kMmaHitQueue = 256;       // per epilogue warp: hits staged in shared memory, flushed once per tile
+constexpr int kMmaHitQueue = 128;       // per epilogue warp (8 of them): hits staged in shared memory, flushed once per tile
 constexpr int kMmaRescoreMax = 1024;    // TERMS = 1: rows re-scored per query at most (else exact re-run)
 constexpr int kMmaBoxCols = 16;         // floats per row per stage (64 B, 64-byte swizzle): small stages, deep ring
 constexpr int kMmaMaxNQ = 256;         // queries per pass == UMMA N (multiple of 16)
@@ -101,6 +101,62 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// ---- CTA pair (cta_group::2): two SMs of one TPC run ONE M = 256 MMA; each holds its own 128 key rows
+// (and their accumulator, in its own TMEM) and HALF of the query tile, which the tensor core reads from
+// both shared memories -- so every SM pulls half the query bytes from L2 that a lone CTA would. ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory location in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// the same-offset mbarrier of BOTH CTAs of the pair arrives when the MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+// TMA load whose completion is signalled on an mbarrier that may live in the peer CTA (cluster address)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1,
+                                                 uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+        "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
+// One lane of a fully active warp (the rest of the warp keeps executing the same, warp-uniform code)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xFFFFFFFF;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -127,8 +183,8 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, bool wide) {
     return wide ? umma_desc_sw128(smem_addr) : umma_desc_sw64(smem_addr);
 }
 // kind::tf32, fp32 accumulator, both operands K-major, M = 128, N = n
-__host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+__host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int n, int m = 128) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 // 16-byte shared load that is re-issued every time (other warps update these words)
 __device__ __forceinline__ float4 __uint4_as_float4(uint4 u) {
@@ -161,34 +217,44 @@ __global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int 
 // TMA issue and tcgen05.commit is then paid half as often, which is what small batches are bound by);
 // the 3xTF32 filter, with four tiles per stage, stays at 16 columns to keep four stages.
 __host__ __device__ inline int mma_box_cols(int terms) { return terms == 3 ? 16 : 32; }
-__host__ __device__ inline size_t mma_stage_bytes(int nqp, int terms) {
+// pair: a CTA of a cta_group::2 pair stages only its half of the query tile
+__host__ __device__ inline size_t mma_stage_bytes(int nqp, int terms, bool pair = false) {
     const size_t row = (size_t)mma_box_cols(terms) * 4;
+    if (pair) return (size_t)kMmaRows * row + (size_t)(nqp / 2) * row;
     return terms == 3 ? 2 * (size_t)kMmaRows * row + 2 * (size_t)nqp * row : (size_t)kMmaRows * row + (size_t)nqp * row;
 }
 __host__ __device__ inline size_t mma_fixed_smem_bytes() {
-    return (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 + 4 * (size_t)kMmaHitQueue * 16 + 16;
+    return (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 + 8 * (size_t)kMmaHitQueue * 16 + 32;
 }
 // as many stages as fit (at least the pipeline's nominal depth at nq = 256, at most kMmaStagesMax)
-__host__ __device__ inline int mma_stage_count(int nqp, int terms, size_t max_smem) {
+__host__ __device__ inline int mma_stage_count(int nqp, int terms, size_t max_smem, bool pair = false) {
     const size_t room = max_smem > mma_fixed_smem_bytes() ? max_smem - mma_fixed_smem_bytes() : 0;
-    int n = (int)(room / mma_stage_bytes(nqp, terms));
+    int n = (int)(room / mma_stage_bytes(nqp, terms, pair));
     return n > kMmaStagesMax ? kMmaStagesMax : n;
 }
-__host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms, int stages) {
-    return stages * mma_stage_bytes(nqp, terms) + mma_fixed_smem_bytes();
+__host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms, int stages, bool pair = false) {
+    return stages * mma_stage_bytes(nqp, terms, pair) + mma_fixed_smem_bytes();
 }
 
-template <int TERMS>
+// PAIR: launched as clusters of two CTAs (cta_group::2, TERMS = 1 only).  CTA r of a pair owns key tile
+// blockIdx.x + i * gridDim.x like a lone CTA and stages query rows [r nqp/2, (r+1) nqp/2); the even CTA
+// ("leader") issues every MMA for both.  Barriers: full[] lives on the leader and counts the bytes of both
+// CTAs' TMA loads; empty[] / acc_full[] are signalled in both CTAs by one multicast commit; acc_empty[] on
+// the leader collects the epilogue warps of both CTAs.  Both CTAs walk the same number of tiles (a tile
+// index past the end is all padding), so the pair stays in step to the last barrier.
+template <int TERMS, bool PAIR>
 __global__ void __launch_bounds__(kMmaThreads, 1)
 mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_q, const MmaParams p) {
+    static_assert(!(PAIR && TERMS == 3), "the CTA-pair variant exists for the single-TF32 filter only");
     const int kMmaStages = p.n_stages;
+    const uint32_t crank = PAIR ? cluster_ctarank() : 0u;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int bc = p.box_cols;                                   // floats per row per stage
     const size_t a_bytes = (size_t)kMmaRows * bc * 4;
-    const size_t b_bytes = (size_t)p.nqp * bc * 4;
+    const size_t b_bytes = (size_t)(PAIR ? p.nqp / 2 : p.nqp) * bc * 4;   // query bytes THIS CTA stages per chunk
     const bool wide = bc == 32;
-    const size_t stage_bytes = mma_stage_bytes(p.nqp, TERMS);
+    const size_t stage_bytes = mma_stage_bytes(p.nqp, TERMS, PAIR);
     // TERMS = 3: [a_hi | a_lo | b_hi | b_lo];  TERMS = 1: [a | b]
     auto a_hi = [&](int s) { return base + s * stage_bytes; };
     auto a_lo = [&](int s) { return base + s * stage_bytes + a_bytes; };
@@ -206,12 +272,15 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
     unsigned int* lb = tau + kMmaMaxNQ;                       // [kMmaMaxNQ] this CTA's best score per query
     float* tau_f = (float*)(lb + kMmaMaxNQ);                  // [kMmaMaxNQ] tau as a float (-inf = admit everything)
     float* lb_f = tau_f + kMmaMaxNQ;                          // [kMmaMaxNQ] lb as a float (may lag behind lb: only a hint)
-    uint4* hitq = (uint4*)(lb_f + kMmaMaxNQ);                 // [4][kMmaHitQueue] (query, row, score bits): staged hits
-    int* hitn = (int*)(hitq + 4 * kMmaHitQueue);              // [4] entries staged per epilogue warp
+    uint4* hitq = (uint4*)(lb_f + kMmaMaxNQ);                 // [8][kMmaHitQueue] (query, row, score bits): staged hits
+    int* hitn = (int*)(hitq + 8 * kMmaHitQueue);              // [8] entries staged per epilogue warp
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t n_tiles_all = (p.n_rows + kMmaRows - 1) / kMmaRows;
     const uint32_t n_tiles = p.mode == 0 ? (n_tiles_all < gridDim.x ? n_tiles_all : gridDim.x) : n_tiles_all;
+    // tiles this CTA walks; a pair walks as many as its even CTA (the odd one may end on a padding tile)
+    const uint32_t first_tile = PAIR ? (blockIdx.x & ~1u) : blockIdx.x;
+    const uint32_t n_iters = first_tile < n_tiles ? (n_tiles - first_tile + gridDim.x - 1) / gridDim.x : 0u;
     const uint32_t tmem_cols = 2 * p.nqp <= 32 ? 32 : (2 * p.nqp <= 64 ? 64 : (2 * p.nqp <= 128 ? 128 : (2 * p.nqp <= 256 ? 256 : 512)));
 
     if (tid == 0) {
@@ -222,12 +291,12 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         }
         for (int s = 0; s < 2; s++) {
             mbar_init(acc_full + s, 1);    // tcgen05.commit
-            mbar_init(acc_empty + s, 4);   // one arrive per epilogue warp
+            mbar_init(acc_empty + s, (TERMS == 1 ? 8 : 4) * (PAIR ? 2 : 1));   // one arrive per epilogue warp (of both CTAs of a pair)
         }
         fence_mbar_init();
         flags[0] = 0;
         flags[1] = p.mode == 0 ? 1 : 0;    // the bound-only pass needs no thresholds
-        hitn[0] = hitn[1] = hitn[2] = hitn[3] = 0;
+        for (int i = 0; i < 8; i++) hitn[i] = 0;
     }
     for (int i = tid; i < kMmaMaxNQ; i += kMmaThreads) {
         tau[i] = 0u;
@@ -236,39 +305,63 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         lb[i] = p.mode == 1 ? p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + i] : 0u;
         lb_f[i] = lb[i] ? order_to_score(lb[i]) : -INFINITY;
     }
-    if (warp == 1) tmem_alloc(tmem_base_s, tmem_cols);
+    if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair(tmem_base_s, tmem_cols); else tmem_alloc(tmem_base_s, tmem_cols); }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // the peer's barriers are initialised too
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_s;
 
     if (warp == 0) {
         // ============================ TMA producer ============================
-        if (lane == 0) {
+        // (whole warp on uniform values, one elected lane issues -- see the MMA issuer)
+        if (elect_one()) {
             tma_prefetch_desc(&tmap_k);
             tma_prefetch_desc(&tmap_q);
-            const uint64_t pol_stream = l2_policy_evict_first();
-            const uint64_t pol_keep = l2_policy_evict_normal();
-            int stage = 0; uint32_t phase = 0;
-            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                for (int c = 0; c < p.n_chunks; c++) {
-                    mbar_wait(empty + stage, phase ^ 1u);
-                    mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + (TERMS == 3 ? 2 : 1) * b_bytes));
-                    tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * bc, (int)(tile * kMmaRows), pol_stream);
-                    tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * bc, 0, pol_keep);
-                    if constexpr (TERMS == 3)
-                        tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * bc, p.nqp, pol_keep);
-                    if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
+        }
+        __syncwarp();
+        const uint64_t pol_stream = l2_policy_evict_first();
+        const uint64_t pol_keep = l2_policy_evict_normal();
+        const uint32_t full0 = PAIR ? mapa_u32(smem_u32(full), 0) : 0u;   // the leader's full[0], as a cluster address
+        int stage = 0; uint32_t phase = 0;
+        for (uint32_t it = 0; it < n_iters; it++) {
+            const uint32_t tile = blockIdx.x + it * gridDim.x;
+            for (int c = 0; c < p.n_chunks; c++) {
+                mbar_wait(empty + stage, phase ^ 1u);
+                if (elect_one()) {
+                    if constexpr (PAIR) {
+                        // the leader's barrier counts both CTAs' bytes; the peer only adds its transfers to it
+                        if (crank == 0) mbar_arrive_expect_tx(full + stage, (uint32_t)(2 * (a_bytes + b_bytes)));
+                        const uint32_t bar = full0 + (uint32_t)stage * 8u;
+                        tma_load_2d_pair(a_hi(stage), &tmap_k, bar, c * bc, (int)(tile * kMmaRows), pol_stream);
+                        tma_load_2d_pair(b_hi(stage), &tmap_q, bar, c * bc, (int)(crank * (uint32_t)(p.nqp / 2)), pol_keep);
+                    } else {
+                        mbar_arrive_expect_tx(full + stage, (uint32_t)(a_bytes + (TERMS == 3 ? 2 : 1) * b_bytes));
+                        tma_load_2d(a_hi(stage), &tmap_k, full + stage, c * bc, (int)(tile * kMmaRows), pol_stream);
+                        tma_load_2d(b_hi(stage), &tmap_q, full + stage, c * bc, 0, pol_keep);
+                        if constexpr (TERMS == 3)
+                            tma_load_2d(b_lo(stage), &tmap_q, full + stage, c * bc, p.nqp, pol_keep);
+                    }
                 }
+                __syncwarp();
+                if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
         // ============================ MMA issuer ============================
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_tf32(p.nqp);
+        // The WHOLE warp walks the loop on warp-uniform values and one elected lane issues: descriptors then
+        // live in uniform registers and an MMA costs a handful of instructions.  (Issuing from inside a
+        // `lane == 0` branch made the compiler wrap every tcgen05 instruction in a uniformity loop: ~35
+        // instructions per MMA, and the issuing thread -- not the tensor core -- set the kernel's pace.)
+        if (crank == 0) {
+            constexpr int kSteps = (TERMS == 3 ? 16 : 32) / 8;       // UMMA K = 8 TF32 = 32 bytes along the swizzled row
+            const uint32_t idesc = umma_idesc_tf32(p.nqp, PAIR ? 256 : 128);
+            // a stage's descriptors are stage 0's plus a multiple of the stage size: the address field counts 16-byte units
+            const uint64_t a_desc0 = umma_desc(smem_u32(a_hi(0)), wide), b_desc0 = umma_desc(smem_u32(b_hi(0)), wide);
+            const uint64_t stage_step = (uint64_t)(stage_bytes >> 4);
+            const uint64_t a_lo_off = (uint64_t)(a_bytes >> 4), b_lo_off = (uint64_t)(b_bytes >> 4);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            for (uint32_t it = 0; it < n_iters; it++) {
                 mbar_wait(acc_empty + acc, acc_phase ^ 1u);     // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.nqp);
@@ -276,21 +369,29 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                     mbar_wait(full + stage, phase);             // key and query boxes landed
                     if constexpr (TERMS == 3) mbar_wait(conv + stage, phase);   // hi / lo key tiles written and fenced
                     tc_fence_after();
-                    const uint32_t ah = smem_u32(a_hi(stage)), bh = smem_u32(b_hi(stage));
-                    for (int k = 0; k < bc / 8; k++) {          // UMMA K = 8 TF32 = 32 bytes along the swizzled row
-                        if (p.debug & 2) break;
-                        const uint32_t off = (uint32_t)k * 32u;
-                        umma_tf32(d_tmem, umma_desc(ah + off, wide), umma_desc(bh + off, wide), idesc, (c | k) != 0);
-                        if constexpr (TERMS == 3) {
-                            const uint32_t al = smem_u32(a_lo(stage)), bl = smem_u32(b_lo(stage));
-                            umma_tf32(d_tmem, umma_desc(ah + off, wide), umma_desc(bl + off, wide), idesc, 1u);
-                            umma_tf32(d_tmem, umma_desc(al + off, wide), umma_desc(bh + off, wide), idesc, 1u);
+                    if (elect_one()) {
+                        const uint64_t ad = a_desc0 + (uint64_t)stage * stage_step, bd = b_desc0 + (uint64_t)stage * stage_step;
+                        if (!(p.debug & 2)) {
+#pragma unroll
+                            for (int k = 0; k < kSteps; k++) {
+                                const uint64_t off = (uint64_t)(2 * k);     // 32 bytes
+                                if constexpr (PAIR) umma_tf32_pair(d_tmem, ad + off, bd + off, idesc, (c | k) != 0);
+                                else umma_tf32(d_tmem, ad + off, bd + off, idesc, (c | k) != 0);
+                                if constexpr (TERMS == 3) {
+                                    umma_tf32(d_tmem, ad + off, bd + b_lo_off + off, idesc, 1u);
+                                    umma_tf32(d_tmem, ad + a_lo_off + off, bd + off, idesc, 1u);
+                                }
+                            }
                         }
+                        if constexpr (PAIR) umma_commit_pair(empty + stage); else umma_commit(empty + stage);   // stage is free once these MMAs retire
                     }
-                    umma_commit(empty + stage);                 // stage is free once these MMAs retire
+                    __syncwarp();
                     if (++stage == kMmaStages) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(acc_full + acc);                    // accumulator complete
+                if (elect_one()) {
+                    if constexpr (PAIR) umma_commit_pair(acc_full + acc); else umma_commit(acc_full + acc);     // accumulator complete
+                }
+                __syncwarp();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
         }
@@ -323,10 +424,39 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                 __nanosleep((unsigned)p.refresh_ns);
             }
         }
-    } else if (warp >= 4 && warp < 8) {
+    } else if (warp >= 4 && (warp < 8 || TERMS == 1)) {
         // ============================ epilogue ============================
+        // Warps 4-7, and with the single-TF32 filter warps 8-11 too (they have nothing to convert): warp w may
+        // read TMEM lanes 32 (w % 4) .. +31, so the two groups take alternate 32-query column blocks of the same rows.
+        constexpr int kEpiWarps = TERMS == 1 ? 8 : 4;
         const int wq = warp & 3;                                // TMEM lane quadrant this warp may read
+        const int ew = warp - 4;                                // epilogue warp index: its hit queue
+        const int cgrp = ew >> 2;                               // which alternate column blocks
         const int row_in_tile = wq * 32 + lane;
+        // One element cleared a threshold (rare once the bounds have tightened): update this CTA's best for the
+        // query and, on the full pass, stage the candidate.  Runs only for rows whose mask bit is set, after the
+        // branch-free pass over the block; all its state is addressed as shared memory (no generic atomics).
+        int* const my_hitn = hitn + ew;
+        uint4* const my_hitq = hitq + ew * kMmaHitQueue;
+        auto on_hit = [&](int q, uint32_t row, float sc) {
+            if (q >= p.nq) return;
+            const unsigned int o = score_to_order(sc);
+            if (o > ((volatile unsigned int*)lb)[q]) {
+                const unsigned int old = atomicMax(lb + q, o);
+                ((volatile float*)lb_f)[q] = order_to_score(old > o ? old : o);
+            }
+            if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
+                // A global atomic per hit would stall the warp ~1 us each time (its result is needed for the
+                // store): stage the hit, the warp flushes all of them after the tile.
+                const int hp = atomicAdd(my_hitn, 1);
+                if (hp < kMmaHitQueue) {
+                    my_hitq[hp] = make_uint4((unsigned)q, row, __float_as_uint(sc), 0u);
+                } else {   // queue full (thresholds still loose): the slow path, rare
+                    const unsigned int pos = atomicAdd(p.cand_cnt + q, 1u);
+                    if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)q * kMmaCandCap + pos] = pack_cand(sc, row);
+                }
+            }
+        };
         {   // first thresholds are in place (bounded wait: a protocol bug must trap, not hang)
             const long long t0 = clock64();
             while (flags[1] == 0) {
@@ -335,82 +465,71 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
             }
         }
         int acc = 0; uint32_t acc_phase = 0;
-        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (uint32_t it = 0; it < n_iters; it++) {
+            const uint32_t tile = blockIdx.x + it * gridDim.x;
             const uint32_t row = tile * kMmaRows + (uint32_t)row_in_tile;
             const bool valid = row < p.n_rows;
             const float inv = (p.f64 && valid) ? (float)(1.0 / __ldg(p.knorm + row)) : 1.0f;
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
-            for (int col0 = 0; col0 < p.nqp; col0 += 32) {
+            for (int col0 = cgrp * 32; col0 < p.nqp; col0 += 32 * (kEpiWarps / 4)) {
                 uint32_t v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(acc * p.nqp + col0), v);
                 // Thresholds and bests of these 32 queries as floats: 16 vector loads up front, then two float
-                // compares per element.  Only an element that passes one of them (rare) takes the slow path,
-                // which works on the exact orderable words.  A stale float is harmless: a lower threshold or
-                // best only sends a few more elements down the slow path.
+                // compares per element folded into one bit of a mask -- no branch per element.  Only a row with
+                // a bit set (rare once the bounds are tight) walks its bits; that path works on the exact
+                // orderable words.  A stale float is harmless: a lower threshold or best only sets a few more bits.
                 float4 tq[8], bq[8];
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
                     tq[i] = __uint4_as_float4(lds_volatile_v4((const unsigned int*)tau_f + col0 + 4 * i));
                     bq[i] = __uint4_as_float4(lds_volatile_v4((const unsigned int*)lb_f + col0 + 4 * i));
                 }
-                if (valid && !(p.debug & 1)) {
+                uint32_t mask = 0u;
 #pragma unroll
-                    for (int j = 0; j < 32; j++) {
-                        const float tj = j % 4 == 0 ? tq[j / 4].x : (j % 4 == 1 ? tq[j / 4].y : (j % 4 == 2 ? tq[j / 4].z : tq[j / 4].w));
-                        const float bj = j % 4 == 0 ? bq[j / 4].x : (j % 4 == 1 ? bq[j / 4].y : (j % 4 == 2 ? bq[j / 4].z : bq[j / 4].w));
-                        const float s = __uint_as_float(v[j]) * inv;
-                        if (s >= tj || s > bj) {                     // false for NaN
-                            const int q = col0 + j;
-                            if (q < p.nq) {
-                                const unsigned int o = score_to_order(s);
-                                if (o > ((volatile unsigned int*)lb)[q]) {
-                                    const unsigned int old = atomicMax(lb + q, o);
-                                    ((volatile float*)lb_f)[q] = order_to_score(old > o ? old : o);
-                                }
-                                if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
-                                    // A global atomic per hit would stall the warp ~1 us each time (its result
-                                    // is needed for the store): stage the hit, flush all of them after the tile.
-                                    const int hp = atomicAdd(hitn + wq, 1);
-                                    if (hp < kMmaHitQueue) {
-                                        hitq[wq * kMmaHitQueue + hp] = make_uint4((unsigned)q, row, __float_as_uint(s), 0u);
-                                    } else {   // queue full (thresholds still loose): the slow path, rare
-                                        const unsigned int pos = atomicAdd(p.cand_cnt + q, 1u);
-                                        if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)q * kMmaCandCap + pos] = pack_cand(s, row);
-                                    }
-                                }
-                            }
-                        }
-                    }
+                for (int j = 0; j < 32; j++) {
+                    const float tj = j % 4 == 0 ? tq[j / 4].x : (j % 4 == 1 ? tq[j / 4].y : (j % 4 == 2 ? tq[j / 4].z : tq[j / 4].w));
+                    const float bj = j % 4 == 0 ? bq[j / 4].x : (j % 4 == 1 ? bq[j / 4].y : (j % 4 == 2 ? bq[j / 4].z : bq[j / 4].w));
+                    const float sj = __uint_as_float(v[j]) * inv;
+                    mask |= ((sj >= tj) | (sj > bj)) ? (1u << j) : 0u;      // both false for NaN
+                }
+                if (!valid || (p.debug & 1)) mask = 0u;
+                if (mask) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++)
+                        if (mask & (1u << j)) on_hit(col0 + j, row, __uint_as_float(v[j]) * inv);
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(acc_empty + acc);        // the tensor core may refill this accumulator now
+            if (lane == 0) {                                    // the tensor core may refill this accumulator now
+                if (PAIR && crank != 0) mbar_arrive_cluster(mapa_u32(smem_u32(acc_empty + acc), 0));
+                else mbar_arrive(acc_empty + acc);
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             // flush the staged hits: 32 global atomics in flight at a time instead of one
             {
-                int nh = *((volatile int*)(hitn + wq));
+                int nh = *((volatile int*)(hitn + ew));
                 nh = nh < kMmaHitQueue ? nh : kMmaHitQueue;
                 for (int i = lane; i < nh; i += 32) {
-                    const uint4 e = hitq[wq * kMmaHitQueue + i];
+                    const uint4 e = hitq[ew * kMmaHitQueue + i];
                     const unsigned int pos = atomicAdd(p.cand_cnt + e.x, 1u);
                     if (pos < (unsigned)kMmaCandCap) p.cand[(size_t)e.x * kMmaCandCap + pos] = pack_cand(__uint_as_float(e.z), e.y);
                 }
                 __syncwarp();
-                if (lane == 0) hitn[wq] = 0;
+                if (lane == 0) hitn[ew] = 0;
                 __syncwarp();
             }
         }
         // publish this CTA's bests (the bound-only pass exists to produce exactly this)
-        named_bar_sync(2, 128);
-        for (int q = tid - 128; q < p.nq; q += 128) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
+        named_bar_sync(2, kEpiWarps * 32);
+        for (int q = tid - 128; q < p.nq; q += kEpiWarps * 32) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
         if (tid == 128) flags[0] = 1;
     } else if (TERMS == 3 && warp >= 8) {
         // ============================ converters (3xTF32 only) ============================
         const int ct = tid - 256;                               // 0..127
         int stage = 0; uint32_t phase = 0;
-        for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (uint32_t it = 0; it < n_iters; it++) {
             for (int c = 0; c < p.n_chunks; c++) {
                 mbar_wait(full + stage, phase);
                 float4* hi4 = reinterpret_cast<float4*>(a_hi(stage));
@@ -434,9 +553,9 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
     }
     // ---- teardown: every MMA has retired (the epilogue consumed the last accumulator) ----
     tc_fence_before();
-    __syncthreads();
+    if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // neither CTA of a pair leaves while the other may touch it
     tc_fence_after();
-    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+    if (warp == 1) { if constexpr (PAIR) tmem_dealloc_pair(tmem_base, tmem_cols); else tmem_dealloc(tmem_base, tmem_cols); }
 }
 
 // ---- finalize: per query, best k+margin candidates by approximate score, exact re-score, top-k ----

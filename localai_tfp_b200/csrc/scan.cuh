@@ -271,8 +271,9 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
                                               uint64_t* big_buf, int big_cap) {
     const int k = p.topk;
     // 1. publish this CTA's survivors: the buffered words that reach the bound.  With the grid-wide
-    // bound in place that is a handful of words, so the usual case needs no sort at all: count them,
-    // and if they fit (<= k) copy them out unsorted (the last CTA orders everything anyway).
+    // bound in place that is a handful of words, so the usual case needs no sort at all: every thread
+    // copies its qualifying words out unsorted (the last CTA orders everything anyway) and the count
+    // decides afterwards whether they fitted.
     for (int q = 0; q < NQ; q++) {
         uint64_t* dst = p.part + ((size_t)blockIdx.x * kMaxNQ + q) * k;
         bool fast = sel[q].m_local == 1;      // larger m publishes its m-th best from the sorted buffer
@@ -281,32 +282,18 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             const unsigned long long bound = *sel[q].tau;
             if (tid == 0) *flag = 0;
             named_bar_sync(kSelBarrier, kSelThreads);
-            int mine = 0;
-            for (int i = tid; i < n; i += kSelThreads) mine += (sel[q].buf[i] >= bound) ? 1 : 0;
-            if (mine) atomicAdd(flag, mine);
+            for (int i = tid; i < n; i += kSelThreads) {
+                const uint64_t c = sel[q].buf[i];
+                if (c >= bound) {
+                    const int pos = atomicAdd(flag, 1);
+                    if (pos < k) dst[pos] = c;
+                }
+            }
             named_bar_sync(kSelBarrier, kSelThreads);
             const int total = *((volatile int*)flag);
-            named_bar_sync(kSelBarrier, kSelThreads);
+            named_bar_sync(kSelBarrier, kSelThreads);   // everyone has read the count before the next query resets it
             if (total <= k) {
-                if (tid == 0) *flag = 0;
-                named_bar_sync(kSelBarrier, kSelThreads);
-                for (int i = tid; i < n; i += kSelThreads) {
-                    const uint64_t c = sel[q].buf[i];
-                    if (c >= bound) dst[atomicAdd(flag, 1)] = c;
-                }
-                named_bar_sync(kSelBarrier, kSelThreads);
                 if (tid == 0) p.part_cnt[blockIdx.x * kMaxNQ + q] = total;
-                // the last CTA continues from its own buffer: compact it the same way
-                if (tid == 0) *flag = 0;
-                named_bar_sync(kSelBarrier, kSelThreads);
-                uint64_t keep[16];   // cap / kSelThreads <= 16 entries per thread
-                int nk = 0;
-                for (int i = tid; i < n; i += kSelThreads) { const uint64_t c = sel[q].buf[i]; if (c >= bound && nk < 16) keep[nk++] = c; }
-                named_bar_sync(kSelBarrier, kSelThreads);
-                for (int j = 0; j < nk; j++) sel[q].buf[atomicAdd(flag, 1)] = keep[j];
-                named_bar_sync(kSelBarrier, kSelThreads);
-                if (tid == 0) *sel[q].cnt = total;
-                named_bar_sync(kSelBarrier, kSelThreads);
             } else {
                 fast = false;
             }
@@ -337,26 +324,22 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
     if (*flag == 0) return;
     __threadfence();
 
-    // 2. last CTA: merge every CTA's survivors (own list is already in sel[q].buf).
-    // Every CTA's final bounds are visible now: fold them in.  tau may then BE another CTA's row
-    // (it travelled through gtau / lbest), and that row is part of the answer: admit words
-    // >= tau, i.e. > tau - 1.  No word is offered twice (own rows are not re-offered), so
-    // equality can only be that one row.
-    if (p.lbest && tid < 32 && big_buf && big_cap >= (int)gridDim.x) {
-        for (int q = 0; q < NQ; q++) {
-            unsigned long long v = lbest_rth(p, q, tid, (unsigned long long*)big_buf);
-            if (tid == 0 && v > *sel[q].tau) *sel[q].tau = v;
-        }
+    // 2. last CTA: merge every CTA's published survivors, its own included (they are in `part` like
+    // everybody's).  Its tau is a valid lower bound of the k-th best and may BE a row of the answer
+    // (its own k-th best, or another CTA's row that travelled through gtau / lbest): admit words
+    // >= tau, i.e. > tau - 1.  Every row is published by exactly one CTA, so nothing is offered twice.
+    if (tid < NQ) {
+        unsigned long long t = *sel[tid].tau;
+        *sel[tid].tau = t ? t - 1 : 0ull;
+        *sel[tid].cnt = 0;
     }
-    named_bar_sync(kSelBarrier, kSelThreads);
-    if (tid < NQ) { unsigned long long t = *sel[tid].tau; *sel[tid].tau = t ? t - 1 : 0ull; }
     named_bar_sync(kSelBarrier, kSelThreads);
     const int grid = (int)gridDim.x;
     for (int q = 0; q < NQ; q++) {
         // Flatten the other CTAs' lists: pref[b] = number of survivors in CTAs < b.  All loads of
         // one round are independent, so the merge costs a few L2 round trips, not one per CTA.
         for (int b = tid; b < grid; b += kSelThreads)
-            pref[b + 1] = (b == (int)blockIdx.x) ? 0 : __ldcg(p.part_cnt + b * kMaxNQ + q);
+            pref[b + 1] = __ldcg(p.part_cnt + b * kMaxNQ + q);
         if (tid == 0) pref[0] = 0;
         named_bar_sync(kSelBarrier, kSelThreads);
         if (tid < 32) {   // inclusive scan of pref[1..grid] by warp 0
@@ -380,11 +363,8 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         // sorts small)
         SelState ms = sel[q];
         ms.gtau = nullptr; ms.lbest = nullptr; ms.lmax = nullptr;
-        if (big_buf && big_cap >= 2 * sel[q].cap && *sel[q].cnt + total <= big_cap / 4) {
-            const int own = *sel[q].cnt;
-            for (int i = tid; i < own; i += kSelThreads) big_buf[i] = sel[q].buf[i];
+        if (big_buf && big_cap >= 2 * sel[q].cap && total <= big_cap / 4) {
             ms.buf = big_buf; ms.cap = big_cap; ms.room = big_cap - k;
-            named_bar_sync(kSelBarrier, kSelThreads);
         }
         const int room = ms.room;
         for (int base = 0; base < total; base += room) {

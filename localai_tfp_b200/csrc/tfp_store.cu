@@ -117,6 +117,7 @@ struct Tuning {
     int mma_min_queries = 5;       // batches at least this large go to the tensor-core path (measured break-even)
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
+    bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)
 };
 static const Tuning& tuning() {
     static Tuning t = [] {
@@ -126,6 +127,7 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_MMA_MIN_QUERIES")) x.mma_min_queries = atoi(e);
         if (const char* e = getenv("TFP_MMA_MIN_ROWS")) x.mma_min_rows = atoll(e);
         if (const char* e = getenv("TFP_MMA_TERMS")) x.mma_terms = atoi(e) == 3 ? 3 : 1;
+        if (const char* e = getenv("TFP_MMA_PAIR")) x.mma_pair = atoi(e) != 0;
         return x;
     }();
     return t;
@@ -415,8 +417,9 @@ static int optin_all(int bytes) {
     CU_OK((optin_gen<4, false, false>(bytes))); CU_OK((optin_gen<4, true, false>(bytes)));
     CU_OK((optin_gen<8, false, false>(bytes))); CU_OK((optin_gen<8, true, false>(bytes)));
     CU_OK((optin_gen<1, false, true>(bytes)));  CU_OK((optin_gen<1, true, true>(bytes)));
-    CU_OK(cudaFuncSetAttribute(mma_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-    CU_OK(cudaFuncSetAttribute(mma_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    CU_OK((cudaFuncSetAttribute(mma_scan_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
+    CU_OK((cudaFuncSetAttribute(mma_scan_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
+    CU_OK((cudaFuncSetAttribute(mma_scan_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
     CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
     CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
     CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
@@ -1035,11 +1038,13 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     CU_OK(cudaMemsetAsync(cand_cnt, 0, (size_t)kMmaMaxNQ * 4, c->stream));
 
     if (get_encoder()) return -2;
+    // CTA pairs (cta_group::2): each CTA of a pair stages half of the query tile, so the box is half as tall
+    const bool pair = terms == 1 && tuning().mma_pair && (grid % 2) == 0 && grid >= 2;
     CUtensorMap tmap_q;
     cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)(2 * nqp)};
     cuuint64_t gstride[1] = {(cuuint64_t)dim * 4};
     const int bc = mma_box_cols(terms);
-    cuuint32_t box[2] = {(cuuint32_t)bc, (cuuint32_t)nqp};
+    cuuint32_t box[2] = {(cuuint32_t)bc, (cuuint32_t)(pair ? nqp / 2 : nqp)};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = g_encode(&tmap_q, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, qs, gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, bc == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1056,17 +1061,33 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     mp.refresh_ns = 5000;
     mp.eps = terms == 1 ? eps : nullptr;
     mp.debug = getenv("TFP_MMA_DEBUG") ? atoi(getenv("TFP_MMA_DEBUG")) : 0;
-    mp.n_stages = mma_stage_count(nqp, terms, (size_t)s->max_smem);
+    mp.n_stages = mma_stage_count(nqp, terms, (size_t)s->max_smem, pair);
     if (mp.n_stages < 2) return fail(-4, "internal: tensor-core stages do not fit shared memory");
-    const size_t smem = mma_smem_bytes(nqp, terms, mp.n_stages);
+    const size_t smem = mma_smem_bytes(nqp, terms, mp.n_stages, pair);
+    if (getenv("TFP_MMA_TRACE"))
+        fprintf(stderr, "tfp mma: terms=%d pair=%d nqp=%d stages=%d smem=%zu grid=%d\n", terms, (int)pair, nqp, mp.n_stages, smem, grid);
+    auto launch_pass = [&]() -> int {
+        if (pair) {
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kMmaThreads); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            CU_OK((cudaLaunchKernelEx(&cfg, mma_scan_kernel<1, true>, tmap_keys, tmap_q, mp)));
+        } else if (terms == 3) {
+            mma_scan_kernel<3, false><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
+        } else {
+            mma_scan_kernel<1, false><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
+        }
+        CU_OK(cudaGetLastError());
+        return 0;
+    };
     mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
-    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
-    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
-    CU_OK(cudaGetLastError());
+    if (launch_pass()) return -1;
     mp.mode = 1;
-    if (terms == 3) mma_scan_kernel<3><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
-    else            mma_scan_kernel<1><<<grid, kMmaThreads, smem, c->stream>>>(tmap_keys, tmap_q, mp);
-    CU_OK(cudaGetLastError());
+    if (launch_pass()) return -1;
 
     FinalizeParams fp;
     memset(&fp, 0, sizeof(fp));
