@@ -91,3 +91,31 @@ def test_small_batches_and_small_stores_stay_on_the_exact_kernel(tfp, oracle):
     Q = make_keys(64, 64, seed=34, normalized=True)
     passes, _ = run_batch(tfp, oracle, K, Q, 10, True, expect_mma=False)
     assert passes == 0
+
+
+@pytest.mark.parametrize("n", [1_200_001, 148 * 128 * 9 + 128])     # ~63 tiles per CTA; and exactly one tile more than a whole round
+def test_mma_path_long_scan_equals_single_finds(tfp, n):
+    """A long scan (many tiles per CTA, thresholds tightening on the way, a CTA pair whose odd CTA ends on a
+    padding tile): the batched answer must be what the single-query exact kernel returns, bit for bit."""
+    import torch
+    d, nq, k = 256, 256, 100
+    g = torch.Generator(device="cuda").manual_seed(n)
+    K = torch.randn((n, d), generator=g, device="cuda", dtype=torch.float32)
+    K /= K.norm(dim=1, keepdim=True)
+    s = tfp.Store(capacity_rows=n)
+    s.set_device(K.data_ptr(), n, d)
+    Q = K[torch.arange(0, n, n // nq, device="cuda")[:nq]] + 0.05 * torch.randn((nq, d), generator=g, device="cuda")
+    Q = (Q / Q.norm(dim=1, keepdim=True)).cpu().numpy().astype(f32)
+    del K
+    c = s.find_context()
+    c.upload(Q)
+    c.launch(0, nq, k)
+    res = c.download()
+    passes, reruns = c.mma_counters()
+    assert passes >= 1 and reruns <= 2
+    for i in list(range(0, nq, 17)) + [nq - 1]:
+        ids, sims = s.find_ids(Q[i], k)                  # one query: the exact scan kernel
+        assert np.array_equal(res[i][1], sims), i
+        assert np.array_equal(res[i][0], ids), i
+        assert list(sims) == sorted(sims, reverse=True)
+    c.close(); s.close()
