@@ -586,60 +586,144 @@ __device__ __forceinline__ void block_sort_desc(uint64_t* buf, int P, int tid, i
     }
 }
 
+// The rows to re-score are found by SELECTION, not by sorting the whole list: the 32-bit score words are
+// staged in shared memory once (64 KiB: two blocks per SM, so the 256 queries of a batch are resident at
+// once), a 4-pass radix select over them gives the approximate score of the rank that matters, and one more
+// pass collects every candidate that reaches the cut (only those are re-read from the list).
+constexpr int kFinThreads = 256;       // few rows are re-scored (tens to hundreds); 128 registers each for their pipelined row walk
+constexpr int kFinWarps = kFinThreads / 32;
+constexpr size_t kFinDynSmem = (size_t)kMmaCandCap * 4;
 template <bool F64, int TERMS>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(kFinThreads, 2)
 mma_finalize_kernel(const FinalizeParams p) {
-    extern __shared__ uint64_t fbuf[];                   // [P] candidate words (approximate score, slot)
+    extern __shared__ unsigned int skey[];               // [n] score words of the candidate list
+    __shared__ uint64_t fbuf[kMmaRescoreMax];            // approximate words of the rows to re-score
     __shared__ uint64_t exact[kMmaRescoreMax];           // exact words of the re-scored rows
-    __shared__ int s_C;
+    __shared__ unsigned int hist[kFinWarps][256];        // one histogram per warp: no cross-warp contention on hot bins
+    __shared__ unsigned int s_prefix, s_rank, s_cnt;
     const int q = blockIdx.x, tid = threadIdx.x;
     const unsigned int cnt = p.cand_cnt[q];
     const int n = cnt < (unsigned)kMmaCandCap ? (int)cnt : kMmaCandCap;
-    int P = 2;
-    while (P < n) P <<= 1;
-    for (int i = tid; i < P; i += blockDim.x) fbuf[i] = i < n ? p.cand[(size_t)q * kMmaCandCap + i] : 0ull;
-    __syncthreads();
-    block_sort_desc(fbuf, P, tid, blockDim.x);
+    const uint64_t* cand = p.cand + (size_t)q * kMmaCandCap;
     const int k = p.topk;
     const int lim = (uint32_t)k < p.n_rows ? k : (int)p.n_rows;
-    // how many of the best candidates to re-score
-    if (tid == 0) {
-        int C;
-        if (TERMS == 3) {
-            C = n < k + kMmaMargin ? n : k + kMmaMargin;
-        } else if (n <= lim) {
-            C = n;
-        } else {
-            // every row whose approximate score is within 2 eps of the k-th best approximate score:
-            // a row below that band is provably below the k-th exact score
-            const float band = cand_score(fbuf[lim - 1]) - 2.0f * p.eps[q];
-            const uint32_t cut = score_to_order(band);
-            int lo = lim, hi = n;                        // first index whose score word is below the band
-            while (lo < hi) { int mid = (lo + hi) >> 1; if ((uint32_t)(fbuf[mid] >> 32) >= cut) lo = mid + 1; else hi = mid; }
-            C = lo;
+    // the rank whose approximate score decides the cut: k-th best (single TF32: the error band hangs below
+    // it), or (k + margin)-th best (3xTF32: exactly that many are re-scored, ties included)
+    const int want = TERMS == 3 ? (n < k + kMmaMargin ? n : k + kMmaMargin) : (n < lim ? n : lim);
+    if (tid == 0) { s_prefix = 0u; s_rank = (unsigned)want; s_cnt = 0u; }
+#pragma unroll 8
+    for (int i = tid; i < n; i += kFinThreads) skey[i] = (unsigned int)(__ldcg(cand + i) >> 32);   // independent loads: many in flight
+    __syncthreads();
+    if (want >= 1) {
+        unsigned int* myhist = hist[tid >> 5];
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            for (int i = tid; i < kFinWarps * 256; i += kFinThreads) (&hist[0][0])[i] = 0u;
+            __syncthreads();
+            const unsigned int prefix = s_prefix;
+            for (int i = tid; i < n; i += kFinThreads) {
+                const unsigned int key = skey[i];
+                if (shift == 24 || ((key ^ prefix) >> (shift + 8)) == 0u) atomicAdd(&myhist[(key >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            for (int b = tid; b < 256; b += kFinThreads) {   // fold the per-warp histograms into hist[0]
+                unsigned int sum = 0;
+                for (int w = 0; w < kFinWarps; w++) sum += hist[w][b];
+                hist[0][b] = sum;
+            }
+            __syncthreads();
+            if (tid < 32) {   // warp 0: lane l owns bins 255 - 8l .. 248 - 8l (descending keys)
+                unsigned int local = 0;
+                for (int j = 0; j < 8; j++) local += hist[0][255 - 8 * tid - j];
+                unsigned int incl = local;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const unsigned int v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                    if (tid >= d) incl += v;
+                }
+                const unsigned int rank = s_rank;
+                const bool mine = incl >= rank && incl - local < rank;   // the rank-th largest falls into my bins
+                if (mine) {
+                    unsigned int acc = incl - local;
+                    for (int j = 0; j < 8; j++) {
+                        const int b = 255 - 8 * tid - j;
+                        if (acc + hist[0][b] >= rank) { s_prefix = prefix | ((unsigned int)b << shift); s_rank = rank - acc; break; }
+                        acc += hist[0][b];
+                    }
+                }
+            }
+            __syncthreads();
         }
-        s_C = C;
+    }
+    // every candidate whose score word reaches `cut` is re-scored
+    unsigned int cut = 0u;                               // n <= lim: take them all
+    if (TERMS == 3) cut = want >= 1 ? s_prefix : 0u;
+    else if (n > lim) {
+        // every row whose approximate score is within 2 eps of the k-th best approximate score:
+        // a row below that band is provably below the k-th exact score
+        cut = score_to_order(order_to_score(s_prefix) - 2.0f * p.eps[q]);
+    }
+    for (int i = tid; i < n; i += kFinThreads) {
+        if (skey[i] >= cut) {
+            const unsigned int pos = atomicAdd(&s_cnt, 1u);
+            if (pos < (unsigned)kMmaRescoreMax) fbuf[pos] = __ldcg(cand + i);
+        }
     }
     __syncthreads();
-    const int C_all = s_C;
+    const int C_all = (int)s_cnt;
     const int C = C_all < kMmaRescoreMax ? C_all : kMmaRescoreMax;
+    const uint32_t cut_order = cut;                      // 3xTF32: rows not re-scored all score below this
     // exact re-score, one thread per candidate row, the reference's arithmetic (scan.cuh Acc<>)
     const float* qv = p.q + (size_t)(p.q_first + q) * p.dim;
     const double mag1 = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    // The query goes to shared memory (the score words there are dead now): every thread reads all of it, and
+    // left in global memory its lines are pushed out of L1 by the key rows streaming through -- each chunk of
+    // the walk then waited a full L2 round trip for its query values (measured: 78 % of this kernel).
+    const bool q_in_smem = (size_t)p.dim * 4 <= kFinDynSmem;
+    float4* qs4 = reinterpret_cast<float4*>(skey);
+    if (q_in_smem)
+        for (int i = tid; i < (p.dim >> 2); i += kFinThreads) qs4[i] = __ldg(reinterpret_cast<const float4*>(qv) + i);
+    __syncthreads();
+    // Every thread walks its own (cold) row, one add after the other: what costs is memory latency, not
+    // arithmetic.  The walk is software-pipelined in 128-byte chunks -- the next chunk's loads are in flight
+    // while this chunk's 32 adds run.  (What remains is HBM's rate for ~190 scattered 4 KiB rows per query:
+    // the same walk over adjacent rows runs 0.14 ms faster per 256-query batch; an L2 prefetch of the whole
+    // row up front was measured and made it slightly slower.)
+    // dim % 4 == 0 on this path; the adds stay in index order.  (A lambda, so that the query pointer keeps
+    // its address space: shared-memory loads when the query is staged there.)
+    auto rescore = [&](uint32_t slot, auto qv4) -> uint64_t {
+        const float4* kr4 = reinterpret_cast<const float4*>(p.keys + (size_t)slot * p.dim);
+        const int n4 = p.dim >> 2;
+        constexpr int CH = 8;
+        const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float4 cur[CH], nxt[CH];
+#pragma unroll
+        for (int j = 0; j < CH; j++) cur[j] = j < n4 ? __ldcs(kr4 + j) : zero4;
+        Acc<F64> acc;
+        acc.zero();
+        for (int base = 0; base < n4; base += CH) {
+#pragma unroll
+            for (int j = 0; j < CH; j++) nxt[j] = base + CH + j < n4 ? __ldcs(kr4 + base + CH + j) : zero4;
+#pragma unroll
+            for (int j = 0; j < CH; j++) {
+                if (base + j < n4) {
+                    const float4 qq = qv4[base + j];
+                    acc.add(qq.x, cur[j].x); acc.add(qq.y, cur[j].y); acc.add(qq.z, cur[j].z); acc.add(qq.w, cur[j].w);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < CH; j++) cur[j] = nxt[j];
+        }
+        return pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[slot] : 1.0), slot);
+    };
     for (int t = tid; t < kMmaRescoreMax; t += blockDim.x) {
         uint64_t w = 0ull;
         if (t < C) {
             const uint32_t slot = cand_slot(fbuf[t]);
-            const float* kr = p.keys + (size_t)slot * p.dim;
-            Acc<F64> acc;
-            acc.zero();
-            for (int i = 0; i < p.dim; i++) acc.add(__ldg(qv + i), kr[i]);
-            w = pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[slot] : 1.0), slot);
+            if (q_in_smem) w = rescore(slot, (const float4*)qs4);
+            else w = rescore(slot, reinterpret_cast<const float4*>(qv));
         }
         exact[t] = w;
     }
     __syncthreads();
-    const uint64_t cut_word = C > 0 ? fbuf[C - 1] : 0ull; // approximate word of the last candidate re-scored
     int PE = 2;
     while (PE < C) PE <<= 1;
     __syncthreads();
@@ -670,7 +754,7 @@ mma_finalize_kernel(const FinalizeParams p) {
             // candidate; rows never listed are below the threshold, which is below it too).  They are
             // irrelevant iff cut + (3xTF32 error) is still below the k-th exact score.
             const float kth = cand_score(exact[m - 1]);
-            const float nxt = cand_score(cut_word);
+            const float nxt = order_to_score(cut_order);
             if (!(nxt + 2e-5f * (fabsf(kth) + 1.0f) < kth)) st = 3;  // too close to call: exact re-run
         }
         p.status[q] = st;

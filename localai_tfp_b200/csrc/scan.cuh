@@ -110,12 +110,23 @@ __device__ __forceinline__ void xchg_raise(const XchgParams& x, int tid) {
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(x.flag[tid]), "r"(x.seq) : "memory");
 }
 // Stand-alone push for the paths whose records are written by other kernels (tensor-core finalize,
-// big-k decode, multi-launch batches, empty shards).
+// big-k decode, multi-launch batches, empty shards).  One CTA per destination rank: it copies the
+// records there and raises that rank's word itself, so no CTA waits for another.
 __global__ void push_records_kernel(const __grid_constant__ XchgParams x, const uint8_t* src, size_t bytes) {
-    xchg_copy(x, src, 0, bytes, (int)threadIdx.x, (int)blockDim.x);
+    const int r = (int)blockIdx.x;
+    const size_t words = bytes >> 4;
+    const uint4* s = (const uint4*)src;
+    uint4* d = (uint4*)x.slot[r];
+    for (size_t w = threadIdx.x; w < words; w += blockDim.x) {
+        const uint4 v = __ldcg(s + w);
+        asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(d + w), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+    __threadfence_system();
     __syncthreads();
-    xchg_raise(x, (int)threadIdx.x);
+    if (threadIdx.x == 0 && x.raise && r != x.me)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(x.flag[r]), "r"(x.seq) : "memory");
 }
+
 // Winning key rows of a sharded find, from the store straight into every rank's slot: CTA (i, q) copies
 // row out_slots[q][i] to byte offset keys_off + (q * topk + i) * dim * 4 of this rank's slot everywhere.
 // The words are raised by the push_records_kernel that follows in the stream.

@@ -420,10 +420,10 @@ static int optin_all(int bytes) {
     CU_OK((cudaFuncSetAttribute(mma_scan_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
     CU_OK((cudaFuncSetAttribute(mma_scan_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
     CU_OK((cudaFuncSetAttribute(mma_scan_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)));
-    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
-    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
-    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
-    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMmaCandCap * 8)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFinDynSmem)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFinDynSmem)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFinDynSmem)));
+    CU_OK((cudaFuncSetAttribute(mma_finalize_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFinDynSmem)));
     return 0;
 }
 
@@ -1098,13 +1098,12 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     fp.out_n = sp.out_n; fp.out_rec = sp.out_rec; fp.rec_bytes = sp.rec_bytes; fp.rec_topk = sp.rec_topk;
     fp.status = status;
     fp.eps = eps;
-    const size_t fsm = (size_t)kMmaCandCap * 8;
     if (terms == 3) {
-        if (norm) mma_finalize_kernel<false, 3><<<g, 512, fsm, c->stream>>>(fp);
-        else      mma_finalize_kernel<true, 3><<<g, 512, fsm, c->stream>>>(fp);
+        if (norm) mma_finalize_kernel<false, 3><<<g, kFinThreads, kFinDynSmem, c->stream>>>(fp);
+        else      mma_finalize_kernel<true, 3><<<g, kFinThreads, kFinDynSmem, c->stream>>>(fp);
     } else {
-        if (norm) mma_finalize_kernel<false, 1><<<g, 512, fsm, c->stream>>>(fp);
-        else      mma_finalize_kernel<true, 1><<<g, 512, fsm, c->stream>>>(fp);
+        if (norm) mma_finalize_kernel<false, 1><<<g, kFinThreads, kFinDynSmem, c->stream>>>(fp);
+        else      mma_finalize_kernel<true, 1><<<g, kFinThreads, kFinDynSmem, c->stream>>>(fp);
     }
     CU_OK(cudaGetLastError());
     c->launches += 4;
@@ -1807,7 +1806,7 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
         c->launches++;
     }
     if (!c->x_pushed) {
-        push_records_kernel<<<1, 256, 0, c->stream>>>(x, c->out_rec, rb * count);
+        push_records_kernel<<<c->x_world, 256, 0, c->stream>>>(x, c->out_rec, rb * count);
         CU_OK(cudaGetLastError());
         c->launches++;
     }
