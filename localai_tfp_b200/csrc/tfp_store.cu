@@ -118,6 +118,9 @@ struct Tuning {
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
     bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)
+    int mma_debug = 0;             // development timing only (results wrong): 1 no epilogue hits, 2 no MMAs
+    bool mma_trace = false;        // print the tensor-core launch shape
+    bool scan_times = false;       // per-CTA time stamps of every exact scan, printed by tfp_find_ctx_sync
 };
 static const Tuning& tuning() {
     static Tuning t = [] {
@@ -128,6 +131,9 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_MMA_MIN_ROWS")) x.mma_min_rows = atoll(e);
         if (const char* e = getenv("TFP_MMA_TERMS")) x.mma_terms = atoi(e) == 3 ? 3 : 1;
         if (const char* e = getenv("TFP_MMA_PAIR")) x.mma_pair = atoi(e) != 0;
+        if (const char* e = getenv("TFP_MMA_DEBUG")) x.mma_debug = atoi(e);
+        x.mma_trace = getenv("TFP_MMA_TRACE") != nullptr;
+        x.scan_times = getenv("TFP_SCAN_TIMES") != nullptr;
         return x;
     }();
     return t;
@@ -381,14 +387,23 @@ static int ensure_capacity(tfp_store* s, int64_t rows) {
     // no virtual memory management: reallocate and copy
     int64_t ncap = std::max<int64_t>({rows, s->cap * 2, s->cap_hint, (int64_t)1024});
     float* nk = nullptr; int64_t* ni = nullptr; double* nn = nullptr;
-    CU_OK(cudaMalloc(&nk, (size_t)ncap * s->dim * 4 + 256));
-    CU_OK(cudaMalloc(&ni, (size_t)ncap * 8));
-    CU_OK(cudaMalloc(&nn, (size_t)ncap * 8));
-    if (s->n > 0) {
-        CU_OK(cudaMemcpyAsync(nk, s->d_keys, (size_t)s->n * s->dim * 4, cudaMemcpyDeviceToDevice, s->s_mut));
-        CU_OK(cudaMemcpyAsync(ni, s->d_ids, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
-        CU_OK(cudaMemcpyAsync(nn, s->d_knorm, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
-        CU_OK(cudaStreamSynchronize(s->s_mut));
+    auto grow = [&]() -> int {
+        CU_OK(cudaMalloc(&nk, (size_t)ncap * s->dim * 4 + 256));
+        CU_OK(cudaMalloc(&ni, (size_t)ncap * 8));
+        CU_OK(cudaMalloc(&nn, (size_t)ncap * 8));
+        if (s->n > 0) {
+            CU_OK(cudaMemcpyAsync(nk, s->d_keys, (size_t)s->n * s->dim * 4, cudaMemcpyDeviceToDevice, s->s_mut));
+            CU_OK(cudaMemcpyAsync(ni, s->d_ids, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
+            CU_OK(cudaMemcpyAsync(nn, s->d_knorm, (size_t)s->n * 8, cudaMemcpyDeviceToDevice, s->s_mut));
+            CU_OK(cudaStreamSynchronize(s->s_mut));
+        }
+        return 0;
+    };
+    if (grow()) {   // the store keeps its old arrays; nothing half-grown is left behind
+        if (nk) cudaFree(nk);
+        if (ni) cudaFree(ni);
+        if (nn) cudaFree(nn);
+        return -1;
     }
     if (s->d_keys) cudaFree(s->d_keys);
     if (s->d_ids) cudaFree(s->d_ids);
@@ -845,10 +860,12 @@ extern "C" int tfp_store_load(tfp_store* s, const char* path) {
     s->next_id = h.next_id;
     s->normalized = h.normalized != 0;
     if (h.rows == 0) { fclose(f); return 0; }
-    if (ensure_capacity(s, h.rows)) { fclose(f); return -1; }
+    // any failure below leaves the store as empty as it was (its arrays may have grown; that is harmless)
+    auto undo = [&]() { s->dim = -1; s->normalized = true; s->next_id = 0; s->n = 0; s->index = FlatIndex(); s->slot_hash.clear(); s->slot_id.clear(); };
+    if (ensure_capacity(s, h.rows)) { fclose(f); undo(); return -1; }
     const size_t chunk = (size_t)64 << 20;
     PinBuf pin;
-    if (pin.reserve(chunk)) { fclose(f); return -1; }
+    if (pin.reserve(chunk)) { fclose(f); undo(); return -1; }
     bool ok = true;
     auto fill = [&](void* dptr, size_t bytes) -> int {
         for (size_t off = 0; ok && off < bytes; off += chunk) {
@@ -862,19 +879,23 @@ extern "C" int tfp_store_load(tfp_store* s, const char* path) {
     if (!rc) rc = fill(s->d_ids, (size_t)h.rows * 8);
     fclose(f);
     pin.release();
-    if (rc) return rc;
-    if (!ok) { s->dim = -1; s->normalized = true; s->next_id = 0; return fail(2, "tfp_store_load: %s is truncated", path); }
+    if (rc) { undo(); return rc; }
+    if (!ok) { undo(); return fail(2, "tfp_store_load: %s is truncated", path); }
     // recompute row hashes and norms on the device, rebuild the host index and mirrors
     const int64_t n = h.rows;
-    if (s->st_hash.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
-    row_stats_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->s_mut>>>(s->d_keys, n, s->dim, s->st_hash.as<uint64_t>(),
-                                                                        s->d_knorm, s->st_isnorm.as<uint8_t>());
-    CU_OK(cudaGetLastError());
-    s->slot_hash.resize((size_t)n);
-    s->slot_id.resize((size_t)n);
-    CU_OK(cudaMemcpyAsync(s->slot_hash.data(), s->st_hash.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
-    CU_OK(cudaMemcpyAsync(s->slot_id.data(), s->d_ids, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
-    CU_OK(cudaStreamSynchronize(s->s_mut));
+    auto rebuild = [&]() -> int {
+        if (s->st_hash.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
+        row_stats_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->s_mut>>>(s->d_keys, n, s->dim, s->st_hash.as<uint64_t>(),
+                                                                            s->d_knorm, s->st_isnorm.as<uint8_t>());
+        CU_OK(cudaGetLastError());
+        s->slot_hash.resize((size_t)n);
+        s->slot_id.resize((size_t)n);
+        CU_OK(cudaMemcpyAsync(s->slot_hash.data(), s->st_hash.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
+        CU_OK(cudaMemcpyAsync(s->slot_id.data(), s->d_ids, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
+        CU_OK(cudaStreamSynchronize(s->s_mut));
+        return 0;
+    };
+    if (rebuild()) { undo(); return -1; }
     s->index.reserve((size_t)n);
     for (int64_t i = 0; i < n; i++) s->index.insert(s->slot_hash[(size_t)i], (uint32_t)i);
     s->n = n;
@@ -1060,11 +1081,11 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
     mp.refresh_ns = 5000;
     mp.eps = terms == 1 ? eps : nullptr;
-    mp.debug = getenv("TFP_MMA_DEBUG") ? atoi(getenv("TFP_MMA_DEBUG")) : 0;
+    mp.debug = tuning().mma_debug;
     mp.n_stages = mma_stage_count(nqp, terms, (size_t)s->max_smem, pair);
     if (mp.n_stages < 2) return fail(-4, "internal: tensor-core stages do not fit shared memory");
     const size_t smem = mma_smem_bytes(nqp, terms, mp.n_stages, pair);
-    if (getenv("TFP_MMA_TRACE"))
+    if (tuning().mma_trace)
         fprintf(stderr, "tfp mma: terms=%d pair=%d nqp=%d stages=%d smem=%zu grid=%d\n", terms, (int)pair, nqp, mp.n_stages, smem, grid);
     auto launch_pass = [&]() -> int {
         if (pair) {
@@ -1185,7 +1206,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
     p.r_local = (ksel + p.m_local - 1) / p.m_local;
     p.refresh_ns = tuning().refresh_ns;
     if (tuning().disable_lbest) p.lbest = nullptr;
-    if (getenv("TFP_SCAN_TIMES")) {   // development: per-CTA time stamps of the next scan, printed by tfp_find_ctx_sync
+    if (tuning().scan_times) {   // development: per-CTA time stamps of the next scan, printed by tfp_find_ctx_sync
         if (c->dbg_times.reserve((size_t)kMaxGrid * 4 * 8)) return -1;
         CU_OK(cudaMemsetAsync(c->dbg_times.p, 0, (size_t)kMaxGrid * 4 * 8, c->stream));
         p.dbg_times = c->dbg_times.as<unsigned long long>();
