@@ -33,7 +33,7 @@ PROTOTYPES = {
     "tfp_store_set_device": (C.c_int, [vp, vp, C.c_int64, C.c_int, i64p, u8p]),
     "tfp_store_delete": (C.c_int, [vp, fp, C.c_int64, C.c_int, i64p]),
     "tfp_store_get": (C.c_int, [vp, fp, C.c_int64, C.c_int, i64p, i64p, i64p]),
-    "tfp_store_find": (C.c_int, [vp, fp, C.c_int, C.c_int, i32p, i64p, fp, fp, i32p]),
+    "tfp_store_find": (C.c_int, [vp, vp, C.c_int, C.c_int, i32p, vp, vp, vp, i32p]),   # array arguments as plain addresses: the per-call path
     "tfp_store_find_batch": (C.c_int, [vp, fp, C.c_int, C.c_int, C.c_int, i32p, i64p, fp, fp]),
     "tfp_store_stats": (C.c_int, [vp, C.POINTER(TfpStats)]),
     "tfp_store_save": (C.c_int, [vp, C.c_char_p]),

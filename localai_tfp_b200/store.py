@@ -61,6 +61,11 @@ def _p(a: np.ndarray, t):
     return a.ctypes.data_as(t)
 
 
+def _addr(a: np.ndarray) -> int:
+    """Address of a contiguous array (several times cheaper than a.ctypes on the per-query path)."""
+    return a.__array_interface__["data"][0]
+
+
 class Store:
     """One store shard resident on one B200."""
 
@@ -172,12 +177,12 @@ class Store:
         ids = np.empty(kk, np.int64)
         sims = np.empty(kk, np.float32)
         outk = np.empty((kk, max(len(q), 1)), np.float32)
-        self._check(self._L.tfp_store_find(self._h, _p(q, fp), len(q), k if k < 1 else kk, C.byref(n), _p(ids, i64p),
-                                           _p(sims, fp), _p(outk, fp), C.byref(path)))
+        self._check(self._L.tfp_store_find(self._h, _addr(q), len(q), k if k < 1 else kk, C.byref(n), _addr(ids),
+                                           _addr(sims), _addr(outk), C.byref(path)))
         m = n.value
         self.last_path = "normalized" if path.value == 1 else "fallback"
-        return ([outk[i, :len(q)].copy() for i in range(m)], [self.values.get(int(ids[i])) for i in range(m)],
-                sims[:m].copy())
+        # outk / sims are this call's own buffers: hand out views, not copies
+        return (list(outk[:m, :len(q)]), [self.values.get(i) for i in ids[:m].tolist()], sims[:m])
 
     def find_ids(self, key, topk: int):
         """StoresFind without the key echo: (ids, similarities)."""
@@ -186,9 +191,9 @@ class Store:
         n = C.c_int()
         ids = np.empty(kk, np.int64)
         sims = np.empty(kk, np.float32)
-        self._check(self._L.tfp_store_find(self._h, _p(q, fp), len(q), int(topk) if topk < 1 else kk, C.byref(n),
-                                           _p(ids, i64p), _p(sims, fp), None, None))
-        return ids[:n.value].copy(), sims[:n.value].copy()
+        self._check(self._L.tfp_store_find(self._h, _addr(q), len(q), int(topk) if topk < 1 else kk, C.byref(n),
+                                           _addr(ids), _addr(sims), None, None))
+        return ids[:n.value], sims[:n.value]
 
     def find_batch(self, queries, topk: int, with_keys: bool = False):
         qs = np.ascontiguousarray(np.asarray(queries, dtype=np.float32))
