@@ -37,8 +37,9 @@
 //   warps 4-7   epilogue: tcgen05.ld the finished accumulator (thread = key row, registers =
 //               queries), scale by 1/|k| on the cosine path, compare against the per-query
 //               threshold, append survivors to the query's candidate list in HBM;
-//   warp 2      bound refresher: publishes this CTA's best score per query and keeps the
-//               thresholds (min over CTAs of those bests: >= 148 rows are at least that good).
+//   warp 2      bound refresher: publishes this CTA's second-best score per query, computes the grid-wide
+//               bound of "its" queries (the r-th largest second-best over the CTAs: r CTAs hold two rows
+//               each at least that good) and keeps all thresholds fresh from the shared bounds.
 // No score matrix is ever written to HBM.
 #pragma once
 #include "scan.cuh"
@@ -67,7 +68,9 @@ struct MmaParams {
     int f64;                     // cosine path: approximate score = dot / |k|
     int mode;                    // 0 = bound-only pass over the first tile of every CTA, 1 = full pass
     const double* knorm;
-    unsigned int* lbest;         // [grid x kMmaMaxNQ] orderable word of each CTA's best approximate score
+    unsigned int* lbest2;        // [grid x kMmaMaxNQ] orderable word of each CTA's SECOND best approximate score of this pass
+    unsigned int* gbound;        // [kMmaMaxNQ] grid-wide lower bound of the need-th best score per query (only rises)
+    int r_need;                  // r = ceil(need / 2): r CTAs with two rows each >= the bound make `need` rows
     uint64_t* cand;              // [nq x kMmaCandCap]
     unsigned int* cand_cnt;      // [nq]
     int refresh_ns;
@@ -224,7 +227,7 @@ __host__ __device__ inline size_t mma_stage_bytes(int nqp, int terms, bool pair 
     return terms == 3 ? 2 * (size_t)kMmaRows * row + 2 * (size_t)nqp * row : (size_t)kMmaRows * row + (size_t)nqp * row;
 }
 __host__ __device__ inline size_t mma_fixed_smem_bytes() {
-    return (3 * kMmaStagesMax + 4) * 8 + 16 + 4 * kMmaMaxNQ * 4 + 1024 + 8 * (size_t)kMmaHitQueue * 16 + 32;
+    return (3 * kMmaStagesMax + 4) * 8 + 16 + 5 * kMmaMaxNQ * 4 + kMaxGrid * 4 + 1024 + 8 * (size_t)kMmaHitQueue * 16 + 32;
 }
 // as many stages as fit (at least the pipeline's nominal depth at nq = 256, at most kMmaStagesMax)
 __host__ __device__ inline int mma_stage_count(int nqp, int terms, size_t max_smem, bool pair = false) {
@@ -234,6 +237,37 @@ __host__ __device__ inline int mma_stage_count(int nqp, int terms, size_t max_sm
 }
 __host__ __device__ inline size_t mma_smem_bytes(int nqp, int terms, int stages, bool pair = false) {
     return stages * mma_stage_bytes(nqp, terms, pair) + mma_fixed_smem_bytes();
+}
+
+// The r-th largest (with multiplicity) of G words spaced kMmaMaxNQ apart, by one warp; 0 = "nothing" and is
+// skipped.  Returns 0 when fewer than r words are set.  `stage`: G words of shared scratch.
+__device__ __forceinline__ unsigned int mma_rth_largest(const unsigned int* col, int G, int r, int lane, unsigned int* stage) {
+    for (int b = lane; b < G; b += 32) stage[b] = ((const volatile unsigned int*)col)[(size_t)b * kMmaMaxNQ];
+    __syncwarp();
+    unsigned int found = 0u;
+    for (int b = lane; b < G; b += 32) {
+        const unsigned int v = stage[b];
+        if (v == 0u || v <= found) continue;
+        int ge = 0;
+        for (int j = 0; j < G; j++) ge += (stage[j] >= v) ? 1 : 0;
+        if (ge >= r) found = v;                           // at least r words reach v: v is a valid bound
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        const unsigned int o = __shfl_xor_sync(0xFFFFFFFFu, found, d);
+        found = o > found ? o : found;
+    }
+    __syncwarp();
+    return found;
+}
+// Between the bound-only pass and the full pass: the first grid-wide bounds, one warp per query, so that
+// the full pass starts with every threshold in place.
+__global__ void mma_bound_kernel(const unsigned int* lbest2, int grid, int r, int nq, unsigned int* gbound) {
+    __shared__ unsigned int stage[8][kMaxGrid];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 8 + w;
+    if (q >= nq) return;
+    const unsigned int v = mma_rth_largest(lbest2 + q, grid, r, lane, stage[w]);
+    if (lane == 0) gbound[q] = v;
 }
 
 // PAIR: launched as clusters of two CTAs (cta_group::2, TERMS = 1 only).  CTA r of a pair owns key tile
@@ -270,9 +304,11 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
     volatile int* flags = (volatile int*)(tmem_base_s + 1);   // [0] done, [1] thresholds ready
     unsigned int* tau = (unsigned int*)(tmem_base_s + 4);     // [kMmaMaxNQ] admission thresholds (orderable words)
     unsigned int* lb = tau + kMmaMaxNQ;                       // [kMmaMaxNQ] this CTA's best score per query
-    float* tau_f = (float*)(lb + kMmaMaxNQ);                  // [kMmaMaxNQ] tau as a float (-inf = admit everything)
-    float* lb_f = tau_f + kMmaMaxNQ;                          // [kMmaMaxNQ] lb as a float (may lag behind lb: only a hint)
-    uint4* hitq = (uint4*)(lb_f + kMmaMaxNQ);                 // [8][kMmaHitQueue] (query, row, score bits): staged hits
+    unsigned int* lb2 = lb + kMmaMaxNQ;                       // [kMmaMaxNQ] ... and its second best
+    float* tau_f = (float*)(lb2 + kMmaMaxNQ);                 // [kMmaMaxNQ] tau as a float (-inf = admit everything)
+    float* lb_f = tau_f + kMmaMaxNQ;                          // [kMmaMaxNQ] lb2 as a float (may lag behind lb2: only a hint)
+    unsigned int* rstage = (unsigned int*)(lb_f + kMmaMaxNQ); // [kMaxGrid] refresher scratch: one query's column of second-bests
+    uint4* hitq = (uint4*)(rstage + kMaxGrid);                // [8][kMmaHitQueue] (query, row, score bits): staged hits
     int* hitn = (int*)(hitq + 8 * kMmaHitQueue);              // [8] entries staged per epilogue warp
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -301,9 +337,12 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
     for (int i = tid; i < kMmaMaxNQ; i += kMmaThreads) {
         tau[i] = 0u;
         tau_f[i] = -INFINITY;
-        // the full pass continues from what the bound-only pass published for this CTA
-        lb[i] = p.mode == 1 ? p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + i] : 0u;
-        lb_f[i] = lb[i] ? order_to_score(lb[i]) : -INFINITY;
+        // Both passes start their own tally: the full pass walks the bound-only pass's tile AGAIN, and a row
+        // offered twice would count as two rows (its score would become the "second best" as well).  What the
+        // bound-only pass found lives on in gbound[], which only rises.
+        lb[i] = 0u;
+        lb2[i] = 0u;
+        lb_f[i] = -INFINITY;
     }
     if (warp == 1) { if constexpr (PAIR) tmem_alloc_pair(tmem_base_s, tmem_cols); else tmem_alloc(tmem_base_s, tmem_cols); }
     tc_fence_before();
@@ -397,22 +436,26 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         }
     } else if (warp == 2) {
         // ============================ bound refresher ============================
-        // tau[q] = min over CTAs of their best score so far for q.  Every CTA holds at least one
-        // row that good, so >= gridDim.x rows of the store reach tau: it can never cut into the
-        // best gridDim.x rows (k + margin is kept below that by the host).
+        // Every CTA tracks its two best scores per query.  The r-th largest of the CTAs' SECOND bests is a
+        // lower bound of the (2r)-th best score of the store (r CTAs hold two rows each at least that good),
+        // and 2r >= need (k for the single-TF32 filter, whose error band hangs below the k-th best; k + margin
+        // for 3xTF32).  Far tighter than the minimum of the CTAs' bests, which the unluckiest CTA sets.
+        // The work is spread: CTA b computes the bound of queries b, b + grid, ... into gbound[] (it only
+        // rises: atomicMax), and every CTA refreshes its thresholds from gbound[] -- 256 loads, not 148 x 256.
         if (p.mode == 1) {
             for (;;) {
-                for (int q = lane; q < p.nq; q += 32) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
+                for (int q = lane; q < p.nq; q += 32) p.lbest2[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb2[q];
+                for (int q = (int)blockIdx.x; q < p.nq; q += (int)gridDim.x) {
+                    const unsigned int v = mma_rth_largest(p.lbest2 + q, (int)gridDim.x, p.r_need, lane, rstage);
+                    if (lane == 0 && v != 0u) atomicMax(p.gbound + q, v);
+                }
                 for (int q = lane; q < p.nq; q += 32) {
-                    unsigned int m = 0xFFFFFFFFu;
-                    for (unsigned b = 0; b < gridDim.x; b++) {
-                        unsigned int v = ((volatile unsigned int*)p.lbest)[(size_t)b * kMmaMaxNQ + q];
-                        m = v < m ? v : m;
-                    }
+                    unsigned int m = ((volatile unsigned int*)p.gbound)[q];
+                    if (m == 0u) continue;                       // no bound yet
                     // admit everything within 2 eps below the bound (eps = 0 when the filter is 3xTF32)
                     const float e2 = p.eps ? 2.0f * p.eps[q] : 0.0f;
-                    if (e2 > 0.0f && m != 0u && m != 0xFFFFFFFFu) m = score_to_order(order_to_score(m) - e2);
-                    if (m != 0xFFFFFFFFu && m > tau[q]) {
+                    if (e2 > 0.0f) m = score_to_order(order_to_score(m) - e2);
+                    if (m > tau[q]) {
                         ((volatile unsigned int*)tau)[q] = m;
                         ((volatile float*)tau_f)[q] = order_to_score(m);
                     }
@@ -441,9 +484,13 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         auto on_hit = [&](int q, uint32_t row, float sc) {
             if (q >= p.nq) return;
             const unsigned int o = score_to_order(sc);
-            if (o > ((volatile unsigned int*)lb)[q]) {
-                const unsigned int old = atomicMax(lb + q, o);
-                ((volatile float*)lb_f)[q] = order_to_score(old > o ? old : o);
+            if (o > ((volatile unsigned int*)lb2)[q]) {
+                // keep the CTA's two best: the new best goes to lb, whichever of (old best, this score) is not
+                // the best any more is offered to lb2.  Every score but the largest ends up offered to lb2.
+                const unsigned int old1 = atomicMax(lb + q, o);
+                const unsigned int lower = old1 < o ? old1 : o;
+                const unsigned int old2 = atomicMax(lb2 + q, lower);
+                ((volatile float*)lb_f)[q] = order_to_score(old2 > lower ? old2 : lower);
             }
             if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
                 // A global atomic per hit would stall the warp ~1 us each time (its result is needed for the
@@ -523,7 +570,7 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         }
         // publish this CTA's bests (the bound-only pass exists to produce exactly this)
         named_bar_sync(2, kEpiWarps * 32);
-        for (int q = tid - 128; q < p.nq; q += kEpiWarps * 32) p.lbest[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb[q];
+        for (int q = tid - 128; q < p.nq; q += kEpiWarps * 32) p.lbest2[(size_t)blockIdx.x * kMmaMaxNQ + q] = lb2[q];
         if (tid == 128) flags[0] = 1;
     } else if (TERMS == 3 && warp >= 8) {
         // ============================ converters (3xTF32 only) ============================

@@ -1033,13 +1033,14 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     const int dim = s->dim;
     const int nqp = (g + 15) & ~15;
     const int terms = tuning().mma_terms;
-    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 3 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
+    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 4 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
     if (c->mma_qsplit.reserve((size_t)2 * kMmaMaxNQ * dim * 4 + 256) || c->mma_cand.reserve((size_t)kMmaMaxNQ * kMmaCandCap * 8) ||
         c->mma_small.reserve(small_bytes) || c->h_status.reserve(kMmaMaxNQ * 4)) return -1;
-    unsigned int* cand_cnt = c->mma_small.as<unsigned int>();
-    int* status = (int*)(cand_cnt + kMmaMaxNQ);
+    unsigned int* cand_cnt = c->mma_small.as<unsigned int>();     // cand_cnt and gbound are adjacent: one memset per batch
+    unsigned int* gbound = cand_cnt + kMmaMaxNQ;
+    int* status = (int*)(gbound + kMmaMaxNQ);
     float* eps = (float*)(status + kMmaMaxNQ);
-    unsigned int* lbest = (unsigned int*)(eps + kMmaMaxNQ);
+    unsigned int* lbest2 = (unsigned int*)(eps + kMmaMaxNQ);
     float* qs = c->mma_qsplit.as<float>();
     if (terms == 1) {
         // |approx - exact| <= (2^-9 + D 2^-23) |q| |k|: TF32 drops < 2^-10 of each operand, the D term covers the
@@ -1056,7 +1057,7 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(
         sp.q + (size_t)q0 * dim, g, nqp, dim, qs);
     CU_OK(cudaGetLastError());
-    CU_OK(cudaMemsetAsync(cand_cnt, 0, (size_t)kMmaMaxNQ * 4, c->stream));
+    CU_OK(cudaMemsetAsync(cand_cnt, 0, (size_t)2 * kMmaMaxNQ * 4, c->stream));   // candidate counts and grid-wide bounds
 
     if (get_encoder()) return -2;
     // CTA pairs (cta_group::2): each CTA of a pair stages half of the query tile, so the box is half as tall
@@ -1078,7 +1079,12 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     mp.box_cols = bc;
     const CUtensorMap& tmap_keys = bc == 32 ? s->tmap : s->tmap_mma;   // the exact scan's [32 x 128] / 128-B-swizzle map serves here too
     mp.nq = g; mp.nqp = nqp; mp.f64 = norm ? 0 : 1;
-    mp.knorm = sp.knorm; mp.lbest = lbest; mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
+    mp.knorm = sp.knorm; mp.lbest2 = lbest2; mp.gbound = gbound;
+    mp.cand = c->mma_cand.as<uint64_t>(); mp.cand_cnt = cand_cnt;
+    // rows that must reach the bound: the k-th best for the single-TF32 filter (its error band hangs below
+    // that score), the (k + margin)-th for 3xTF32 (exactly that many are re-scored); two rows per CTA
+    const int need = terms == 1 ? sp.topk : sp.topk + kMmaMargin;
+    mp.r_need = (need + 1) / 2;
     mp.refresh_ns = 5000;
     mp.eps = terms == 1 ? eps : nullptr;
     mp.debug = tuning().mma_debug;
@@ -1107,6 +1113,8 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     };
     mp.mode = 0;   // bound-only pass: one tile per CTA, so that every CTA owns a published best per query
     if (launch_pass()) return -1;
+    mma_bound_kernel<<<(g + 7) / 8, 256, 0, c->stream>>>(lbest2, grid, mp.r_need, g, gbound);
+    CU_OK(cudaGetLastError());
     mp.mode = 1;
     if (launch_pass()) return -1;
 
@@ -1127,7 +1135,7 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
         else      mma_finalize_kernel<true, 1><<<g, kFinThreads, kFinDynSmem, c->stream>>>(fp);
     }
     CU_OK(cudaGetLastError());
-    c->launches += 4;
+    c->launches += 5;
     c->mma_passes++;
     // the status decides whether a query must be re-run exactly; this is the one place a launch waits
     CU_OK(cudaMemcpyAsync(c->h_status.p, status, (size_t)g * 4, cudaMemcpyDeviceToHost, c->stream));

@@ -26,7 +26,8 @@ def run_batch(tfp, oracle, K, Q, k, normalized, expect_mma=True):
     return passes, reruns
 
 
-@pytest.mark.parametrize("nq,d,k", [(5, 64, 10), (17, 160, 3), (32, 256, 10), (64, 768, 10), (200, 128, 100), (256, 64, 100), (300, 96, 7)])
+@pytest.mark.parametrize("nq,d,k", [(5, 64, 10), (17, 160, 3), (32, 256, 10), (64, 768, 10), (200, 128, 100), (256, 64, 100), (300, 96, 7),
+                                    (64, 128, 1), (256, 256, 3), (100, 64, 2)])   # small k: the grid-wide bound sits right at the answer
 def test_mma_path_matches_oracle_normalized(tfp, oracle, nq, d, k):
     K = make_keys(70000, d, seed=nq + d, normalized=True)
     Q = make_keys(nq, d, seed=nq + d + 1, normalized=True)
