@@ -104,7 +104,7 @@ int tfp_store_find(tfp_store* s, const float* q, int dim, int topk,
 
 /* nq independent finds that share passes over the keys.  Same per-query results
  * as nq calls of tfp_store_find (bit-identical similarities).  Up to 4 same-path
- * queries share one pass of the exact scan kernel; 5 or more on a store of
+ * queries share one pass of the exact scan kernel; 3 or more on a store of
  * >= 65536 rows (topk <= 100) go through the tensor cores in groups of up to 256
  * (TF32 filter + exact re-score, mma_scan.cuh).  Replaces nq sequential
  * Store.StoresFind calls (the reference has no batch RPC).
@@ -169,7 +169,7 @@ int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d
  * address: [count x stride x dim] floats, stride as returned by
  * tfp_find_ctx_device_results (what StoresFindResult.Keys is built from). */
 int  tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys);
-/* How often this context took the tensor-core path (batches of >= 5 same-path queries on a
+/* How often this context took the tensor-core path (batches of >= 3 same-path queries on a
  * store of >= 65536 rows: tcgen05 3xTF32 filter + exact re-score) and how many queries it then had to
  * re-run on the exact scan kernel.  Either pointer may be NULL. */
 int  tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64_t* exact_reruns);
@@ -217,7 +217,7 @@ int tfp_find_ctx_comm_init(tfp_find_ctx* c, const void* unique_id, int rank, int
 int tfp_find_ctx_comm_share(tfp_find_ctx* c, tfp_find_ctx* owner);
 int tfp_find_ctx_launch_sharded(tfp_find_ctx* c, int qi, int topk);
 /* Same for staged queries [first, first+count): one all-gather of count records, one merge CTA per
- * query.  Batches of >= 5 same-path queries take the tensor-core path on every shard. */
+ * query.  Batches of >= 3 same-path queries take the tensor-core path on every shard. */
 int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int count, int topk);
 int tfp_find_ctx_merged_results(tfp_find_ctx* c, float** d_sims, int64_t** d_ids, int** d_shard,
                                 int** d_index, int** d_n);

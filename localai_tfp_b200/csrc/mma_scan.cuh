@@ -1,6 +1,6 @@
 // mma_scan.cuh -- batched StoresFind on the 5th-generation tensor cores (tcgen05 + TMEM).
 //
-// For batches of queries (5 or more: the measured break-even) the scan is a dense contraction S = K . Q^T
+// For batches of queries (3 or more: the measured break-even) the scan is a dense contraction S = K . Q^T
 // (K: [rows x D] keys, Q: [nq x D] queries).  It replaces nq sequential runs of the
 // reference loop (backend/go/stores/store.go:378-389 / :441-452) -- the reference has no
 // batched path at all.

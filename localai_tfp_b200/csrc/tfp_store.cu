@@ -114,7 +114,7 @@ static int get_encoder() {
 struct Tuning {
     int refresh_ns = 4000;
     bool disable_lbest = false;
-    int mma_min_queries = 5;       // batches at least this large go to the tensor-core path (measured break-even)
+    int mma_min_queries = 3;       // batches at least this large go to the tensor-core path (measured break-even: 531 us per batch vs 896 us for 2 + 1 exact scans on 1M x 768)
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
     bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)

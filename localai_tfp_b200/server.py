@@ -35,7 +35,7 @@ def _ident(b):
 class _FindBatcher:
     """Concurrent StoresFind requests become ONE batched find ("micro-batcher for concurrent
     StoresFind").  Whatever has queued up while the previous batch ran is taken together, grouped by
-    top-k; 5 or more same-path queries on a large store ride the tensor-core path.  A lone request is
+    top-k; 3 or more same-path queries on a large store ride the tensor-core path.  A lone request is
     served at once: nothing waits for company."""
 
     def __init__(self, backend: "Backend", max_batch: int = 256):

@@ -1,4 +1,4 @@
-"""The tensor-core path (5 or more same-path queries on a store of >= 65536 rows): tcgen05 TF32 filter
+"""The tensor-core path (3 or more same-path queries on a store of >= 65536 rows): tcgen05 TF32 filter
 + exact re-score.  Results must be what nq single finds return: similarities bit-identical to the oracle."""
 import numpy as np
 import pytest
@@ -85,7 +85,7 @@ def test_mma_path_mixed_paths_split_into_runs(tfp, oracle):
 
 def test_small_batches_and_small_stores_stay_on_the_exact_kernel(tfp, oracle):
     K = make_keys(70000, 64, seed=31, normalized=True)
-    Q = make_keys(4, 64, seed=32, normalized=True)
+    Q = make_keys(2, 64, seed=32, normalized=True)
     passes, _ = run_batch(tfp, oracle, K, Q, 10, True, expect_mma=False)
     assert passes == 0
     K = make_keys(5000, 64, seed=33, normalized=True)
