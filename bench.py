@@ -211,15 +211,11 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     if sharded is not None:
         sharded.key_len = DIM
         if args.exchange == "p2p":              # the scan kernel pushes its records to the peers over NVLink
-            ok = True
             try:
-                ops.init_p2p(rank, world)
+                ops.init_p2p(rank, world)       # all ranks succeed or all ranks raise (it agrees step by step)
             except Exception as e:
-                ok = False
-                print(f"bench[{rank}]: peer exchange unavailable ({e})", file=sys.stderr)
-            flags = [None] * world
-            dist.all_gather_object(flags, ok)
-            if not all(flags):                  # every rank must take the same path
+                if rank == 0:
+                    print(f"bench: {e}; falling back to ncclAllGather", file=sys.stderr)
                 args.exchange = "native"
         if args.exchange in ("native", "native-per-lane"):   # scan + ncclAllGather + merge in one library call
             try:

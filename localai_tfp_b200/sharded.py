@@ -175,11 +175,35 @@ class CudaShardOps:
         """Peer exchange: every lane's gather block is mapped into every rank (cudaIpc handles travel
         over torch.distributed); after this find_merged() is ONE library call whose scan kernel pushes
         the records to the peers over NVLink -- no collective call, no extra kernel per find."""
+        # Every step is agreed on by all ranks before the next one (a rank that fails alone would leave the
+        # others waiting in a collective): either every rank ends up attached on every lane, or none does.
+        def agree(step, err):
+            errs = [None] * world
+            dist.all_gather_object(errs, err, group=group)
+            bad = [f"rank {r}: {e}" for r, e in enumerate(errs) if e]
+            if bad:
+                for ln in self.lanes:
+                    try:
+                        ln.ctx.p2p_detach()
+                    except Exception:
+                        pass
+                raise StoreError(f"peer exchange unavailable ({step}): " + "; ".join(bad))
+
         for lane in self.lanes:
-            mine = lane.ctx.p2p_export(world, slot_bytes)
+            mine, err = None, None
+            try:
+                mine = lane.ctx.p2p_export(world, slot_bytes)
+            except Exception as e:
+                err = str(e)
+            agree("export", err)
             handles = [None] * world
             dist.all_gather_object(handles, mine, group=group)
-            lane.ctx.p2p_attach(b"".join(handles), rank, world)
+            err = None
+            try:
+                lane.ctx.p2p_attach(b"".join(handles), rank, world)
+            except Exception as e:
+                err = str(e)
+            agree("attach", err)
         dist.barrier(group=group)      # nobody launches before everybody has attached
         self.native = True
         self.p2p = True
