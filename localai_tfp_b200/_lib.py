@@ -42,7 +42,7 @@ PROTOTYPES = {
     "tfp_store_default_ctx": (vp, [vp]),
     "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_destroy": (None, [vp]),
-    "tfp_find_ctx_upload": (C.c_int, [vp, fp, C.c_int, C.c_int]),
+    "tfp_find_ctx_upload": (C.c_int, [vp, vp, C.c_int, C.c_int]),                       # per-query path: plain addresses
     "tfp_find_ctx_launch": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
     "tfp_find_ctx_download": (C.c_int, [vp, i32p, i64p, fp, fp]),
     "tfp_find_ctx_sync": (C.c_int, [vp]),
@@ -66,7 +66,7 @@ PROTOTYPES = {
     "tfp_find_ctx_p2p_detach": (C.c_int, [vp]),
     "tfp_p2p_slot_bytes_with_keys": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "tfp_find_ctx_launch_sharded_keys": (C.c_int, [vp, C.c_int, C.c_int, C.c_int]),
-    "tfp_find_ctx_download_merged_keys": (C.c_int, [vp, i32p, i64p, fp, fp]),
+    "tfp_find_ctx_download_merged_keys": (C.c_int, [vp, vp, vp, vp, vp]),             # per-query path: plain addresses
     "tfp_host_alloc": (vp, [C.c_size_t]),
     "tfp_host_free": (None, [vp]),
     "tfp_scan_topk_noalloc": (C.c_int, [vp, C.c_int64, C.c_int, vp, vp, C.c_int, vp, vp, vp, vp]),

@@ -392,7 +392,7 @@ class ShardedStore:
             got = self.ops.find_host(q, int(topk))     # peer exchange: three library calls, one D2H copy
             if got is not None:
                 ids_h, sims_h, keys_h = got
-                return [r.copy() for r in keys_h], [self.values.get(int(i)) for i in ids_h], sims_h
+                return list(keys_h), [self.values.get(i) for i in ids_h.tolist()], sims_h
         self.ops.stage_queries(q[None, :])
         sims, ids, shard, index, n, g_keys = self.find_device(0, int(topk), with_keys)
         with self.ops.stream():

@@ -268,7 +268,7 @@ class FindContext:
         if qs.ndim == 1:
             qs = qs[None, :]
         self.nq, self.dim = qs.shape
-        self.store._check(self._L.tfp_find_ctx_upload(self._h, _p(qs, fp), self.nq, self.dim))
+        self.store._check(self._L.tfp_find_ctx_upload(self._h, _addr(qs), self.nq, self.dim))
 
     def launch(self, first: int, count: int, topk: int):
         self.store._check(self._L.tfp_find_ctx_launch(self._h, first, count, topk))
@@ -339,9 +339,8 @@ class FindContext:
         n = np.empty(cnt, np.int32)
         ids = np.empty((cnt, k), np.int64); sims = np.empty((cnt, k), np.float32)
         keys = np.empty((cnt, k, dim), np.float32)
-        self.store._check(self._L.tfp_find_ctx_download_merged_keys(self._h, _p(n, i32p), _p(ids, i64p), _p(sims, fp),
-                                                                    _p(keys, fp)))
-        out = [(ids[i, :n[i]].copy(), sims[i, :n[i]].copy(), keys[i, :n[i]].copy()) for i in range(cnt)]
+        self.store._check(self._L.tfp_find_ctx_download_merged_keys(self._h, _addr(n), _addr(ids), _addr(sims), _addr(keys)))
+        out = [(ids[i, :n[i]], sims[i, :n[i]], keys[i, :n[i]]) for i in range(cnt)]   # views of this call's own buffers
         return out[0] if cnt == 1 else out
 
     def launch_sharded(self, qi: int, topk: int, count: int = 1):
