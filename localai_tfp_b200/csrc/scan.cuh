@@ -87,6 +87,7 @@ struct ScanParams {
     int rec_bytes;
     int rec_topk;
     XchgParams xchg;          // fused push of the finished records to the peer ranks (world == 0: off)
+    float* out_keys;          // [* x topk x dim] the winning key rows (StoresFindResult.Keys), or nullptr: gathered by a later kernel
 };
 
 // Copy `bytes` (a multiple of 16) of finished records from local memory to the same offset of this
@@ -407,6 +408,23 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
                 p.out_sims[at] = 0.0f;
                 p.out_slots[at] = 0xFFFFFFFFu;
                 p.out_ids[at] = -1;
+            }
+        }
+        if (p.out_keys) {
+            // the reply wants the winning rows (store.go:399-401): copy them here and save the host a kernel launch
+            float* dst = p.out_keys + (size_t)o * k * p.dim;
+            if ((p.dim & 3) == 0) {
+                const int n4 = p.dim >> 2;
+                for (int e = tid; e < m * n4; e += kSelThreads) {
+                    const int i = e / n4, c4 = e - i * n4;
+                    const float4* src = reinterpret_cast<const float4*>(p.keys + (size_t)cand_slot(ms.buf[i]) * p.dim);
+                    reinterpret_cast<float4*>(dst + (size_t)i * p.dim)[c4] = __ldcs(src + c4);
+                }
+            } else {
+                for (int e = tid; e < m * p.dim; e += kSelThreads) {
+                    const int i = e / p.dim, cc = e - i * p.dim;
+                    dst[(size_t)i * p.dim + cc] = p.keys[(size_t)cand_slot(ms.buf[i]) * p.dim + cc];
+                }
             }
         }
         if (tid == 0) {

@@ -314,6 +314,7 @@ struct tfp_find_ctx {
     unsigned int x_seq = 0;
     bool x_ready = false;
     bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
+    bool keys_gathered = false;          // the last launch's scan kernels wrote the winning key rows themselves
     int64_t mma_passes = 0, mma_fallbacks = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
@@ -1154,9 +1155,13 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
 // Enqueue the scan(s) for staged queries [first, first+count).  Caller holds the shared lock.
 // xchg: push the finished records to the peer ranks from inside the scan kernel when the find is
 // made of exact fused scans only (c->x_pushed tells the caller whether that happened).
-static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, const XchgParams* xchg = nullptr) {
+// want_keys: the caller will ask for the key rows; exact fused scans then write them from their last CTA
+// (c->keys_gathered), other paths leave them to gather_rows_kernel.
+static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, const XchgParams* xchg = nullptr,
+                             bool want_keys = false) {
     tfp_store* s = c->st;
     c->x_pushed = false;
+    c->keys_gathered = false;
     if (c->dim != s->dim)                                                            // store.go:480-482
         return fail(1, "Try to find key with length %d when existing length is %d", c->dim, s->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
@@ -1289,9 +1294,14 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
     const bool mma_ok = fused && s->tmap_ok && ksel <= kMmaMaxTopK && grid >= ksel + kMmaMargin &&
                         n >= tuning().mma_min_rows && tuning().mma_min_queries > 0 &&
                         mma_stage_count(kMmaMaxNQ, 3, (size_t)s->max_smem) >= 3;
-    if (xchg && fused && !(mma_ok && count >= tuning().mma_min_queries)) {
+    const bool all_exact_fused = fused && !(mma_ok && count >= tuning().mma_min_queries);
+    if (xchg && all_exact_fused) {
         p.xchg = *xchg;     // every launch below is an exact fused scan: each pushes its own records
         c->x_pushed = true;
+    }
+    if (want_keys && all_exact_fused && (size_t)ksel == (size_t)c->last_stride) {
+        p.out_keys = c->out_keys;   // ... and each copies its winners' rows
+        c->keys_gathered = true;
     }
     int i = 0;
     while (i < count) {
@@ -1360,7 +1370,7 @@ static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, fl
     if (c->h_out.reserve(total)) return -1;
     uint8_t* h = (uint8_t*)c->h_out.p;
     if (s->n > 0) {
-        if (out_keys && ctx_gather_locked(c)) return -1;
+        if (out_keys && !c->keys_gathered && ctx_gather_locked(c)) return -1;
         CU_OK(cudaMemcpyAsync(h, c->out_block.p, total, cudaMemcpyDeviceToHost, c->stream));
     }
     CU_OK(cudaStreamSynchronize(c->stream));
@@ -1439,7 +1449,7 @@ extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int di
     tfp_find_ctx* c = s->default_ctx;
     int rc = ctx_upload_locked(c, q, nq, dim);
     if (rc) return rc;
-    rc = ctx_launch_locked(c, 0, nq, topk);
+    rc = ctx_launch_locked(c, 0, nq, topk, nullptr, out_keys != nullptr);
     if (rc) return rc;
     return ctx_download_locked(c, out_n, out_ids, out_sims, out_keys);
 }
