@@ -68,3 +68,41 @@ def test_sharded_store_world2_nccl(tfp):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     mp.spawn(sharded_worker.run, args=(2, free_port(), "nccl"), nprocs=2, join=True)
+
+
+@pytest.mark.gpu
+def test_peer_exchange_argument_errors_leave_the_context_usable(tfp):
+    """The peer-exchange set-up on ONE GPU: every misuse is a clean error (no hang, nothing half set up),
+    and the find context keeps serving ordinary finds afterwards."""
+    from conftest import make_keys
+    K = make_keys(500, 32, seed=3, normalized=True)
+    s = tfp.Store()
+    s.StoresSet(K, [b""] * len(K))
+    c = s.find_context()
+    c.upload(K[:2])
+    for world, slot, text in ((1, 1 << 16, "world = 1 outside [2, 8]"), (9, 1 << 16, "world = 9 outside [2, 8]"),
+                              (2, 16, "slot_bytes outside [256, 64 MiB]")):
+        with pytest.raises(tfp.StoreError) as e:
+            c.p2p_export(world, slot)
+        assert text in str(e.value)
+    with pytest.raises(tfp.StoreError) as e:            # neither a peer exchange nor a communicator
+        c.launch_sharded(0, 5)
+    assert "tfp_find_ctx_p2p_attach or tfp_find_ctx_comm_init first" in str(e.value)
+    with pytest.raises(tfp.StoreError) as e:            # attach before export
+        c.p2p_attach(bytes(128), 0, 2)
+    assert "tfp_find_ctx_p2p_export with the same world first" in str(e.value)
+    handle = c.p2p_export(2, 1 << 16)
+    assert len(handle) == 64
+    with pytest.raises(RuntimeError) as e:              # rank 1's handle is garbage: the mapping must fail (a device-side
+        c.p2p_attach(handle + bytes(64), 0, 2)          # failure, code < 0), not crash
+    assert "cudaIpcOpenMemHandle" in str(e.value)
+    with pytest.raises(tfp.StoreError):                 # still not attached
+        c.launch_sharded(0, 5)
+    with pytest.raises(tfp.StoreError) as e:
+        c.launch_sharded_keys(0, 5)
+    assert "tfp_find_ctx_p2p_attach first" in str(e.value)
+    c.p2p_detach()
+    c.launch(0, 2, 5)                                   # the context is intact
+    res = c.download()
+    assert res[0][0][0] == 0 and res[1][0][0] == 1
+    c.close(); s.close()
