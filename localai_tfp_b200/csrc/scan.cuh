@@ -335,6 +335,8 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
     named_bar_sync(kSelBarrier, kSelThreads);
     if (*flag == 0) return;
     __threadfence();
+    unsigned long long* lstamp = p.dbg_times ? p.dbg_times + (size_t)kMaxGrid * 4 : nullptr;   // development: the last CTA's phases
+    if (lstamp && tid == 0) lstamp[0] = globaltimer_ns();
 
     // 2. last CTA: merge every CTA's published survivors, its own included (they are in `part` like
     // everybody's).  Its tau is a valid lower bound of the k-th best and may BE a row of the answer
@@ -370,13 +372,15 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         }
         named_bar_sync(kSelBarrier, kSelThreads);
         const int total = pref[grid];
+        if (lstamp && tid == 0 && q == 0) { lstamp[1] = globaltimer_ns(); lstamp[5] = (unsigned long long)total; }
         // merge buffer: everything in ONE round in the lent buffer when it fits, else rounds in the
         // query's own buffer (a huge survivor count means the bounds did not bite; rounds keep the
         // sorts small)
         SelState ms = sel[q];
         ms.gtau = nullptr; ms.lbest = nullptr; ms.lmax = nullptr;
         if (big_buf && big_cap >= 2 * sel[q].cap && total <= big_cap / 4) {
-            ms.buf = big_buf; ms.cap = big_cap; ms.room = big_cap - k;
+            ms.buf = big_buf; ms.cap = big_cap;
+            ms.room = total > 0 ? total : 1;      // everything fits: one round, no prune before the final one
         }
         const int room = ms.room;
         for (int base = 0; base < total; base += room) {
@@ -389,7 +393,9 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             named_bar_sync(kSelBarrier, kSelThreads);
             sel_maybe_prune(ms, tid, false);
         }
+        if (lstamp && tid == 0 && q == 0) lstamp[2] = globaltimer_ns();
         sel_prune(ms, tid, false);
+        if (lstamp && tid == 0 && q == 0) lstamp[3] = globaltimer_ns();
         int m = *ms.cnt;
         const int o = p.out_first + q;
         for (int i = tid; i < k; i += kSelThreads) {
@@ -437,6 +443,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         named_bar_sync(kSelBarrier, kSelThreads);
     }
     if (tid == 0) { *p.ticket = 0u; *p.tile_counter = 0u; }
+    if (lstamp && tid == 0) lstamp[4] = globaltimer_ns();
     if (p.xchg.world > 0) {
         // this launch's records are final (the loop above ended on a barrier): push them to the peers
         const size_t off = (size_t)p.out_first * p.rec_bytes;

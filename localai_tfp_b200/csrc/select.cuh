@@ -56,15 +56,46 @@ __device__ __forceinline__ void sel_sort_desc(uint64_t* buf, int P, int tid) {
     }
 }
 
+// Rank sort for short lists: every word's place is the number of words larger than it (the words are
+// unique: a row appears once), so the best k land in order with two barriers instead of one per bitonic
+// stage -- the per-stage barrier is what a sort of a few dozen words by 128 threads spends its time on.
+template <int SLOTS>
+__device__ __forceinline__ void sel_rank_sort(const SelState& s, int n, int tid) {
+    uint64_t v[SLOTS];
+    int rk[SLOTS];
+#pragma unroll
+    for (int e = 0; e < SLOTS; e++) {
+        const int i = tid + e * kSelThreads;
+        v[e] = i < n ? s.buf[i] : ~0ull;      // a padding slot outranks everything: it never counts, never lands
+        rk[e] = 0;
+    }
+    for (int j = 0; j < n; j++) {
+        const uint64_t w = s.buf[j];          // same address for the whole warp: a broadcast
+#pragma unroll
+        for (int e = 0; e < SLOTS; e++) rk[e] += (w > v[e]) ? 1 : 0;
+    }
+    named_bar_sync(kSelBarrier, kSelThreads);  // every read is done before the first word moves
+#pragma unroll
+    for (int e = 0; e < SLOTS; e++)
+        if (tid + e * kSelThreads < n && rk[e] < s.k) s.buf[rk[e]] = v[e];
+    named_bar_sync(kSelBarrier, kSelThreads);
+}
+
 // Keep the best k of buf[0..cnt); raise tau; publish this CTA's bounds.
 // Must be called by all kSelThreads threads with a uniform view of *cnt.
 __device__ __forceinline__ void sel_prune(const SelState& s, int tid, bool publish) {
-    int n = *s.cnt;
-    int P = 2;
-    while (P < n) P <<= 1;
-    for (int i = n + tid; i < P; i += kSelThreads) s.buf[i] = 0ull;
-    named_bar_sync(kSelBarrier, kSelThreads);
-    sel_sort_desc(s.buf, P, tid);
+    int n = *s.cnt;                            // (thread 0 rewrites it only after the barriers of the sort)
+    if (n <= kSelThreads) {
+        sel_rank_sort<1>(s, n, tid);
+    } else if (n <= 4 * kSelThreads) {
+        sel_rank_sort<4>(s, n, tid);
+    } else {
+        int P = 2;
+        while (P < n) P <<= 1;
+        for (int i = n + tid; i < P; i += kSelThreads) s.buf[i] = 0ull;
+        named_bar_sync(kSelBarrier, kSelThreads);
+        sel_sort_desc(s.buf, P, tid);
+    }
     if (tid == 0) {
         int m = n < s.k ? n : s.k;
         unsigned long long t = *s.tau;

@@ -1220,8 +1220,8 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
     p.refresh_ns = tuning().refresh_ns;
     if (tuning().disable_lbest) p.lbest = nullptr;
     if (tuning().scan_times) {   // development: per-CTA time stamps of the next scan, printed by tfp_find_ctx_sync
-        if (c->dbg_times.reserve((size_t)kMaxGrid * 4 * 8)) return -1;
-        CU_OK(cudaMemsetAsync(c->dbg_times.p, 0, (size_t)kMaxGrid * 4 * 8, c->stream));
+        if (c->dbg_times.reserve((size_t)(kMaxGrid * 4 + 8) * 8)) return -1;
+        CU_OK(cudaMemsetAsync(c->dbg_times.p, 0, (size_t)(kMaxGrid * 4 + 8) * 8, c->stream));
         p.dbg_times = c->dbg_times.as<unsigned long long>();
         c->dbg_grid = grid;
     }
@@ -1412,6 +1412,12 @@ extern "C" int tfp_find_ctx_sync(tfp_find_ctx* c) {
                         "kernel end %.1f | tiles per CTA %llu..%llu\n",
                 (start_max - t0) / 1e3, (s_min - t0) / 1e3, s_sum / c->dbg_grid / 1e3, (s_max - t0) / 1e3, (e_max - t0) / 1e3,
                 tl_min, tl_max);
+        unsigned long long ls[8];
+        CU_OK(cudaMemcpy(ls, c->dbg_times.as<unsigned long long>() + (size_t)kMaxGrid * 4, sizeof(ls), cudaMemcpyDeviceToHost));
+        if (ls[0])
+            fprintf(stderr, "tfp last CTA (us from first CTA start): ticket %.1f | lists counted %.1f (%llu words) | merged %.1f | "
+                            "sorted %.1f | written %.1f\n",
+                    (ls[0] - t0) / 1e3, (ls[1] - t0) / 1e3, ls[5], (ls[2] - t0) / 1e3, (ls[3] - t0) / 1e3, (ls[4] - t0) / 1e3);
         c->dbg_grid = 0;
     }
     return 0;
