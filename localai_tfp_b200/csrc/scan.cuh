@@ -382,6 +382,15 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
             ms.buf = big_buf; ms.cap = big_cap;
             ms.room = total > 0 ? total : 1;      // everything fits: one round, no prune before the final one
         }
+        // Many survivors mean the CTAs finished before a grid-wide bound had formed (a store of one or two tiles
+        // per CTA): fold in the bound their final bests give now, so that the offers below are a handful.
+        if (p.lbest && total > kSelThreads && ms.buf == big_buf && big_cap / 2 >= grid) {
+            if (tid < 32) {
+                const unsigned long long v = lbest_rth(p, q, tid, (unsigned long long*)(big_buf + big_cap / 2));
+                if (tid == 0 && v > 0ull && v - 1 > *ms.tau) *ms.tau = v - 1;   // v may BE a row of the answer: admit >= v
+            }
+            named_bar_sync(kSelBarrier, kSelThreads);
+        }
         const int room = ms.room;
         for (int base = 0; base < total; base += room) {
             const int stop = base + room < total ? base + room : total;
