@@ -122,12 +122,39 @@ __global__ void gather_rows_kernel(const float* __restrict__ keys, int dim, cons
 // n_shards x topk words (sim order, then lower shard, then position).  Input is the
 // gathered block of packed records: shard sh's nq records (rec_bytes each) start at sh * shard_stride
 // bytes.  Read with ld.cg: with the peer exchange the records were written by other GPUs over NVLink.
+// wait_words != nullptr (peer exchange): the kernel itself waits until every peer's sequence word has
+// reached wait_seq -- the peers' scan kernels raise them with st.release.sys after their records have
+// landed -- so a sharded find is the scan plus THIS one launch, with no stream wait operations in
+// between.  The CTA is small (no dynamic shared memory to speak of), so it co-resides with the scan
+// CTAs of the other lanes while it waits.
 __global__ void merge_records_kernel(const uint8_t* g, int rec_bytes, size_t shard_stride, int n_shards, int nq, int topk, int P,
                                      float* __restrict__ o_sims, int64_t* __restrict__ o_ids,
-                                     int* __restrict__ o_shard, int* __restrict__ o_index, int* __restrict__ o_n) {
+                                     int* __restrict__ o_shard, int* __restrict__ o_index, int* __restrict__ o_n,
+                                     const unsigned int* wait_words, int wait_me, unsigned int wait_seq) {
     extern __shared__ uint64_t mbuf[];
     const int q = blockIdx.x;
     const int total = n_shards * topk;
+    if (wait_words) {
+        if ((int)threadIdx.x < n_shards && (int)threadIdx.x != wait_me) {
+            const unsigned int* w = wait_words + threadIdx.x;
+            unsigned int v;
+            unsigned long long t0 = 0ull;
+            for (;;) {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+                if ((int)(v - wait_seq) >= 0) break;
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0ull) t0 = now;
+                else if (now - t0 > 10000000000ull) {   // 10 s: a peer never ran this find (the ranks' call sequences differ)
+                    printf("tfp: sharded find timed out waiting for the records of rank %d (seq %u, saw %u)\n",
+                           (int)threadIdx.x, wait_seq, v);
+                    __trap();
+                }
+                __nanosleep(200);
+            }
+        }
+        __syncthreads();
+    }
     auto rec = [&](int sh) { return g + (size_t)sh * shard_stride + (size_t)q * rec_bytes; };
     for (int i = threadIdx.x; i < P; i += blockDim.x) {
         uint64_t w = 0ull;

@@ -121,6 +121,8 @@ struct Tuning {
     int mma_debug = 0;             // development timing only (results wrong): 1 no epilogue hits, 2 no MMAs
     bool mma_trace = false;        // print the tensor-core launch shape
     bool scan_times = false;       // per-CTA time stamps of every exact scan, printed by tfp_find_ctx_sync
+    int scan_stages = 0;           // cap on the exact scan's TMA ring depth (0 = as many as fit): fewer stages let two CTAs share an SM
+    bool xchg_stream_wait = false; // peer exchange: wait for the peers' words with stream memory operations instead of inside the merge kernel
 };
 static const Tuning& tuning() {
     static Tuning t = [] {
@@ -134,6 +136,8 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_MMA_DEBUG")) x.mma_debug = atoi(e);
         x.mma_trace = getenv("TFP_MMA_TRACE") != nullptr;
         x.scan_times = getenv("TFP_SCAN_TIMES") != nullptr;
+        if (const char* e = getenv("TFP_SCAN_STAGES")) x.scan_stages = atoi(e);
+        if (const char* e = getenv("TFP_XCHG_STREAM_WAIT")) x.xchg_stream_wait = atoi(e) != 0;
         return x;
     }();
     return t;
@@ -1249,6 +1253,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
                 size_t fixed = scan_smem_bytes(0, g, dpad, cap) + 2 * kMaxStages * 8;
                 int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
                 n_stages = std::min(kMaxStages, room);
+                if (tuning().scan_stages >= 3) n_stages = std::min(n_stages, tuning().scan_stages);
                 if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, dpad, cap); break; }
                 if (g > 1) { g >>= 1; continue; }
                 use_tma = false;
@@ -1493,7 +1498,7 @@ extern "C" int tfp_merge_records(const void* d_gathered, int n_shards, int nq, i
     merge_records_kernel<<<nq, 256, (size_t)P * 8, (cudaStream_t)stream>>>((const uint8_t*)d_gathered,
                                                                            (int)record_bytes(topk),
                                                                            record_bytes(topk) * (size_t)nq, n_shards, nq, topk, P,
-                                                                           o_sims, o_ids, o_shard, o_index, o_n);
+                                                                           o_sims, o_ids, o_shard, o_index, o_n, nullptr, 0, 0u);
     CU_OK(cudaGetLastError());
     return 0;
 }
@@ -1805,7 +1810,9 @@ struct MergedLayout {   // [count x topk] sims f32 | ids i64 | shard i32 | index
     }
 };
 
-static int launch_merge(tfp_find_ctx* c, const uint8_t* gathered, size_t shard_stride, size_t rb, int world, int count, int k) {
+// wait_words: the peers' sequence words the merge kernel itself waits on (peer exchange), or nullptr.
+static int launch_merge(tfp_find_ctx* c, const uint8_t* gathered, size_t shard_stride, size_t rb, int world, int count, int k,
+                        const unsigned int* wait_words = nullptr, int wait_me = 0, unsigned int wait_seq = 0) {
     MergedLayout L(k, count);
     if (c->merged.reserve(L.total)) return -1;
     uint8_t* m = c->merged.as<uint8_t>();
@@ -1814,7 +1821,8 @@ static int launch_merge(tfp_find_ctx* c, const uint8_t* gathered, size_t shard_s
         CU_OK(cudaFuncSetAttribute(merge_records_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P * 8));
     merge_records_kernel<<<count, 256, (size_t)P * 8, c->stream>>>(gathered, (int)rb, shard_stride, world, count, k, P,
                                                                   (float*)(m + L.sims), (int64_t*)(m + L.ids),
-                                                                  (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n));
+                                                                  (int*)(m + L.shard), (int*)(m + L.index), (int*)(m + L.n),
+                                                                  wait_words, wait_me, wait_seq);
     CU_OK(cudaGetLastError());
     c->launches++;
     c->merged_topk = k;
@@ -1856,16 +1864,21 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
         c->launches++;
     }
     unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + flags_off);
-    for (int r = 0; r < c->x_world; r++) {
-        if (r == c->x_me) continue;
-        CUresult wr = g_wait32((CUstream)c->stream, (CUdeviceptr)(words + r), seq, CU_STREAM_WAIT_VALUE_GEQ);
-        if (wr != CUDA_SUCCESS) return fail(-7, "cuStreamWaitValue32 failed with CUresult %d", (int)wr);
+    // The merge kernel waits for the peers' words itself (default).  TFP_XCHG_STREAM_WAIT=1 keeps the wait in the
+    // stream instead: one cuStreamWaitValue32 per peer, measured 7 driver calls + a late kernel launch per find.
+    const bool kernel_wait = !tuning().xchg_stream_wait;
+    if (!kernel_wait) {
+        for (int r = 0; r < c->x_world; r++) {
+            if (r == c->x_me) continue;
+            CUresult wr = g_wait32((CUstream)c->stream, (CUdeviceptr)(words + r), seq, CU_STREAM_WAIT_VALUE_GEQ);
+            if (wr != CUDA_SUCCESS) return fail(-7, "cuStreamWaitValue32 failed with CUresult %d", (int)wr);
+        }
     }
     const uint8_t* block = c->xbuf.as<uint8_t>() + par_off;
     MergedLayout L(k, count);
     const size_t want = L.total + (with_keys ? (size_t)count * k * dim * 4 : 0);
     if (c->merged.reserve(want)) return -1;
-    rc = launch_merge(c, block, c->x_slot, rb, c->x_world, count, k);
+    rc = launch_merge(c, block, c->x_slot, rb, c->x_world, count, k, kernel_wait ? words : nullptr, c->x_me, seq);
     if (rc) return rc;
     c->merged_keys_dim = 0;
     if (with_keys) {
