@@ -24,6 +24,7 @@
 #ifndef TFP_STORE_H
 #define TFP_STORE_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -57,8 +58,36 @@ typedef struct {
 int  tfp_store_open(const tfp_cfg* cfg, tfp_store** out);
 void tfp_store_close(tfp_store* s);
 
-/* Text of the calling thread's most recent non-zero return. */
+/* ONE logical store over several GPUs of one box, inside one process.
+ * LocalAI spawns a single `local-store` process per backend and passes it only --addr and
+ * the environment (pkg/model/initializers.go:333-368, pkg/model/process.go:94-124), so
+ * the multi-GPU store sits behind the SAME handle and the SAME entry points as the
+ * one-GPU store: every tfp_store_* function below accepts the handle this returns.
+ * devices: n_devices CUDA ordinals (1..8; one shard per entry; cfg->device is ignored;
+ * cfg->capacity_rows is the whole store's hint).  Keys are routed to a shard by a hash
+ * of their canonical bits (tfp_route_rows); a find scans every shard, the scan kernels
+ * write their result records into GPU devices[0]'s memory over NVLink (peer access;
+ * without it the per-shard answers are merged on the host), one merge kernel there
+ * produces the answer.  Calls may come from any thread; up to TFP_MULTI_LANES (default 4)
+ * finds run at once, further callers wait their turn.  Shard g hands out ids from
+ * cfg->id_base + (g << 40).  Not available on such a handle: tfp_store_set_device and
+ * the find-context calls (tfp_find_ctx_create fails; the store runs its own lanes). */
+int  tfp_store_open_devices(const tfp_cfg* cfg, const int* devices, int n_devices, tfp_store** out);
+/* Number of shards behind a handle (1 for tfp_store_open) and one shard's figures: what a
+ * host's Status reply lists per GPU (pkg/grpc/base/base.go:77-81 memory breakdown). */
+int  tfp_store_shard_count(tfp_store* s);
+/* Which shard of an n_shards-wide store owns each of n keys (pure host arithmetic; equal
+ * keys under Go's cmp.Compare -- -0 == +0, NaN == NaN, store.go:48-52 -- share a shard). */
+int  tfp_route_rows(const float* keys, int64_t n, int dim, int n_shards, int* out_shard);
+
+/* Text of the calling thread's most recent non-zero return.  Thread-local: a host whose
+ * calls may change OS thread between the failing call and this one (goroutines under
+ * cgo) either pins the thread around the pair (runtime.LockOSThread) or uses
+ * tfp_store_last_error. */
 const char* tfp_last_error(void);
+/* Text of the most recent failing call ON THIS HANDLE, whichever thread made it, copied
+ * into buf (NUL-terminated, truncated to cap).  SURVEY App. D tfp_store_last_error. */
+int tfp_store_last_error(tfp_store* s, char* buf, size_t cap);
 
 /* ---- StoresSet: replaces Store.StoresSet (store.go:106-198) ------------------
  * keys: n x dim floats in host memory, copied before return (the Go host may
@@ -123,6 +152,7 @@ typedef struct {
     int     reserved;
 } tfp_stats;
 int tfp_store_stats(tfp_store* s, tfp_stats* out);
+int tfp_store_shard_stats(tfp_store* s, int shard, tfp_stats* out);
 
 /* ---- snapshot / restore ----------------------------------------------
  * The reference keeps the store in process memory only (Load is a no-op, store.go:101-103): a
@@ -131,6 +161,16 @@ int tfp_store_stats(tfp_store* s, tfp_stats* out);
  * (hashes and norms are recomputed on the device).  Values stay with the host, keyed by id. */
 int tfp_store_save(tfp_store* s, const char* path);
 int tfp_store_load(tfp_store* s, const char* path);
+/* Crash consistency.  A save writes `path.tmp`, fsyncs it and renames it over `path`: a kill at any
+ * moment leaves either the previous snapshot or the complete new one (a multi-GPU store writes one
+ * file per shard, `path.g<i>`, and its manifest at `path` last; a load checks the shards against it).
+ * The host's values live in a file of the host's own; to tie the two together the host picks a fresh
+ * 64-bit tag per save, writes its values to a NEW file named after the tag, then calls
+ * tfp_store_save_tagged -- the rename of `path` is the commit point -- and only then removes older
+ * values files.  At start it reads the tag back with tfp_snapshot_tag and opens the values file of
+ * that name.  tfp_store_save is tfp_store_save_tagged with tag 0. */
+int tfp_store_save_tagged(tfp_store* s, const char* path, uint64_t tag);
+int tfp_snapshot_tag(const char* path, uint64_t* out_tag);
 
 /* A shard of a logical multi-GPU store is told that another shard has seen a key that
  * is not unit length: the sticky flag (store.go:27,126-127) is a property of the whole

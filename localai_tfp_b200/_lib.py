@@ -28,7 +28,11 @@ vp = C.c_void_p
 PROTOTYPES = {
     "tfp_store_open": (C.c_int, [C.POINTER(TfpCfg), C.POINTER(vp)]),
     "tfp_store_close": (None, [vp]),
+    "tfp_store_open_devices": (C.c_int, [C.POINTER(TfpCfg), i32p, C.c_int, C.POINTER(vp)]),
+    "tfp_store_shard_count": (C.c_int, [vp]),
+    "tfp_route_rows": (C.c_int, [fp, C.c_int64, C.c_int, C.c_int, i32p]),
     "tfp_last_error": (C.c_char_p, []),
+    "tfp_store_last_error": (C.c_int, [vp, C.c_char_p, C.c_size_t]),
     "tfp_store_set": (C.c_int, [vp, fp, C.c_int64, C.c_int, C.c_int64, i64p, u8p]),
     "tfp_store_set_device": (C.c_int, [vp, vp, C.c_int64, C.c_int, i64p, u8p]),
     "tfp_store_delete": (C.c_int, [vp, fp, C.c_int64, C.c_int, i64p]),
@@ -36,8 +40,11 @@ PROTOTYPES = {
     "tfp_store_find": (C.c_int, [vp, vp, C.c_int, C.c_int, i32p, vp, vp, vp, i32p]),   # array arguments as plain addresses: the per-call path
     "tfp_store_find_batch": (C.c_int, [vp, fp, C.c_int, C.c_int, C.c_int, i32p, i64p, fp, fp]),
     "tfp_store_stats": (C.c_int, [vp, C.POINTER(TfpStats)]),
+    "tfp_store_shard_stats": (C.c_int, [vp, C.c_int, C.POINTER(TfpStats)]),
     "tfp_store_save": (C.c_int, [vp, C.c_char_p]),
     "tfp_store_load": (C.c_int, [vp, C.c_char_p]),
+    "tfp_store_save_tagged": (C.c_int, [vp, C.c_char_p, C.c_uint64]),
+    "tfp_snapshot_tag": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint64)]),
     "tfp_store_mark_not_normalized": (C.c_int, [vp]),
     "tfp_store_default_ctx": (vp, [vp]),
     "tfp_find_ctx_create": (C.c_int, [vp, C.POINTER(vp)]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libtfpstore.so")
 SOURCES = [os.path.join(CSRC, "tfp_store.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("common.cuh", "select.cuh", "scan.cuh", "mma_scan.cuh", "ingest.cuh", "host_index.hpp")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("common.cuh", "select.cuh", "scan.cuh", "mma_scan.cuh", "ingest.cuh", "host_index.hpp", "multi_store.inl")] + [
     os.path.join(os.path.dirname(HERE), "include", "tfp_store.h")
 ]
 

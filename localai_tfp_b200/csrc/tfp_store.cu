@@ -12,9 +12,12 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <dlfcn.h>
+#include <fcntl.h>
+#include <unistd.h>
 #include <mutex>
 #include <shared_mutex>
 #include <string>
@@ -261,8 +264,12 @@ struct VmmArray {
 // the store
 // ---------------------------------------------------------------------------
 struct tfp_find_ctx;
+struct tfp_multi;
 
 struct tfp_store {
+    tfp_multi* multi = nullptr;   // set: this handle is ONE logical store over several GPUs (multi_store.inl); the fields below are unused
+    std::mutex err_mu;
+    std::string last_err;         // text of the last failing call on this handle, from any thread (tfp_store_last_error)
     int device = 0;
     std::shared_mutex rw;      // finds: shared while enqueueing; mutations: exclusive
     int dim = -1;              // store.go:29,44 keyLen
@@ -317,6 +324,7 @@ struct tfp_find_ctx {
     int x_world = 0, x_me = 0;
     unsigned int x_seq = 0;
     bool x_ready = false;
+    bool x_root_mode = false;            // one process over several GPUs: records are gathered on shard 0 only
     bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
     bool keys_gathered = false;          // the last launch's scan kernels wrote the winning key rows themselves
     int64_t mma_passes = 0, mma_fallbacks = 0;
@@ -327,6 +335,7 @@ struct tfp_find_ctx {
     uint64_t* out_cand = nullptr; uint32_t* out_slots = nullptr; uint8_t* out_rec = nullptr;
     size_t off_ids = 0, off_sims = 0, off_keys = 0;   // byte offsets inside out_block
     int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
+    int last_topk_host = 0;              // the topk the caller passed (host arrays are strided by it; last_topk may be clamped)
     int64_t launches = 0;
 };
 
@@ -453,7 +462,7 @@ static int optin_all(int bytes) {
 static int ctx_create(tfp_store* s, tfp_find_ctx** out);
 static void ctx_destroy(tfp_find_ctx* c);
 
-extern "C" int tfp_store_open(const tfp_cfg* cfg, tfp_store** out) {
+static int store_open(const tfp_cfg* cfg, tfp_store** out) {
     if (!out) return fail(2, "tfp_store_open: out is NULL");
     *out = nullptr;
     int ndev = 0;
@@ -483,7 +492,7 @@ extern "C" int tfp_store_open(const tfp_cfg* cfg, tfp_store** out) {
     return 0;
 }
 
-extern "C" void tfp_store_close(tfp_store* s) {
+static void store_close(tfp_store* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaDeviceSynchronize();
@@ -503,7 +512,7 @@ extern "C" void tfp_store_close(tfp_store* s) {
     delete s;
 }
 
-extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
+static int store_stats(tfp_store* s, tfp_stats* out) {
     if (!s || !out) return fail(2, "tfp_store_stats: NULL argument");
     std::shared_lock<std::shared_mutex> lk(s->rw);
     out->rows = s->n;
@@ -517,7 +526,7 @@ extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
     return 0;
 }
 
-extern "C" int tfp_store_mark_not_normalized(tfp_store* s) {
+static int store_mark_not_normalized(tfp_store* s) {
     if (!s) return fail(2, "tfp_store_mark_not_normalized: store is NULL");
     std::unique_lock<std::shared_mutex> lk(s->rw);
     s->normalized = false;
@@ -673,8 +682,8 @@ static int check_scatter_grid(int64_t n) {
     return 0;
 }
 
-extern "C" int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_t n_values, int64_t* out_ids,
-                             uint8_t* out_was_new) {
+static int store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_t n_values, int64_t* out_ids,
+                     uint8_t* out_was_new) {
     if (!s) return fail(2, "tfp_store_set: store is NULL");
     if (n == 0) return fail(1, "no keys to add");                                     // store.go:107-109
     if (n != n_values) return fail(1, "len(keys) = %lld, len(values) = %lld", (long long)n, (long long)n_values);  // :111-113
@@ -690,8 +699,8 @@ extern "C" int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim
     return set_impl(s, d_rows, n, out_ids, out_was_new);
 }
 
-extern "C" int tfp_store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim, int64_t* out_ids,
-                                    uint8_t* out_was_new) {
+static int store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim, int64_t* out_ids,
+                            uint8_t* out_was_new) {
     if (!s) return fail(2, "tfp_store_set_device: store is NULL");
     if (n == 0) return fail(1, "no keys to add");
     if (!d_keys || dim <= 0) return fail(2, "tfp_store_set_device: d_keys is NULL or dim <= 0");
@@ -713,8 +722,8 @@ static void sorted_order(const float* keys, int64_t n, int dim, std::vector<int6
     });
 }
 
-extern "C" int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids, int64_t* out_order,
-                             int64_t* out_n_found) {
+static int store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids, int64_t* out_order,
+                     int64_t* out_n_found) {
     if (!s) return fail(2, "tfp_store_get: store is NULL");
     if (out_n_found) *out_n_found = 0;
     if (n == 0) return fail(1, "no keys to get");   // reference panics here (store.go:276); documented deviation
@@ -746,7 +755,7 @@ extern "C" int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim
     return 0;
 }
 
-extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids) {
+static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids) {
     if (!s) return fail(2, "tfp_store_delete: store is NULL");
     if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203
     if (!keys || dim <= 0) return fail(2, "tfp_store_delete: keys is NULL or dim <= 0");
@@ -812,43 +821,65 @@ extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int 
 // snapshot / restore
 // ---------------------------------------------------------------------------
 struct SnapHeader {
-    char magic[8];        // "TFPSTOR1"
+    char magic[8];        // "TFPSTOR2" ("TFPSTOR1": the same without the tag)
     int32_t dim;
     int32_t normalized;
     int64_t rows;
     int64_t next_id;
+    uint64_t tag;         // the host's generation stamp: names the values file that belongs to this snapshot
 };
+constexpr size_t kSnapHeaderV1Bytes = 32;
 
-extern "C" int tfp_store_save(tfp_store* s, const char* path) {
+// Write a file so that a crash at any moment leaves either the previous file or the complete new one:
+// `path.tmp` is written and fsync'ed, then renamed over `path` (and the directory entry synced).
+template <class Body>
+static int write_file_atomically(const char* path, Body&& body) {
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return fail(2, "tfp_store_save: cannot open %s", tmp.c_str());
+    bool ok = body(f);
+    ok = (fflush(f) == 0) && ok;
+    ok = (fsync(fileno(f)) == 0) && ok;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) { remove(tmp.c_str()); return fail(2, "tfp_store_save: short write to %s", tmp.c_str()); }
+    if (rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return fail(2, "tfp_store_save: cannot rename %s to %s", tmp.c_str(), path); }
+    std::string dir(path);
+    const size_t slash = dir.find_last_of('/');
+    dir = slash == std::string::npos ? "." : dir.substr(0, slash ? slash : 1);
+    const int dfd = open(dir.c_str(), O_RDONLY | O_DIRECTORY);
+    if (dfd >= 0) { fsync(dfd); close(dfd); }
+    return 0;
+}
+
+static int store_save(tfp_store* s, const char* path, uint64_t tag) {
     if (!s || !path) return fail(2, "tfp_store_save: NULL argument");
     std::unique_lock<std::shared_mutex> lk(s->rw);
     if (set_device(s) || quiesce_finds(s)) return -1;
-    FILE* f = fopen(path, "wb");
-    if (!f) return fail(2, "tfp_store_save: cannot open %s", path);
     SnapHeader h;
-    memcpy(h.magic, "TFPSTOR1", 8);
-    h.dim = s->dim; h.normalized = s->normalized ? 1 : 0; h.rows = s->n; h.next_id = s->next_id;
-    bool ok = fwrite(&h, sizeof(h), 1, f) == 1;
+    memcpy(h.magic, "TFPSTOR2", 8);
+    h.dim = s->dim; h.normalized = s->normalized ? 1 : 0; h.rows = s->n; h.next_id = s->next_id; h.tag = tag;
     const size_t chunk = (size_t)64 << 20;
     PinBuf pin;
-    if (ok && s->n > 0 && pin.reserve(chunk)) { fclose(f); return -1; }
-    auto dump = [&](const void* dptr, size_t bytes) -> int {
-        for (size_t off = 0; ok && off < bytes; off += chunk) {
-            size_t m = std::min(chunk, bytes - off);
-            CU_OK(cudaMemcpy(pin.p, (const uint8_t*)dptr + off, m, cudaMemcpyDeviceToHost));
-            ok = fwrite(pin.p, 1, m, f) == m;
-        }
-        return 0;
-    };
-    if (s->n > 0) {
-        if (dump(s->d_keys, (size_t)s->n * s->dim * 4) || dump(s->d_ids, (size_t)s->n * 8)) { fclose(f); pin.release(); return -1; }
-    }
+    if (s->n > 0 && pin.reserve(chunk)) return -1;
+    int cuda_rc = 0;
+    int rc = write_file_atomically(path, [&](FILE* f) -> bool {
+        bool ok = fwrite(&h, sizeof(h), 1, f) == 1;
+        auto dump = [&](const void* dptr, size_t bytes) {
+            for (size_t off = 0; ok && !cuda_rc && off < bytes; off += chunk) {
+                size_t m = std::min(chunk, bytes - off);
+                if (cudaMemcpy(pin.p, (const uint8_t*)dptr + off, m, cudaMemcpyDeviceToHost) != cudaSuccess) { cuda_rc = -1; return; }
+                ok = fwrite(pin.p, 1, m, f) == m;
+            }
+        };
+        if (s->n > 0) { dump(s->d_keys, (size_t)s->n * s->dim * 4); dump(s->d_ids, (size_t)s->n * 8); }
+        return ok && !cuda_rc;
+    });
     pin.release();
-    ok = (fclose(f) == 0) && ok;
-    return ok ? 0 : fail(2, "tfp_store_save: short write to %s", path);
+    if (cuda_rc) return fail(-1, "tfp_store_save: device-to-host copy failed");
+    return rc;
 }
 
-extern "C" int tfp_store_load(tfp_store* s, const char* path) {
+static int store_load(tfp_store* s, const char* path) {
     if (!s || !path) return fail(2, "tfp_store_load: NULL argument");
     std::unique_lock<std::shared_mutex> lk(s->rw);
     if (s->n != 0 || s->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
@@ -856,8 +887,11 @@ extern "C" int tfp_store_load(tfp_store* s, const char* path) {
     FILE* f = fopen(path, "rb");
     if (!f) return fail(2, "tfp_store_load: cannot open %s", path);
     SnapHeader h;
-    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "TFPSTOR1", 8) != 0 || h.rows < 0 || h.rows > 0xFFFFFFF0ll ||
-        (h.rows > 0 && h.dim <= 0)) {
+    memset(&h, 0, sizeof(h));
+    bool hdr = fread(&h, kSnapHeaderV1Bytes, 1, f) == 1;
+    if (hdr && memcmp(h.magic, "TFPSTOR2", 8) == 0) hdr = fread(&h.tag, sizeof(h.tag), 1, f) == 1;
+    else if (hdr && memcmp(h.magic, "TFPSTOR1", 8) != 0) hdr = false;
+    if (!hdr || h.rows < 0 || h.rows > 0xFFFFFFF0ll || (h.rows > 0 && h.dim <= 0)) {
         fclose(f);
         return fail(2, "tfp_store_load: %s is not a store snapshot", path);
     }
@@ -927,7 +961,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     c->nccl_comm = nullptr;
     for (int r = 0; r < kXchgMaxWorld; r++)
-        if (c->x_peer[r] && r != c->x_me) cudaIpcCloseMemHandle(c->x_peer[r]);
+        if (c->x_peer[r] && r != c->x_me && !c->x_root_mode) cudaIpcCloseMemHandle(c->x_peer[r]);
     c->xbuf.release();
     if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
@@ -940,10 +974,13 @@ static void ctx_destroy(tfp_find_ctx* c) {
     delete c;
 }
 
-extern "C" tfp_find_ctx* tfp_store_default_ctx(tfp_store* s) { return s ? s->default_ctx : nullptr; }
+extern "C" tfp_find_ctx* tfp_store_default_ctx(tfp_store* s) { return (s && !s->multi) ? s->default_ctx : nullptr; }
 
 extern "C" int tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out) {
     if (!s || !out) return fail(2, "tfp_find_ctx_create: NULL argument");
+    if (s->multi)
+        return fail(2, "tfp_find_ctx_create: a multi-GPU store runs its own find lanes; call tfp_store_find / "
+                       "tfp_store_find_batch from several threads instead");
     std::unique_lock<std::shared_mutex> lk(s->rw);
     if (set_device(s)) return -1;
     return ctx_create(s, out);
@@ -971,7 +1008,9 @@ static double host_query_mag(const float* q, int d) {
     return std::sqrt(m);
 }
 
-static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim) {
+// pre: the queries' QInfo records when the caller has computed them already (one logical store over several
+// GPUs computes them once for all its shards), else nullptr.
+static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim, const QInfo* pre = nullptr) {
     tfp_store* s = c->st;
     size_t qbytes = (size_t)nq * dim * 4, ibytes = (size_t)nq * sizeof(QInfo);
     qbytes = (qbytes + 15) & ~(size_t)15;
@@ -982,6 +1021,7 @@ static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim) {
     for (int i = 0; i < nq; i++) {
         const float* qi = q + (size_t)i * dim;
         QInfo& info = c->qinfo[(size_t)i];
+        if (pre) { info = pre[i]; continue; }
         info.normalized = host_is_normalized(qi, dim) ? 1 : 0;   // the store flag is folded in at launch
         info.mag1 = host_query_mag(qi, dim);
         info.pad = 0;
@@ -1161,20 +1201,25 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
 // made of exact fused scans only (c->x_pushed tells the caller whether that happened).
 // want_keys: the caller will ask for the key rows; exact fused scans then write them from their last CTA
 // (c->keys_gathered), other paths leave them to gather_rows_kernel.
+// local_records: the find never leaves this shard (tfp_store_find[_batch]): size the packed records by
+// min(topk, rows) instead of the caller's topk -- only shards that exchange records need them equal.
 static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, const XchgParams* xchg = nullptr,
-                             bool want_keys = false) {
+                             bool want_keys = false, bool local_records = false) {
     tfp_store* s = c->st;
     c->x_pushed = false;
     c->keys_gathered = false;
     if (c->dim != s->dim)                                                            // store.go:480-482
         return fail(1, "Try to find key with length %d when existing length is %d", c->dim, s->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
+    const int topk_host = topk;                              // the caller's arrays are strided by what the caller asked for
     if ((int64_t)topk > (int64_t)1 << 26) topk = 1 << 26;   // more than any shard can hold; keeps record sizes sane
     if (first < 0 || count <= 0 || first + count > c->nq) return fail(2, "find: query range [%d,%d) outside the %d staged queries", first, first + count, c->nq);
     const int64_t n = s->n;
     const int ksel = (int)std::min<int64_t>((int64_t)topk, std::max<int64_t>(n, 1));
+    if (local_records) topk = ksel;
     c->last_count = count;
     c->last_topk = topk;
+    c->last_topk_host = topk_host;
     c->last_stride = ksel;
     c->last_path = (s->normalized && c->qinfo[(size_t)first].normalized) ? TFP_PATH_NORMALIZED : TFP_PATH_FALLBACK;
     size_t slots = (size_t)count * ksel;
@@ -1253,7 +1298,15 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
                 size_t fixed = scan_smem_bytes(0, g, dpad, cap) + 2 * kMaxStages * 8;
                 int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
                 n_stages = std::min(kMaxStages, room);
+                // A small shard (<= 32 tiles per CTA) scanned from a caller-made find context -- finds that are meant to
+                // overlap -- gets a 6-stage ring: two CTAs then share an SM, so one find's prologue / publish / merge
+                // runs under the other's streaming, and finds that run side by side read each tile from HBM once and
+                // from L2 after that.  Measured on 125k x 768 (profiles/r02_probe_small_stages.log): 58 -> 51 us per find
+                // with four finds in flight, 57 -> 40 with two; a lone scan pays 2-3 % (68.0 -> 69.3 us), so the
+                // store's own synchronous context and large stores keep the deep ring.
                 if (tuning().scan_stages >= 3) n_stages = std::min(n_stages, tuning().scan_stages);
+                else if (tuning().scan_stages == 0 && c != s->default_ctx && n_tiles <= 32u * (uint32_t)grid)
+                    n_stages = std::min(n_stages, 6);
                 if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, dpad, cap); break; }
                 if (g > 1) { g >>= 1; continue; }
                 use_tma = false;
@@ -1367,7 +1420,7 @@ extern "C" int tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys) {
 
 static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys) {
     tfp_store* s = c->st;
-    const int count = c->last_count, topk = c->last_topk, ks = c->last_stride, dim = s->dim;
+    const int count = c->last_count, topk = c->last_topk_host, ks = c->last_stride, dim = s->dim;
     if (count <= 0) return fail(2, "find download: nothing was launched on this context");
     const size_t slots = (size_t)count * ks;
     // one D2H copy of the block's head: [n | ids | sims] and, when asked for, the key rows
@@ -1447,8 +1500,8 @@ extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, i
 // ---------------------------------------------------------------------------
 // synchronous finds (what the Go host calls)
 // ---------------------------------------------------------------------------
-extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
-                                    float* out_sims, float* out_keys) {
+static int store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
+                            float* out_sims, float* out_keys, int* out_path) {
     if (!s) return fail(2, "tfp_store_find: store is NULL");
     std::shared_lock<std::shared_mutex> lk(s->rw);
     if (dim != s->dim)                                                               // store.go:480-482 (fires on -1 too)
@@ -1460,16 +1513,10 @@ extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int di
     tfp_find_ctx* c = s->default_ctx;
     int rc = ctx_upload_locked(c, q, nq, dim);
     if (rc) return rc;
-    rc = ctx_launch_locked(c, 0, nq, topk, nullptr, out_keys != nullptr);
+    rc = ctx_launch_locked(c, 0, nq, topk, nullptr, out_keys != nullptr, /*local_records=*/true);
     if (rc) return rc;
+    if (out_path) *out_path = c->last_path;   // read while find_mu is held: another thread's find cannot slip in
     return ctx_download_locked(c, out_n, out_ids, out_sims, out_keys);
-}
-
-extern "C" int tfp_store_find(tfp_store* s, const float* q, int dim, int topk, int* out_n, int64_t* out_ids,
-                              float* out_sims, float* out_keys, int* out_path) {
-    int rc = tfp_store_find_batch(s, q, 1, dim, topk, out_n, out_ids, out_sims, out_keys);
-    if (rc == 0 && out_path) *out_path = s->default_ctx->last_path;
-    return rc;
 }
 
 // ---------------------------------------------------------------------------
@@ -1734,7 +1781,7 @@ static size_t xbuf_flags_offset(int world, size_t slot) { return ((size_t)2 * wo
 
 static void p2p_detach(tfp_find_ctx* c) {
     for (int r = 0; r < kXchgMaxWorld; r++) {
-        if (c->x_peer[r] && r != c->x_me) cudaIpcCloseMemHandle(c->x_peer[r]);
+        if (c->x_peer[r] && r != c->x_me && !c->x_root_mode) cudaIpcCloseMemHandle(c->x_peer[r]);
         c->x_peer[r] = nullptr;
     }
     c->x_ready = false;
@@ -1844,6 +1891,14 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
         x.slot[r] = c->x_peer[r] + par_off + (size_t)c->x_me * c->x_slot;
         x.flag[r] = (unsigned int*)(c->x_peer[r] + flags_off) + c->x_me;
     }
+    if (c->x_root_mode) {
+        // One process, several GPUs (multi_store.inl): records are gathered on shard 0 only.  The kernels see a
+        // one-destination exchange: shard 0 writes its own slot and raises nothing (its merge follows in the same
+        // stream), every other shard writes into shard 0's block over NVLink and raises its word there.
+        x.world = 1;
+        x.slot[0] = c->x_peer[0] + par_off + (size_t)c->x_me * c->x_slot;
+        x.flag[0] = (unsigned int*)(c->x_peer[0] + flags_off) + c->x_me;
+    }
     // records travel inside the scan kernel when nothing else has to be pushed before the words are raised
     int rc = ctx_launch_locked(c, first, count, topk, with_keys ? nullptr : &x);
     if (rc) return rc;     // argument errors: nothing was enqueued and seq was not consumed (same on every rank)
@@ -1859,10 +1914,11 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
         c->launches++;
     }
     if (!c->x_pushed) {
-        push_records_kernel<<<c->x_world, 256, 0, c->stream>>>(x, c->out_rec, rb * count);
+        push_records_kernel<<<x.world, 256, 0, c->stream>>>(x, c->out_rec, rb * count);
         CU_OK(cudaGetLastError());
         c->launches++;
     }
+    if (c->x_root_mode && c->x_me != 0) return 0;   // only shard 0 merges
     unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + flags_off);
     // The merge kernel waits for the peers' words itself (default).  TFP_XCHG_STREAM_WAIT=1 keeps the wait in the
     // stream instead: one cuStreamWaitValue32 per peer, measured 7 driver calls + a late kernel launch per find.
@@ -2015,3 +2071,130 @@ extern "C" void* tfp_host_alloc(size_t bytes) {
     return p;
 }
 extern "C" void tfp_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---------------------------------------------------------------------------
+// one logical store over several GPUs in one process
+// ---------------------------------------------------------------------------
+#include "multi_store.inl"
+
+// ---------------------------------------------------------------------------
+// The store's public entry points: dispatch on the kind of handle, keep the error text per handle.
+// ---------------------------------------------------------------------------
+static int keep_err(tfp_store* s, int rc) {
+    if (rc && s) {
+        std::lock_guard<std::mutex> g(s->err_mu);
+        s->last_err = g_err;
+    }
+    return rc;
+}
+
+extern "C" int tfp_store_open(const tfp_cfg* cfg, tfp_store** out) { return store_open(cfg, out); }
+
+extern "C" int tfp_store_open_devices(const tfp_cfg* cfg, const int* devices, int n_devices, tfp_store** out) {
+    if (!out) return fail(2, "tfp_store_open_devices: out is NULL");
+    *out = nullptr;
+    if (!devices || n_devices < 1) return fail(2, "tfp_store_open_devices: no devices");
+    if (n_devices == 1) {
+        tfp_cfg c;
+        memset(&c, 0, sizeof(c));
+        if (cfg) c = *cfg;
+        c.device = devices[0];
+        return store_open(&c, out);
+    }
+    return multi_open(cfg, devices, n_devices, out);
+}
+
+extern "C" void tfp_store_close(tfp_store* s) {
+    if (!s) return;
+    if (s->multi) { multi_close(s); delete s; return; }
+    store_close(s);
+}
+
+extern "C" int tfp_store_last_error(tfp_store* s, char* buf, size_t cap) {
+    if (!s || !buf || cap == 0) return fail(2, "tfp_store_last_error: bad argument");
+    std::lock_guard<std::mutex> g(s->err_mu);
+    snprintf(buf, cap, "%s", s->last_err.c_str());
+    return 0;
+}
+
+extern "C" int tfp_store_shard_count(tfp_store* s) { return !s ? 0 : (s->multi ? (int)s->multi->shards.size() : 1); }
+
+extern "C" int tfp_store_shard_stats(tfp_store* s, int shard, tfp_stats* out) {
+    if (!s || !out) return fail(2, "tfp_store_shard_stats: NULL argument");
+    if (shard < 0 || shard >= tfp_store_shard_count(s)) return keep_err(s, fail(2, "tfp_store_shard_stats: shard %d out of range", shard));
+    return keep_err(s, store_stats(s->multi ? s->multi->shards[(size_t)shard] : s, out));
+}
+
+extern "C" int tfp_route_rows(const float* keys, int64_t n, int dim, int n_shards, int* out_shard) {
+    if (!keys || !out_shard || n < 0 || dim <= 0 || n_shards < 1) return fail(2, "tfp_route_rows: bad argument");
+    for (int64_t i = 0; i < n; i++) out_shard[i] = route_of(keys + (size_t)i * dim, dim, n_shards);
+    return 0;
+}
+
+extern "C" int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_t n_values, int64_t* out_ids,
+                             uint8_t* out_was_new) {
+    if (!s) return fail(2, "tfp_store_set: store is NULL");
+    return keep_err(s, s->multi ? multi_set(s, keys, n, dim, n_values, out_ids, out_was_new)
+                                : store_set(s, keys, n, dim, n_values, out_ids, out_was_new));
+}
+extern "C" int tfp_store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim, int64_t* out_ids,
+                                    uint8_t* out_was_new) {
+    if (!s) return fail(2, "tfp_store_set_device: store is NULL");
+    if (s->multi)
+        return keep_err(s, fail(2, "tfp_store_set_device: keys in one GPU's memory cannot be routed across a multi-GPU store; "
+                                   "use tfp_store_set"));
+    return keep_err(s, store_set_device(s, d_keys, n, dim, out_ids, out_was_new));
+}
+extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids) {
+    if (!s) return fail(2, "tfp_store_delete: store is NULL");
+    return keep_err(s, s->multi ? multi_delete(s, keys, n, dim, out_ids) : store_delete(s, keys, n, dim, out_ids));
+}
+extern "C" int tfp_store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids, int64_t* out_order,
+                             int64_t* out_n_found) {
+    if (!s) return fail(2, "tfp_store_get: store is NULL");
+    return keep_err(s, s->multi ? multi_get(s, keys, n, dim, out_ids, out_order, out_n_found)
+                                : store_get(s, keys, n, dim, out_ids, out_order, out_n_found));
+}
+extern "C" int tfp_store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
+                                    float* out_sims, float* out_keys) {
+    if (!s) return fail(2, "tfp_store_find: store is NULL");
+    return keep_err(s, s->multi ? multi_find_batch(s, q, nq, dim, topk, out_n, out_ids, out_sims, out_keys, nullptr)
+                                : store_find_batch(s, q, nq, dim, topk, out_n, out_ids, out_sims, out_keys, nullptr));
+}
+extern "C" int tfp_store_find(tfp_store* s, const float* q, int dim, int topk, int* out_n, int64_t* out_ids,
+                              float* out_sims, float* out_keys, int* out_path) {
+    if (!s) return fail(2, "tfp_store_find: store is NULL");
+    return keep_err(s, s->multi ? multi_find_batch(s, q, 1, dim, topk, out_n, out_ids, out_sims, out_keys, out_path)
+                                : store_find_batch(s, q, 1, dim, topk, out_n, out_ids, out_sims, out_keys, out_path));
+}
+extern "C" int tfp_store_stats(tfp_store* s, tfp_stats* out) {
+    if (!s || !out) return fail(2, "tfp_store_stats: NULL argument");
+    return keep_err(s, s->multi ? multi_stats(s, out) : store_stats(s, out));
+}
+extern "C" int tfp_store_mark_not_normalized(tfp_store* s) {
+    if (!s) return fail(2, "tfp_store_mark_not_normalized: store is NULL");
+    return keep_err(s, s->multi ? multi_mark_not_normalized(s) : store_mark_not_normalized(s));
+}
+extern "C" int tfp_store_save_tagged(tfp_store* s, const char* path, uint64_t tag) {
+    if (!s || !path) return fail(2, "tfp_store_save: NULL argument");
+    return keep_err(s, s->multi ? multi_save(s, path, tag) : store_save(s, path, tag));
+}
+extern "C" int tfp_store_save(tfp_store* s, const char* path) { return tfp_store_save_tagged(s, path, 0); }
+extern "C" int tfp_snapshot_tag(const char* path, uint64_t* out_tag) {
+    if (!path || !out_tag) return fail(2, "tfp_snapshot_tag: NULL argument");
+    *out_tag = 0;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(2, "tfp_snapshot_tag: cannot open %s", path);
+    char magic[8];
+    bool ok = fread(magic, 8, 1, f) == 1;
+    if (ok && memcmp(magic, "TFPSTOR2", 8) == 0) ok = fseek(f, (long)kSnapHeaderV1Bytes, SEEK_SET) == 0 && fread(out_tag, 8, 1, f) == 1;
+    else if (ok && memcmp(magic, "TFPMULT1", 8) == 0) ok = fseek(f, (long)offsetof(MultiManifest, tag), SEEK_SET) == 0 && fread(out_tag, 8, 1, f) == 1;
+    else if (ok && memcmp(magic, "TFPSTOR1", 8) == 0) *out_tag = 0;
+    else ok = false;
+    fclose(f);
+    return ok ? 0 : fail(2, "tfp_snapshot_tag: %s is not a store snapshot", path);
+}
+extern "C" int tfp_store_load(tfp_store* s, const char* path) {
+    if (!s || !path) return fail(2, "tfp_store_load: NULL argument");
+    return keep_err(s, s->multi ? multi_load(s, path) : store_load(s, path));
+}

@@ -16,6 +16,7 @@ import argparse
 import os
 import queue
 import signal
+import sys
 import threading
 from concurrent import futures
 
@@ -96,13 +97,39 @@ class _FindBatcher:
                 b.busy = False
 
 
+def devices_from_env(default_device: int = 0):
+    """The GPUs this backend spreads its store over.  LocalAI's loader gives a backend process only `--addr` and
+    the inherited environment (pkg/model/process.go:112-113), so the device list travels in TFP_DEVICES:
+    "0,1,2,3", or "all" for every visible GPU.  Unset: one GPU (`--device`)."""
+    spec = os.environ.get("TFP_DEVICES", "").strip()
+    if not spec:
+        return None
+    if spec.lower() == "all":
+        import ctypes
+        n = ctypes.c_int(0)
+        try:
+            ctypes.CDLL("libcudart.so").cudaGetDeviceCount(ctypes.byref(n))
+        except OSError:
+            import torch
+            n = ctypes.c_int(torch.cuda.device_count())
+        return list(range(max(n.value, 1)))
+    return [int(x) for x in spec.split(",") if x.strip() != ""] or [default_device]
+
+
 class Backend:
-    def __init__(self, device: int = 0, snapshot: str | None = None):
-        self.store = Store(device=device)
+    def __init__(self, device: int = 0, snapshot: str | None = None, devices=None):
+        self._open = (lambda: Store(devices=devices)) if devices and len(devices) > 1 else \
+                     (lambda: Store(device=devices[0] if devices else device))
+        self.store = self._open()
         self.snapshot = snapshot
         self.batcher = None
-        if snapshot and os.path.exists(snapshot) and os.path.exists(snapshot + ".values"):
-            self.store.load(snapshot)             # survive a watchdog kill / respawn
+        if snapshot and os.path.exists(snapshot):
+            try:
+                self.store.load(snapshot)         # SURVEY §8f.4: survive a watchdog kill / respawn
+            except Exception as e:                # a damaged or mismatched snapshot must not crash-loop the backend
+                print(f"local-store: snapshot {snapshot} not restored ({e}); starting empty", file=sys.stderr, flush=True)
+                self.store.close()
+                self.store = self._open()
         self.lock = threading.Lock()          # base.SingleThread (pkg/grpc/base/singlethread.go:13-29)
         self.busy = False
 
@@ -116,8 +143,12 @@ class Backend:
     def Status(self, request: bytes, context) -> bytes:
         st = self.store.stats()
         state = STATE_BUSY if self.busy else STATE_READY
-        return wire.enc_status(state, int(st.hbm_bytes), {f"hbm-bytes-gpu{st.device}": int(st.hbm_bytes),
-                                                         "rows": int(st.rows)})
+        breakdown = {"rows": int(st.rows)}
+        for g in range(self.store.shard_count):                        # one entry per GPU (base.go:77-81 memory breakdown)
+            sg = self.store.shard_stats(g)
+            key = f"hbm-bytes-gpu{sg.device}"
+            breakdown[key] = breakdown.get(key, 0) + int(sg.hbm_bytes)
+        return wire.enc_status(state, int(st.hbm_bytes), breakdown)
 
     # -- the four store RPCs -------------------------------------------------------------------
     def _run(self, context, fn):
@@ -184,8 +215,9 @@ class Backend:
         return wire.enc_find_batch_result(self._run(context, serve))
 
 
-def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | None = None, batch_finds: bool = True):
-    backend = Backend(device, snapshot)
+def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | None = None, batch_finds: bool = True,
+                devices=None):
+    backend = Backend(device, snapshot, devices if devices is not None else devices_from_env(device))
     if batch_finds:
         backend.batcher = _FindBatcher(backend)
     methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,

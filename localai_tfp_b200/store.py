@@ -67,17 +67,28 @@ def _addr(a: np.ndarray) -> int:
 
 
 class Store:
-    """One store shard resident on one B200."""
+    """One store resident on one B200 -- or, with `devices=[...]`, ONE logical store over several B200s of
+    this box inside this process (tfp_store_open_devices): same methods, same results."""
 
-    def __init__(self, device: int = 0, capacity_rows: int = 0, id_base: int = 0):
+    def __init__(self, device: int = 0, capacity_rows: int = 0, id_base: int = 0, devices: Sequence[int] | None = None):
         self._L = _lib.load()
-        cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0, id_base=id_base)
         h = C.c_void_p()
-        rc = self._L.tfp_store_open(C.byref(cfg), C.byref(h))
+        if devices is not None:
+            devs = [int(d) for d in devices]
+            if not devs:
+                raise ValueError("devices must name at least one GPU")
+            device = devs[0]
+            cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0, id_base=id_base)
+            arr = (C.c_int * len(devs))(*devs)
+            rc = self._L.tfp_store_open_devices(C.byref(cfg), arr, len(devs), C.byref(h))
+        else:
+            cfg = TfpCfg(device=device, capacity_rows=capacity_rows, flags=0, reserved=0, id_base=id_base)
+            rc = self._L.tfp_store_open(C.byref(cfg), C.byref(h))
         if rc:
             raise RuntimeError(f"tfp_store_open failed ({rc}): {self._err()}")
         self._h = h
         self.device = device
+        self.devices = list(devices) if devices is not None else [device]
         self.values = {}  # id -> bytes; values never cross the C ABI (store.go:23)
         self.last_path = None
 
@@ -106,6 +117,21 @@ class Store:
         st = TfpStats()
         self._check(self._L.tfp_store_stats(self._h, C.byref(st)))
         return st
+
+    @property
+    def shard_count(self) -> int:
+        return int(self._L.tfp_store_shard_count(self._h))
+
+    def shard_stats(self, shard: int) -> TfpStats:
+        st = TfpStats()
+        self._check(self._L.tfp_store_shard_stats(self._h, shard, C.byref(st)))
+        return st
+
+    def last_error(self) -> str:
+        """Text of the last failing call on this handle, whichever thread made it."""
+        buf = C.create_string_buffer(512)
+        self._L.tfp_store_last_error(self._h, buf, 512)
+        return buf.value.decode(errors="replace")
 
     def __len__(self):
         return int(self.stats().rows)
@@ -210,19 +236,60 @@ class Store:
         return (res, outk) if with_keys else res
 
     # -- snapshot / restore ---------------------------------------------------------
+    # The library writes keys, ids and flags to `path` (atomically: tmp + fsync + rename).  The values belong to
+    # the host; they go to `path.values.<tag>`, a flat little-endian file a Go host reads just as easily:
+    #     b"TFPVALS1" | u64 tag | u64 count | count x (i64 id | u32 len | bytes)
+    # A save writes the values under a NEW tag first, then the keys file carrying that tag (its rename is the
+    # commit point), then removes older values files -- so a kill at any moment leaves a matching pair.
     def save(self, path: str):
-        """Write the store to `path` (keys, ids, flags: the library) and `path + ".values"` (id -> bytes: the host)."""
-        import pickle
-        self._check(self._L.tfp_store_save(self._h, os.fsencode(path)))
-        with open(path + ".values", "wb") as f:
-            pickle.dump(self.values, f, protocol=4)
+        import glob
+        import struct
+        tag = int.from_bytes(os.urandom(8), "little") | 1
+        vpath = f"{path}.values.{tag:016x}"
+        tmp = vpath + ".tmp"
+        with open(tmp, "wb") as f:
+            f.write(b"TFPVALS1" + struct.pack("<QQ", tag, len(self.values)))
+            for i, v in self.values.items():
+                v = b"" if v is None else bytes(v)
+                f.write(struct.pack("<qI", int(i), len(v)))
+                f.write(v)
+            f.flush()
+            os.fsync(f.fileno())
+        os.replace(tmp, vpath)
+        self._check(self._L.tfp_store_save_tagged(self._h, os.fsencode(path), tag))
+        for old in glob.glob(glob.escape(path) + ".values.*"):
+            if old != vpath:
+                try:
+                    os.remove(old)
+                except OSError:
+                    pass
 
     def load(self, path: str):
-        """Fill this (empty) store from a snapshot written by save()."""
-        import pickle
+        """Fill this (empty) store from a snapshot written by save().  Raises (and leaves the values empty) when
+        the keys file and the values file do not belong together."""
+        import struct
+        tag = C.c_uint64()
+        self._check(self._L.tfp_snapshot_tag(os.fsencode(path), C.byref(tag)))
+        vpath = f"{path}.values.{tag.value:016x}"
+        with open(vpath, "rb") as f:
+            head = f.read(24)
+            if len(head) != 24 or head[:8] != b"TFPVALS1":
+                raise StoreError(f"{vpath} is not a values file", 2)
+            vtag, count = struct.unpack("<QQ", head[8:])
+            if vtag != tag.value:
+                raise StoreError(f"{vpath} carries tag {vtag:x}, the snapshot {tag.value:x}", 2)
+            values = {}
+            for _ in range(count):
+                rec = f.read(12)
+                if len(rec) != 12:
+                    raise StoreError(f"{vpath} is truncated", 2)
+                i, n = struct.unpack("<qI", rec)
+                v = f.read(n)
+                if len(v) != n:
+                    raise StoreError(f"{vpath} is truncated", 2)
+                values[i] = v
         self._check(self._L.tfp_store_load(self._h, os.fsencode(path)))
-        with open(path + ".values", "rb") as f:
-            self.values = pickle.load(f)
+        self.values = values
 
     def mark_not_normalized(self):
         self._check(self._L.tfp_store_mark_not_normalized(self._h))

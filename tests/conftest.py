@@ -31,6 +31,12 @@ def tfp():
     return localai_tfp_b200
 
 
+def two_devices():
+    """Device list for the in-process multi-GPU store tests: two GPUs when the box has them, else two shards on GPU 0."""
+    import torch
+    return [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
+
+
 def normalize_rows(a):
     """Row-normalise in fp32 the way the reference's test helper does
     (tests/integration/stores_test.go:26-37): fp64 norm of fp32-rounded squares, fp32 divide."""

@@ -10,9 +10,12 @@ pytestmark = pytest.mark.gpu
 f32 = np.float32
 
 
-@pytest.fixture()
-def pair(tfp, oracle):
-    s = tfp.Store()
+@pytest.fixture(params=["one-gpu", "multi"])
+def pair(request, tfp, oracle):
+    """Every case runs twice: on the one-GPU store and on ONE logical store over two shards in this process
+    (tfp_store_open_devices; the two shards share GPU 0 when the box has a single GPU)."""
+    from conftest import two_devices
+    s = tfp.Store() if request.param == "one-gpu" else tfp.Store(devices=two_devices())
     yield s, oracle.OracleStore()
     s.close()
 
