@@ -247,6 +247,7 @@ static int multi_open(const tfp_cfg* cfg, const int* devices, int n_devices, tfp
 // store.go:115-116 / :209-210 / :275-276: the first Set, Delete or Get fixes the key length -- of every shard, so
 // that a shard which owns no key yet answers finds with an empty list instead of a length error.
 static int multi_latch(tfp_store* top, int dim, const char* fmt) {
+    std::unique_lock<std::shared_mutex> lk(top->rw);
     if (top->dim == -1) {
         top->dim = dim;
         for (tfp_store* sh : top->multi->shards) {
@@ -288,7 +289,7 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     if (n != n_values) return fail(1, "len(keys) = %lld, len(values) = %lld", (long long)n, (long long)n_values);
     if (!keys || dim <= 0) return fail(2, "tfp_store_set: keys is NULL or dim <= 0");
     if (check_scatter_grid(n)) return 2;
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::lock_guard<std::mutex> mut(top->mut_mu);   // one mutation at a time; finds go on (the shards publish appends themselves)
     if (multi_latch(top, dim, "Try to add key with length %d when existing length is %d")) return 1;
     Routed r;
     route_rows(m, keys, n, dim, r);
@@ -314,6 +315,7 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     bool all_norm = true;
     for (tfp_store* sh : m->shards) { std::shared_lock<std::shared_mutex> l2(sh->rw); all_norm = all_norm && sh->normalized; }
     if (!all_norm) {
+        std::unique_lock<std::shared_mutex> lk(top->rw);
         top->normalized = false;
         for (tfp_store* sh : m->shards) store_mark_not_normalized(sh);
     }
@@ -324,7 +326,7 @@ static int multi_delete(tfp_store* top, const float* keys, int64_t n, int dim, i
     tfp_multi* m = top->multi;
     if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203
     if (!keys || dim <= 0) return fail(2, "tfp_store_delete: keys is NULL or dim <= 0");
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::lock_guard<std::mutex> mut(top->mut_mu);
     if (multi_latch(top, dim, "Trying to delete key with length %d when existing length is %d")) return 1;
     if (out_ids) for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     Routed r;
@@ -350,7 +352,7 @@ static int multi_get(tfp_store* top, const float* keys, int64_t n, int dim, int6
     if (out_n_found) *out_n_found = 0;
     if (n == 0) return fail(1, "no keys to get");   // reference panics here (store.go:276); documented deviation
     if (!keys || dim <= 0 || !out_ids) return fail(2, "tfp_store_get: NULL argument or dim <= 0");
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::lock_guard<std::mutex> mut(top->mut_mu);
     if (multi_latch(top, dim, "Try to get a key with length %d when existing length is %d")) return 1;
     for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     Routed r;
@@ -429,29 +431,28 @@ static int multi_find_device(tfp_multi* m, MultiLane& L, const float* q, int nq,
         if (set_device(sh)) return -1;
         int r = ctx_upload_locked(c, q, nq, dim, qi);
         if (r) return r;
-        r = p2p_launch_locked(c, 0, nq, topk, with_keys);
+        r = p2p_launch_locked(c, 0, nq, topk, with_keys, /*defer_merge=*/true);
         if (r) return r;
         launched[(size_t)g] = 1;
         return 0;
     });
     tfp_find_ctx* root = L.ctx[0];
     if (rc) {
-        // A shard could not launch.  If shard 0's merge kernel is already waiting for that shard's word, raise the word
-        // from the host so that the kernel can finish; the answer is discarded.
-        if (launched[0]) {
-            set_device(m->shards[0]);
-            unsigned int* words = (unsigned int*)(root->xbuf.as<uint8_t>() + xbuf_flags_offset(G, m->slot_bytes));
-            const unsigned int seq = root->x_seq;
-            for (int g = 1; g < G; g++)
-                if (!launched[(size_t)g]) cudaMemcpyAsync(words + g, &seq, 4, cudaMemcpyHostToDevice, m->shards[0]->s_mut);
-            cudaStreamSynchronize(m->shards[0]->s_mut);
-            cudaStreamSynchronize(root->stream);
-        }
-        for (int g = 0; g < G; g++) L.ctx[(size_t)g]->x_seq = root->x_seq;   // keep the lane's sequence numbers together
+        // A shard could not launch: no merge is enqueued (nothing waits for the missing records); bring the lane's
+        // sequence numbers back together so that the next find on it pairs up again.
+        unsigned int top_seq = 0;
+        for (int g = 0; g < G; g++) top_seq = std::max(top_seq, L.ctx[(size_t)g]->x_seq);
+        for (int g = 0; g < G; g++) L.ctx[(size_t)g]->x_seq = top_seq;
         return rc;
     }
-    if (out_path) *out_path = root->last_path;
+    // every shard's scan is in its stream: now the merge kernel, which waits for their records, can go in
     if (set_device(m->shards[0])) return -1;
+    {
+        std::shared_lock<std::shared_mutex> lk(m->shards[0]->rw);
+        rc = p2p_merge_locked(root);
+        if (rc) return rc;
+    }
+    if (out_path) *out_path = root->last_path;
     return with_keys ? tfp_find_ctx_download_merged_keys(root, out_n, out_ids, out_sims, out_keys)
                      : tfp_find_ctx_download_merged(root, out_n, out_ids, out_sims, nullptr, nullptr);
 }
@@ -550,7 +551,7 @@ struct MultiManifest {
 
 static int multi_save(tfp_store* top, const char* path, uint64_t tag) {
     tfp_multi* m = top->multi;
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::lock_guard<std::mutex> mut(top->mut_mu);
     MultiManifest mf;
     memset(&mf, 0, sizeof(mf));
     memcpy(mf.magic, "TFPMULT1", 8);
@@ -566,6 +567,7 @@ static int multi_save(tfp_store* top, const char* path, uint64_t tag) {
 
 static int multi_load(tfp_store* top, const char* path) {
     tfp_multi* m = top->multi;
+    std::lock_guard<std::mutex> mut(top->mut_mu);
     std::unique_lock<std::shared_mutex> lk(top->rw);
     if (top->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
     FILE* f = fopen(path, "rb");

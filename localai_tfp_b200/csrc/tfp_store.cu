@@ -271,7 +271,9 @@ struct tfp_store {
     std::mutex err_mu;
     std::string last_err;         // text of the last failing call on this handle, from any thread (tfp_store_last_error)
     int device = 0;
-    std::shared_mutex rw;      // finds: shared while enqueueing; mutations: exclusive
+    std::mutex mut_mu;         // one mutation (set / delete / get / save / load) at a time: owns the staging buffers, the host index and its mirrors
+    std::shared_mutex rw;      // finds: shared while enqueueing.  Mutations take it exclusively only to PUBLISH (row count, flags,
+                               // capacity, tensor maps) and, for overwrites and compaction, to fence the finds; taken after mut_mu
     int dim = -1;              // store.go:29,44 keyLen
     bool normalized = true;    // store.go:27,43 keysAreNormalized (sticky)
     int64_t n = 0, cap = 0, cap_hint = 0;
@@ -325,6 +327,8 @@ struct tfp_find_ctx {
     unsigned int x_seq = 0;
     bool x_ready = false;
     bool x_root_mode = false;            // one process over several GPUs: records are gathered on shard 0 only
+    int x_m_count = 0;                   // the pending peer-exchange merge: queries, and whether key rows travel too
+    bool x_m_with_keys = false;
     bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
     bool keys_gathered = false;          // the last launch's scan kernels wrote the winning key rows themselves
     int64_t mma_passes = 0, mma_fallbacks = 0;
@@ -567,7 +571,7 @@ struct Lookup {
 static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::vector<int64_t>& order, Lookup& L) {
     const int dim = s->dim;
     if (s->st_hash.reserve((size_t)n * 8) || s->st_knorm.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
-    int threads = 128;
+    int threads = kStatRows;
     int64_t blocks = (n + threads - 1) / threads;
     row_stats_kernel<<<(unsigned)blocks, threads, 0, s->s_mut>>>(d_rows, n, dim, s->st_hash.as<uint64_t>(),
                                                                s->st_knorm.as<double>(), s->st_isnorm.as<uint8_t>());
@@ -624,13 +628,18 @@ static int stage_rows(tfp_store* s, const float* keys, int64_t n, int dim, const
     return 0;
 }
 
+// Caller holds mut_mu (not rw).  Pure appends never stop the finds: new rows land beyond the published row count,
+// which a scan launched earlier never reads (a tile that straddles the old end loads them and masks them), HBM
+// grows by mapping more memory behind the same addresses, and the new row count is published -- under the
+// exclusive lock, for the instant that takes -- only after the rows are in place.  An overwrite of a stored row
+// (store.go:183-187) or a grow that has to move the arrays (no virtual memory management) fences the finds first.
 static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_ids, uint8_t* out_was_new) {
     const int dim = s->dim;
     Lookup L;
     std::vector<int64_t> order;
     if (lookup_rows(s, d_rows, n, order, L)) return -1;
-    // sticky flag (store.go:125-135)
-    for (int64_t i = 0; i < n; i++) if (!L.is_norm[(size_t)i]) { s->normalized = false; break; }
+    bool all_norm = true;                                  // sticky flag (store.go:125-135)
+    for (int64_t i = 0; i < n; i++) if (!L.is_norm[(size_t)i]) { all_norm = false; break; }
 
     std::vector<uint32_t> src((size_t)n), dst((size_t)n);
     std::vector<int64_t> ids((size_t)n);
@@ -649,7 +658,19 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         }
         if (out_ids) out_ids[i] = ids[(size_t)i];
     }
-    if (ensure_capacity(s, s->n + n_new)) return -1;
+    const bool overwrites = n_new != n;
+    const bool must_move = s->n + n_new > s->cap && !(vmm_api() && (s->vm_keys.active() || s->cap == 0));
+    std::unique_lock<std::shared_mutex> fence(s->rw, std::defer_lock);
+    if (overwrites || must_move) {
+        fence.lock();
+        if (quiesce_finds(s)) return -1;
+    }
+    if (s->n + n_new > s->cap) {
+        // growing changes what finds read when they launch (capacity, tensor maps, the first time the base addresses)
+        std::unique_lock<std::shared_mutex> grow(s->rw, std::defer_lock);
+        if (!fence.owns_lock()) grow.lock();
+        if (ensure_capacity(s, s->n + n_new)) return -1;
+    }
     if (s->st_src.reserve((size_t)n * 4) || s->st_dst.reserve((size_t)n * 4) || s->st_ids.reserve((size_t)n * 8)) return -1;
     CU_OK(cudaMemcpyAsync(s->st_src.p, src.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
     CU_OK(cudaMemcpyAsync(s->st_dst.p, dst.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
@@ -659,7 +680,7 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
                                                              s->st_dst.as<uint32_t>(), s->st_ids.as<int64_t>(), n, dim,
                                                              s->d_keys, s->d_ids, s->d_knorm);
     CU_OK(cudaGetLastError());
-    // host mirrors and index
+    // host mirrors and index (mutation-side state: mut_mu)
     s->slot_hash.resize((size_t)(s->n + n_new));
     s->slot_id.resize((size_t)(s->n + n_new));
     s->index.reserve((size_t)(s->n + n_new));
@@ -671,9 +692,22 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
             s->index.insert(L.hash[(size_t)i], slot);
         }
     }
-    s->n += n_new;
-    s->next_id += n_new;
-    CU_OK(cudaStreamSynchronize(s->s_mut));
+    CU_OK(cudaStreamSynchronize(s->s_mut));   // the rows are in HBM ...
+    {                                         // ... now finds may see them
+        std::unique_lock<std::shared_mutex> pub(s->rw, std::defer_lock);
+        if (!fence.owns_lock()) pub.lock();
+        s->n += n_new;
+        s->next_id += n_new;
+        if (!all_norm) s->normalized = false;
+    }
+    return 0;
+}
+
+// store.go:115-116 / :209-210 / :275-276: the first Set, Delete or Get fixes the key length.
+static int latch_dim(tfp_store* s, int dim, const char* fmt) {
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (s->dim == -1) s->dim = dim;
+    else if (dim != s->dim) return fail(1, fmt, dim, s->dim);
     return 0;
 }
 
@@ -689,11 +723,9 @@ static int store_set(tfp_store* s, const float* keys, int64_t n, int dim, int64_
     if (n != n_values) return fail(1, "len(keys) = %lld, len(values) = %lld", (long long)n, (long long)n_values);  // :111-113
     if (!keys || dim <= 0) return fail(2, "tfp_store_set: keys is NULL or dim <= 0");
     if (check_scatter_grid(n)) return 2;
-    std::unique_lock<std::shared_mutex> lk(s->rw);
-    if (s->dim == -1) s->dim = dim;                                                  // :115-116
-    else if (dim != s->dim)
-        return fail(1, "Try to add key with length %d when existing length is %d", dim, s->dim);  // :118-120
-    if (set_device(s) || quiesce_finds(s)) return -1;
+    std::lock_guard<std::mutex> mut(s->mut_mu);
+    if (latch_dim(s, dim, "Try to add key with length %d when existing length is %d")) return 1;   // :115-120
+    if (set_device(s)) return -1;
     const float* d_rows = nullptr;
     if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
     return set_impl(s, d_rows, n, out_ids, out_was_new);
@@ -705,10 +737,9 @@ static int store_set_device(tfp_store* s, const float* d_keys, int64_t n, int di
     if (n == 0) return fail(1, "no keys to add");
     if (!d_keys || dim <= 0) return fail(2, "tfp_store_set_device: d_keys is NULL or dim <= 0");
     if (check_scatter_grid(n)) return 2;
-    std::unique_lock<std::shared_mutex> lk(s->rw);
-    if (s->dim == -1) s->dim = dim;
-    else if (dim != s->dim) return fail(1, "Try to add key with length %d when existing length is %d", dim, s->dim);
-    if (set_device(s) || quiesce_finds(s)) return -1;
+    std::lock_guard<std::mutex> mut(s->mut_mu);
+    if (latch_dim(s, dim, "Try to add key with length %d when existing length is %d")) return 1;
+    if (set_device(s)) return -1;
     CU_OK(cudaDeviceSynchronize());   // the caller's producer stream is unknown: order after all of it
     return set_impl(s, d_keys, n, out_ids, out_was_new);
 }
@@ -728,10 +759,8 @@ static int store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_
     if (out_n_found) *out_n_found = 0;
     if (n == 0) return fail(1, "no keys to get");   // reference panics here (store.go:276); documented deviation
     if (!keys || dim <= 0 || !out_ids) return fail(2, "tfp_store_get: NULL argument or dim <= 0");
-    std::unique_lock<std::shared_mutex> lk(s->rw);   // uses the mutation staging buffers
-    if (s->dim == -1) s->dim = dim;                                                  // :275-276
-    else if (dim != s->dim)
-        return fail(1, "Try to get a key with length %d when existing length is %d", dim, s->dim);  // :278-280
+    std::lock_guard<std::mutex> mut(s->mut_mu);      // uses the mutation staging buffers and the host index; finds go on
+    if (latch_dim(s, dim, "Try to get a key with length %d when existing length is %d")) return 1;   // :275-280
     if (set_device(s)) return -1;
     std::vector<int64_t> order;
     sorted_order(keys, n, dim, order);
@@ -759,13 +788,11 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
     if (!s) return fail(2, "tfp_store_delete: store is NULL");
     if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203
     if (!keys || dim <= 0) return fail(2, "tfp_store_delete: keys is NULL or dim <= 0");
-    std::unique_lock<std::shared_mutex> lk(s->rw);
-    if (s->dim == -1) s->dim = dim;                                                  // :209-210
-    else if (dim != s->dim)
-        return fail(1, "Trying to delete key with length %d when existing length is %d", dim, s->dim);  // :212-214
+    std::lock_guard<std::mutex> mut(s->mut_mu);
+    if (latch_dim(s, dim, "Trying to delete key with length %d when existing length is %d")) return 1;   // :209-214
     if (out_ids) for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     if (s->n == 0) return 0;
-    if (set_device(s) || quiesce_finds(s)) return -1;
+    if (set_device(s)) return -1;
     std::vector<int64_t> order;
     sorted_order(keys, n, dim, order);
     const float* d_rows = nullptr;
@@ -781,6 +808,9 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
         }
     }
     if (holes.empty()) return 0;
+    // compaction moves rows that running scans read, and shrinks the row count: fence the finds (the look-up above did not)
+    std::unique_lock<std::shared_mutex> lk(s->rw);
+    if (quiesce_finds(s)) return -1;
     const int64_t new_n = s->n - (int64_t)holes.size();
     std::vector<uint8_t> dead((size_t)(s->n - new_n), 0);   // marks deleted slots in the tail [new_n, n)
     for (uint32_t h : holes) {
@@ -853,8 +883,9 @@ static int write_file_atomically(const char* path, Body&& body) {
 
 static int store_save(tfp_store* s, const char* path, uint64_t tag) {
     if (!s || !path) return fail(2, "tfp_store_save: NULL argument");
-    std::unique_lock<std::shared_mutex> lk(s->rw);
-    if (set_device(s) || quiesce_finds(s)) return -1;
+    std::lock_guard<std::mutex> mut(s->mut_mu);
+    std::shared_lock<std::shared_mutex> lk(s->rw);   // finds only read: they may go on while the rows are copied out
+    if (set_device(s)) return -1;
     SnapHeader h;
     memcpy(h.magic, "TFPSTOR2", 8);
     h.dim = s->dim; h.normalized = s->normalized ? 1 : 0; h.rows = s->n; h.next_id = s->next_id; h.tag = tag;
@@ -881,6 +912,7 @@ static int store_save(tfp_store* s, const char* path, uint64_t tag) {
 
 static int store_load(tfp_store* s, const char* path) {
     if (!s || !path) return fail(2, "tfp_store_load: NULL argument");
+    std::lock_guard<std::mutex> mut(s->mut_mu);
     std::unique_lock<std::shared_mutex> lk(s->rw);
     if (s->n != 0 || s->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
     if (set_device(s)) return -1;
@@ -924,7 +956,7 @@ static int store_load(tfp_store* s, const char* path) {
     const int64_t n = h.rows;
     auto rebuild = [&]() -> int {
         if (s->st_hash.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
-        row_stats_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s->s_mut>>>(s->d_keys, n, s->dim, s->st_hash.as<uint64_t>(),
+        row_stats_kernel<<<(unsigned)((n + kStatRows - 1) / kStatRows), kStatRows, 0, s->s_mut>>>(s->d_keys, n, s->dim, s->st_hash.as<uint64_t>(),
                                                                             s->d_knorm, s->st_isnorm.as<uint8_t>());
         CU_OK(cudaGetLastError());
         s->slot_hash.resize((size_t)n);
@@ -1879,7 +1911,12 @@ static int launch_merge(tfp_find_ctx* c, const uint8_t* gathered, size_t shard_s
 
 // Peer exchange of one sharded find (see the block comment above tfp_find_ctx_p2p_export).
 // with_keys: the winning key rows travel too, so that the merged answer carries StoresFindResult.Keys.
-static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bool with_keys) {
+static int p2p_merge_locked(tfp_find_ctx* c);
+
+// defer_merge: enqueue the scan and the pushes only; the caller enqueues the merge later with p2p_merge_locked
+// (one process over several GPUs: shard 0's waiting merge kernel is launched once every shard's scan is in its
+// stream, so that nothing the host still has to do can end up waiting behind a kernel that waits for it).
+static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bool with_keys, bool defer_merge = false) {
     tfp_store* s = c->st;
     const unsigned int seq = c->x_seq + 1;
     const size_t par_off = (size_t)(seq & 1u) * c->x_world * c->x_slot;
@@ -1918,12 +1955,29 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
         CU_OK(cudaGetLastError());
         c->launches++;
     }
+    c->x_m_count = count;
+    c->x_m_with_keys = with_keys;
     if (c->x_root_mode && c->x_me != 0) return 0;   // only shard 0 merges
+    if (defer_merge) return 0;
+    return p2p_merge_locked(c);
+}
+
+// Second half of a peer-exchange find: wait for the peers' records of find x_seq, merge, gather the winners' rows.
+static int p2p_merge_locked(tfp_find_ctx* c) {
+    tfp_store* s = c->st;
+    const unsigned int seq = c->x_seq;
+    const int count = c->x_m_count, k = c->last_topk, dim = s->dim;
+    const bool with_keys = c->x_m_with_keys;
+    const size_t par_off = (size_t)(seq & 1u) * c->x_world * c->x_slot;
+    const size_t flags_off = xbuf_flags_offset(c->x_world, c->x_slot);
+    const size_t rb = record_bytes(k);
+    const size_t keys_off = (rb * count + 255) & ~(size_t)255;
     unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + flags_off);
     // The merge kernel waits for the peers' words itself (default).  TFP_XCHG_STREAM_WAIT=1 keeps the wait in the
     // stream instead: one cuStreamWaitValue32 per peer, measured 7 driver calls + a late kernel launch per find.
     const bool kernel_wait = !tuning().xchg_stream_wait;
     if (!kernel_wait) {
+        if (wait32_api()) return -7;
         for (int r = 0; r < c->x_world; r++) {
             if (r == c->x_me) continue;
             CUresult wr = g_wait32((CUstream)c->stream, (CUdeviceptr)(words + r), seq, CU_STREAM_WAIT_VALUE_GEQ);
@@ -1934,7 +1988,7 @@ static int p2p_launch_locked(tfp_find_ctx* c, int first, int count, int topk, bo
     MergedLayout L(k, count);
     const size_t want = L.total + (with_keys ? (size_t)count * k * dim * 4 : 0);
     if (c->merged.reserve(want)) return -1;
-    rc = launch_merge(c, block, c->x_slot, rb, c->x_world, count, k, kernel_wait ? words : nullptr, c->x_me, seq);
+    int rc = launch_merge(c, block, c->x_slot, rb, c->x_world, count, k, kernel_wait ? words : nullptr, c->x_me, seq);
     if (rc) return rc;
     c->merged_keys_dim = 0;
     if (with_keys) {
