@@ -606,7 +606,8 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
                                    if sh.exchange == "p2p" else "one all-gather of top-k records + device merge per query")
                                   if world > 1 else "single GPU"},
         "clocks": clk,
-        "tensor_core_path": dict(zip(("passes", "exact_reruns"), ctx.mma_counters())) if batched else None,
+        "tensor_core_path": dict(zip(("passes", "exact_reruns", "escalated_to_3xtf32"), ctx.mma_counters() + (ctx.mma_escalated,)))
+                            if batched else None,
         "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
         "roofline": roof,

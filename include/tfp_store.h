@@ -209,10 +209,13 @@ int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d
  * address: [count x stride x dim] floats, stride as returned by
  * tfp_find_ctx_device_results (what StoresFindResult.Keys is built from). */
 int  tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys);
-/* How often this context took the tensor-core path (batches of >= 3 same-path queries on a
- * store of >= 65536 rows: tcgen05 3xTF32 filter + exact re-score) and how many queries it then had to
- * re-run on the exact scan kernel.  Either pointer may be NULL. */
+/* How often this context ran a tensor-core pass over the keys (batches of >= 3 same-path queries on a
+ * store of >= 65536 rows: tcgen05 single-TF32 filter on CTA pairs + exact re-score) and how many queries
+ * it then had to re-run on the exact scan kernel.  Either pointer may be NULL.
+ * tfp_find_ctx_mma_escalated: queries whose scores lay too close together for the single-TF32 filter
+ * and went through a second pass with the 3xTF32 filter (counted in `passes` too). */
 int  tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64_t* exact_reruns);
+int64_t tfp_find_ctx_mma_escalated(tfp_find_ctx* c);
 /* Number of kernels the context has launched so far (for bench accounting). */
 int64_t tfp_find_ctx_launch_count(tfp_find_ctx* c);
 

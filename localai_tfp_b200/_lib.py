@@ -57,6 +57,7 @@ PROTOTYPES = {
     "tfp_find_ctx_device_results": (C.c_int, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "tfp_find_ctx_gather_keys": (C.c_int, [vp, C.POINTER(vp)]),
     "tfp_find_ctx_mma_counters": (C.c_int, [vp, i64p, i64p]),
+    "tfp_find_ctx_mma_escalated": (C.c_int64, [vp]),
     "tfp_find_ctx_launch_count": (C.c_int64, [vp]),
     "tfp_record_bytes": (C.c_size_t, [C.c_int]),
     "tfp_find_ctx_device_records": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),

@@ -205,12 +205,14 @@ __device__ __forceinline__ void tf32_split(float a, float& hi, float& lo) {
 }
 
 // ---- query preparation: [nq x D] -> hi parts in rows [0, nqp), lo parts in rows [nqp, 2 nqp) -------
-__global__ void qsplit_kernel(const float* __restrict__ q, int nq, int nqp, int dim, float* __restrict__ out) {
+// Row r of the pass is staged query qmap[r] (a pass may serve any subset of the staged queries).
+__global__ void qsplit_kernel(const float* __restrict__ q, const int* __restrict__ qmap, int nq, int nqp, int dim,
+                              float* __restrict__ out) {
     const size_t total = (size_t)nqp * dim;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         const int r = (int)(i / dim);
         float hi = 0.0f, lo = 0.0f;
-        if (r < nq) tf32_split(q[i], hi, lo);
+        if (r < nq) tf32_split(q[(size_t)qmap[r] * dim + (i - (size_t)r * dim)], hi, lo);
         out[i] = hi;
         out[total + i] = lo;
     }
@@ -609,7 +611,8 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
 struct FinalizeParams {
     const float* keys; const int64_t* ids; const double* knorm;
     uint32_t n_rows; int dim;
-    const float* q; const QInfo* qinfo; int q_first;     // original (unsplit) staged queries
+    const float* q; const QInfo* qinfo; int q_first;     // original (unsplit) staged queries; q_first: the staged query of output slot out_first
+    const int* qmap;                                     // [nq] staged query served by each query of this pass
     const uint64_t* cand; const unsigned int* cand_cnt;
     int topk;
     int out_first;
@@ -719,8 +722,9 @@ mma_finalize_kernel(const FinalizeParams p) {
     const int C = C_all < kMmaRescoreMax ? C_all : kMmaRescoreMax;
     const uint32_t cut_order = cut;                      // 3xTF32: rows not re-scored all score below this
     // exact re-score, one thread per candidate row, the reference's arithmetic (scan.cuh Acc<>)
-    const float* qv = p.q + (size_t)(p.q_first + q) * p.dim;
-    const double mag1 = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    const int sq = p.qmap[q];                            // the staged query this block serves
+    const float* qv = p.q + (size_t)sq * p.dim;
+    const double mag1 = F64 ? p.qinfo[sq].mag1 : 0.0;
     // The query goes to shared memory (the score words there are dead now): every thread reads all of it, and
     // left in global memory its lines are pushed out of L1 by the key rows streaming through -- each chunk of
     // the walk then waited a full L2 round trip for its query values (measured: 78 % of this kernel).
@@ -776,7 +780,7 @@ mma_finalize_kernel(const FinalizeParams p) {
     __syncthreads();
     block_sort_desc(exact, PE, tid, blockDim.x);
     const int m = C < lim ? C : lim;
-    const int o = p.out_first + q;
+    const int o = p.out_first + (sq - p.q_first);
     for (int i = tid; i < k; i += blockDim.x) {
         size_t at = (size_t)o * k + i;
         if (i < m) {

@@ -331,7 +331,7 @@ struct tfp_find_ctx {
     bool x_m_with_keys = false;
     bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
     bool keys_gathered = false;          // the last launch's scan kernels wrote the winning key rows themselves
-    int64_t mma_passes = 0, mma_fallbacks = 0;
+    int64_t mma_passes = 0, mma_fallbacks = 0, mma_escalated = 0;
     // Results of the last launch live in ONE block so that a download is one D2H copy:
     // [n | ids | sims | key rows] first (what the host reads), then [cand | slots | records].
     DevBuf out_block;
@@ -1100,39 +1100,42 @@ static int launch_scan_nq(tfp_find_ctx* c, int nq, const ScanParams& p, bool use
     }
 }
 
-// Tensor-core path for one group of g same-path queries (staged [q0, q0+g), outputs from slot o0).
-// Enqueues: query split, bound-only pass, full pass, finalize; then reads the per-query status and
-// re-runs flagged queries on the exact scan kernel.  `exact_one` launches that kernel for one query.
-template <class ExactOne>
-static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o0, int g, bool norm, int grid,
-                            ExactOne&& exact_one) {
+// One tensor-core pass over the keys for g same-path staged queries named by index: h_qidx[j] is a staged query,
+// its answer goes to output slot o_base + (h_qidx[j] - q_base).  Enqueues query split, bound-only pass, full pass
+// and finalize with the `terms`-TF32 filter (1 or 3), then the copy of the per-query status words to h_status.
+static int mma_pass_launch(tfp_find_ctx* c, const ScanParams& sp, const int* h_qidx, int g, int q_base, int o_base, bool norm,
+                           int grid, int terms) {
     tfp_store* s = c->st;
     const int dim = s->dim;
     const int nqp = (g + 15) & ~15;
-    const int terms = tuning().mma_terms;
-    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 4 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
+    const size_t small_bytes = (size_t)kMmaMaxNQ * 4 * 5 + (size_t)kMaxGrid * kMmaMaxNQ * 4;
     if (c->mma_qsplit.reserve((size_t)2 * kMmaMaxNQ * dim * 4 + 256) || c->mma_cand.reserve((size_t)kMmaMaxNQ * kMmaCandCap * 8) ||
-        c->mma_small.reserve(small_bytes) || c->h_status.reserve(kMmaMaxNQ * 4)) return -1;
+        c->mma_small.reserve(small_bytes) || c->h_status.reserve(kMmaMaxNQ * 12)) return -1;
     unsigned int* cand_cnt = c->mma_small.as<unsigned int>();     // cand_cnt and gbound are adjacent: one memset per batch
     unsigned int* gbound = cand_cnt + kMmaMaxNQ;
     int* status = (int*)(gbound + kMmaMaxNQ);
     float* eps = (float*)(status + kMmaMaxNQ);
-    unsigned int* lbest2 = (unsigned int*)(eps + kMmaMaxNQ);
+    int* qmap = (int*)(eps + kMmaMaxNQ);
+    unsigned int* lbest2 = (unsigned int*)(qmap + kMmaMaxNQ);
     float* qs = c->mma_qsplit.as<float>();
-    if (terms == 1) {
-        // |approx - exact| <= (2^-9 + D 2^-23) |q| |k|: TF32 drops < 2^-10 of each operand, the D term covers the
-        // reference's own fp32 rounding.  Normalised path: |q|, |k| <= 1.01.  Cosine path: the approximate score
-        // is dot / |k|, so the bound scales with |q| only.  5 % slack on top.
-        if (c->h_status.reserve(kMmaMaxNQ * 8)) return -1;
-        float* he = c->h_status.as<float>() + kMmaMaxNQ;
-        const float unit = (1.0f / 512.0f + (float)dim / 8388608.0f) * 1.05f;
-        for (int j = 0; j < g; j++)
-            he[j] = norm ? unit * 1.0201f : unit * (float)c->qinfo[(size_t)(q0 + j)].mag1;
-        CU_OK(cudaMemcpyAsync(eps, he, (size_t)g * 4, cudaMemcpyHostToDevice, c->stream));
+    // pinned staging: [status | eps | qmap], one H2D copy for eps + qmap
+    float* he = c->h_status.as<float>() + kMmaMaxNQ;
+    int* hq = (int*)(he + kMmaMaxNQ);
+    // Single-TF32 filter: |approx - exact| <= eps = unit |q| |k| with
+    //   unit = 2^-9 + 2^-20   the operands lose < 2^-10 of their value each (TF32 keeps 10 mantissa bits), Cauchy-Schwarz
+    //        + 2 D 2^-23      the tensor core's fp32 accumulation (adds that may truncate: D 2^-23) and the reference's own
+    //                         sequential fp32 rounding (D 2^-24), rounded up
+    // Normalised path: |q|, |k| <= 1.01.  Cosine path: the approximate score is dot / |k|, so the bound scales with
+    // |q| only (+ 2^-22 for the fp32 reciprocal and multiply).  2 % slack on top.
+    const float unit = (1.0f / 512.0f + 1.0f / 1048576.0f + 2.0f * (float)dim / 8388608.0f + 1.0f / 4194304.0f) * 1.02f;
+    for (int j = 0; j < g; j++) {
+        he[j] = terms == 1 ? (norm ? unit * 1.0201f : unit * (float)c->qinfo[(size_t)h_qidx[j]].mag1) : 0.0f;
+        hq[j] = h_qidx[j];
     }
+    for (int j = g; j < kMmaMaxNQ; j++) { he[j] = 0.0f; hq[j] = h_qidx[0]; }
+    CU_OK(cudaMemcpyAsync(eps, he, (size_t)2 * kMmaMaxNQ * 4, cudaMemcpyHostToDevice, c->stream));
 
-    qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(
-        sp.q + (size_t)q0 * dim, g, nqp, dim, qs);
+    qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(sp.q, qmap, g, nqp, dim, qs);
     CU_OK(cudaGetLastError());
     CU_OK(cudaMemsetAsync(cand_cnt, 0, (size_t)2 * kMmaMaxNQ * 4, c->stream));   // candidate counts and grid-wide bounds
 
@@ -1169,7 +1172,7 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     if (mp.n_stages < 2) return fail(-4, "internal: tensor-core stages do not fit shared memory");
     const size_t smem = mma_smem_bytes(nqp, terms, mp.n_stages, pair);
     if (tuning().mma_trace)
-        fprintf(stderr, "tfp mma: terms=%d pair=%d nqp=%d stages=%d smem=%zu grid=%d\n", terms, (int)pair, nqp, mp.n_stages, smem, grid);
+        fprintf(stderr, "tfp mma: terms=%d pair=%d nq=%d nqp=%d stages=%d smem=%zu grid=%d\n", terms, (int)pair, g, nqp, mp.n_stages, smem, grid);
     auto launch_pass = [&]() -> int {
         if (pair) {
             cudaLaunchConfig_t cfg;
@@ -1198,8 +1201,8 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     FinalizeParams fp;
     memset(&fp, 0, sizeof(fp));
     fp.keys = sp.keys; fp.ids = sp.ids; fp.knorm = sp.knorm; fp.n_rows = sp.n_rows; fp.dim = dim;
-    fp.q = sp.q; fp.qinfo = sp.qinfo; fp.q_first = q0;
-    fp.cand = mp.cand; fp.cand_cnt = cand_cnt; fp.topk = sp.topk; fp.out_first = o0;
+    fp.q = sp.q; fp.qinfo = sp.qinfo; fp.q_first = q_base; fp.qmap = qmap;
+    fp.cand = mp.cand; fp.cand_cnt = cand_cnt; fp.topk = sp.topk; fp.out_first = o_base;
     fp.out_cand = sp.out_cand; fp.out_ids = sp.out_ids; fp.out_sims = sp.out_sims; fp.out_slots = sp.out_slots;
     fp.out_n = sp.out_n; fp.out_rec = sp.out_rec; fp.rec_bytes = sp.rec_bytes; fp.rec_topk = sp.rec_topk;
     fp.status = status;
@@ -1214,18 +1217,44 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
     CU_OK(cudaGetLastError());
     c->launches += 5;
     c->mma_passes++;
-    // the status decides whether a query must be re-run exactly; this is the one place a launch waits
     CU_OK(cudaMemcpyAsync(c->h_status.p, status, (size_t)g * 4, cudaMemcpyDeviceToHost, c->stream));
-    CU_OK(cudaStreamSynchronize(c->stream));
-    const int* hs = c->h_status.as<int>();
-    for (int j = 0; j < g; j++) {
-        if (hs[j] != 0 && !mp.debug) {   // (development timing runs skip the exact re-run)
+    return 0;
+}
+
+// Tensor-core path for one group of g same-path queries (staged [q0, q0+g), outputs from slot o0).  The filter only
+// has to be good enough to leave few rows to re-score exactly; when it is not -- scores so close together that the
+// single-TF32 error band holds more rows than can be re-scored, or a candidate list that overflowed -- the flagged
+// queries go, TOGETHER, through one more pass with the 3xTF32 filter (error ~1e-6 instead of ~2e-3), and only what
+// that cannot settle either is re-run, query by query, on the exact scan kernel.  `exact_one` launches that kernel.
+// The status words decide the escalation, so this is the one place a launch waits for the GPU.
+template <class ExactOne>
+static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o0, int g, bool norm, int grid,
+                            ExactOne&& exact_one) {
+    std::vector<int> idx((size_t)g);
+    for (int j = 0; j < g; j++) idx[(size_t)j] = q0 + j;
+    int terms = tuning().mma_terms;
+    for (;;) {
+        int rc = mma_pass_launch(c, sp, idx.data(), (int)idx.size(), q0, o0, norm, grid, terms);
+        if (rc) return rc;
+        CU_OK(cudaStreamSynchronize(c->stream));
+        if (tuning().mma_debug) return 0;   // (development timing runs skip the re-runs)
+        const int* hs = c->h_status.as<int>();
+        std::vector<int> flagged;
+        for (size_t j = 0; j < idx.size(); j++) if (hs[j] != 0) flagged.push_back(idx[j]);
+        if (flagged.empty()) return 0;
+        if (terms == 1 && flagged.size() >= 3) {   // (one or two queries: an exact scan each costs no more than another pass)
+            c->mma_escalated += (int64_t)flagged.size();
+            idx.swap(flagged);
+            terms = 3;
+            continue;
+        }
+        for (int qi : flagged) {
             c->mma_fallbacks++;
-            int rc = exact_one(q0 + j, o0 + j);
+            rc = exact_one(qi, o0 + (qi - q0));
             if (rc) return rc;
         }
+        return 0;
     }
-    return 0;
 }
 
 // Enqueue the scan(s) for staged queries [first, first+count).  Caller holds the shared lock.
@@ -1520,6 +1549,7 @@ extern "C" int tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64
     if (exact_reruns) *exact_reruns = c->mma_fallbacks;
     return 0;
 }
+extern "C" int64_t tfp_find_ctx_mma_escalated(tfp_find_ctx* c) { return c ? c->mma_escalated : 0; }
 extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids, float** d_sims, int** d_n) {
     if (!c) return fail(2, "tfp_find_ctx_device_results: ctx is NULL");
     if (d_cand) *d_cand = c->out_cand;

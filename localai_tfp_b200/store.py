@@ -298,11 +298,12 @@ class Store:
         return FindContext(self)
 
     def mma_counters(self):
-        """(tensor-core passes, queries re-run exactly) of the built-in context that serves find_batch."""
+        """(tensor-core passes, queries escalated to the 3xTF32 filter, queries re-run exactly) of the built-in
+        context that serves find_batch."""
         a, b = C.c_int64(), C.c_int64()
         ctx = C.c_void_p(self._L.tfp_store_default_ctx(self._h))
         self._check(self._L.tfp_find_ctx_mma_counters(ctx, C.byref(a), C.byref(b)))
-        return a.value, b.value
+        return a.value, int(self._L.tfp_find_ctx_mma_escalated(ctx)), b.value
 
 
 class FindContext:
@@ -439,6 +440,11 @@ class FindContext:
         a, b = C.c_int64(), C.c_int64()
         self.store._check(self._L.tfp_find_ctx_mma_counters(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    @property
+    def mma_escalated(self) -> int:
+        """Queries that needed a second tensor-core pass with the 3xTF32 filter so far on this context."""
+        return int(self._L.tfp_find_ctx_mma_escalated(self._h))
 
     def device_records(self):
         """(device address, record_bytes) of the last launch's packed per-query records."""

@@ -17,6 +17,7 @@ def run_batch(tfp, oracle, K, Q, k, normalized, expect_mma=True):
     c.launch(0, len(Q), k)
     res = c.download()
     passes, reruns = c.mma_counters()
+    run_batch.escalated = c.mma_escalated
     if expect_mma:
         assert passes >= 1, "the batch did not take the tensor-core path"
     for i in range(len(Q)):
@@ -73,7 +74,38 @@ def test_mma_path_band_wider_than_the_rescore_budget_reruns_exactly(tfp, oracle)
     K[:3000] = normalize_rows(base[None, :] + rng.standard_normal((3000, 64)).astype(f32) * f32(1e-5))
     Q = normalize_rows(np.repeat(base[None, :], 32, axis=0) + rng.standard_normal((32, 64)).astype(f32) * f32(1e-4))
     passes, reruns = run_batch(tfp, oracle, K, Q, 20, True)
-    assert reruns >= 1
+    assert reruns >= 1 or run_batch.escalated >= 1     # settled by the 3xTF32 pass or, failing that, by the exact kernel
+
+
+@pytest.mark.parametrize("d,k,nq", [(768, 10, 24), (768, 100, 24), (1536, 10, 8), (4096, 100, 8)])
+@pytest.mark.parametrize("normalized", [True, False])
+def test_mma_path_non_negative_keys(tfp, oracle, d, k, nq, normalized):
+    """The reference's own test distribution: uniform[0,1) components (stores_test.go:326-333).  Every partial sum
+    of q.k grows monotonically (no cancellation, the worst case for accumulation error) and all similarities crowd
+    around 0.75: the filter's error band must still cover the tensor core's fp32 accumulation at every D."""
+    rng = np.random.default_rng(d + k)
+    K = rng.random((66000, d), dtype=np.float32)
+    Q = rng.random((nq, d), dtype=np.float32)
+    if normalized:
+        K, Q = normalize_rows(K), normalize_rows(Q)
+    run_batch(tfp, oracle, K, Q, k, normalized)
+
+
+@pytest.mark.parametrize("k", [10, 100])
+def test_mma_path_tightly_clustered_keys_escalate_to_3xtf32(tfp, oracle, k):
+    """A store whose keys all sit within the single-TF32 error band of each other (a tight cluster: every similarity
+    within ~1e-3): that filter cannot thin the store out, so the flagged queries must go through the 3xTF32 pass
+    TOGETHER -- not one exact scan per query -- and still come back bit-exact."""
+    rng = np.random.default_rng(77 + k)
+    d, n, nq = 768, 70000, 16
+    centre = normalize_rows(rng.standard_normal((1, d)).astype(f32))[0]
+    K = normalize_rows(centre[None, :] + f32(0.05 / np.sqrt(d)) * rng.standard_normal((n, d)).astype(f32))
+    Q = normalize_rows(centre[None, :] + f32(0.05 / np.sqrt(d)) * rng.standard_normal((nq, d)).astype(f32))
+    passes, reruns = run_batch(tfp, oracle, K, Q, k, True)
+    import os
+    if os.environ.get("TFP_MMA_TERMS") != "3":
+        assert run_batch.escalated >= nq // 2 and passes >= 2
+        assert reruns <= nq // 4
 
 
 def test_mma_path_mixed_paths_split_into_runs(tfp, oracle):
