@@ -618,6 +618,85 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
     return out
 
 
+def measure_inproc(env, wl: Workload, args):
+    """The same store as ONE logical store over all N GPUs inside ONE process (tfp_store_open_devices) -- the shape
+    in which LocalAI's loader runs a backend (one process, pkg/model/process.go:94-124).  Rank 0 drives it through
+    the plain tfp_store_find entry point with host buffers from several host threads (each call takes one of the
+    store's find lanes); the other ranks wait.  Wall-clock: this is an end-to-end figure by construction."""
+    import ctypes as C
+    import torch
+    from oracle import oracle as orc
+    from localai_tfp_b200.store import Store
+    world, device = env["world"], env["device"]
+    st = Store(devices=list(range(world)), capacity_rows=wl.n_keys)
+    L = st._L
+    fp, i64p, u8p = C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_uint8)
+    n_blocks = wl.n_keys // BLOCK_ROWS
+    all_ids = np.empty(wl.n_keys, np.int64)
+    pin = torch.empty((BLOCK_ROWS, wl.dim), dtype=torch.float32).pin_memory()
+    for b in range(n_blocks):
+        pin.copy_(gen_block_torch(wl, b, device))
+        new = np.empty(BLOCK_ROWS, np.uint8)
+        ids = all_ids[b * BLOCK_ROWS:(b + 1) * BLOCK_ROWS]
+        st._check(L.tfp_store_set(st._h, C.cast(pin.data_ptr(), fp), BLOCK_ROWS, wl.dim, BLOCK_ROWS,
+                                  ids.ctypes.data_as(i64p), new.ctypes.data_as(u8p)))
+        assert new.all()
+    shard_rows = [int(st.shard_stats(g).rows) for g in range(st.shard_count)]
+    Q = gen_queries(wl)
+    k = wl.topk
+
+    def finder(nfinds, first, out):
+        n = C.c_int()
+        ids = np.empty(k, np.int64); sims = np.empty(k, np.float32)
+        for i in range(nfinds):
+            q = Q[(first + i) % N_QUERIES]
+            st._check(L.tfp_store_find(st._h, q.ctypes.data, wl.dim, k, C.byref(n), ids.ctypes.data, sims.ctypes.data, None, None))
+        out.append((ids.copy(), sims.copy(), (first + nfinds - 1) % N_QUERIES))
+
+    def run(threads, nfinds):
+        outs = []
+        ts = [threading.Thread(target=finder, args=(nfinds, 7 * t, outs)) for t in range(threads)]
+        t0 = time.perf_counter()
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        return time.perf_counter() - t0, outs
+
+    lanes = 4
+    run(lanes, 8)
+    per_thread = max(args.steps, 50)
+    reps = [run(lanes, per_thread)[0] for _ in range(5)]
+    qps = lanes * per_thread / float(np.median(reps))
+    lat = [run(1, per_thread)[0] for _ in range(3)]
+    single_ms = float(np.median(lat)) / per_thread * 1e3
+    # parity: returned rows re-scored by the oracle, and a sample of the store scanned by it
+    order = np.argsort(all_ids)
+    problems = []
+    _, outs = run(4, 1)
+    sample = np.concatenate([gen_block_torch(wl, b, device).cpu().numpy() for b in range(2)])
+    sample_ids = all_ids[:len(sample)]
+    for ids, sims, qi in outs:
+        rows = order[np.searchsorted(all_ids, ids, sorter=order)]
+        keys = np.empty((len(rows), wl.dim), np.float32)
+        for j, r in enumerate(rows):
+            keys[j] = gen_block_torch(wl, int(r) // BLOCK_ROWS, device)[int(r) % BLOCK_ROWS].cpu().numpy()
+        if not np.array_equal(orc.scores_block(keys, Q[qi], True), sims):
+            problems.append(f"q{qi}: returned similarity differs from the oracle's score of the returned row")
+        if not (np.diff(sims.astype(np.float64)) <= 0).all() or len(ids) != k:
+            problems.append(f"q{qi}: bad ordering or count")
+        sc = orc.scores_block(sample, Q[qi], True)
+        if set(sample_ids[sc > sims[-1]].tolist()) - set(ids.tolist()):
+            problems.append(f"q{qi}: a sample row beats the k-th returned similarity but was not returned")
+    st.close()
+    out = {"what": "C2 as ONE logical store over %d GPUs in ONE process (tfp_store_open_devices), driven through tfp_store_find "
+                   "with host buffers from %d host threads" % (world, lanes),
+           "value": qps, "unit": "queries/s", "timing": "wall clock, median of 5 runs of %d finds per thread" % per_thread,
+           "single_find_ms": single_ms, "shard_rows": shard_rows,
+           "parity": {"ok": not problems, "checked_queries": len(outs), "sample_rows_scanned_by_oracle": int(len(sample))}}
+    if problems:
+        out["parity"]["problems"] = problems[:6]
+    return out
+
+
 # ----------------------------------------------------------------------------- our arm
 def run_ours(args, rank: int, local_rank: int, world: int):
     import torch
@@ -654,6 +733,14 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     for sh in cache.values():
         sh.close()
     cache.clear()
+    torch.cuda.empty_cache()
+    if world > 1 and args.inproc and args.workload == "c2" and not any("error" in v for v in also.values()):
+        if rank == 0:
+            try:
+                also["inproc"] = measure_inproc(env, wl, args)
+            except Exception as e:
+                also["inproc"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        dist.barrier()
 
     ok = head["parity"]["ok"] and all(v.get("parity", {}).get("ok", True) for v in also.values())
     if rank == 0:
@@ -686,6 +773,8 @@ def main():
     ap.add_argument("--also", default="auto",
                     help="extra workloads measured after the headline in the same run: auto (target + c3, and c4 on 8 GPUs, "
                          "when the headline is c2), none, or a comma-separated list")
+    ap.add_argument("--inproc", type=int, default=1,
+                    help="N>1: also measure the store as one process over all N GPUs (rank 0 only, after the ranks' own runs)")
     ap.add_argument("--lanes", type=int, default=0,
                     help="single-query finds kept in flight per GPU (find contexts); default 2 on one GPU, 4 on several "
                          "(a sharded find waits for its slowest peer: more finds in flight absorb the skew between ranks)")

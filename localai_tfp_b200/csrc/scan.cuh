@@ -86,6 +86,8 @@ struct ScanParams {
     uint8_t* out_rec;         // [*] packed records (include/tfp_store.h), rec_bytes each, rec_topk slots
     int rec_bytes;
     int rec_topk;
+    int qsel[8];              // use_qsel: the staged queries this launch serves (any subset, e.g. the queries the tensor-core
+    int use_qsel;             //   filter could not settle); output slot of query j = out_first + (qsel[j] - q_first)
     XchgParams xchg;          // fused push of the finished records to the peer ranks (world == 0: off)
     float* out_keys;          // [* x topk x dim] the winning key rows (StoresFindResult.Keys), or nullptr: gathered by a later kernel
 };
@@ -155,6 +157,10 @@ __global__ void gather_merged_rows_kernel(const uint8_t* block, size_t shard_str
     float* dst = out + at * dim;
     for (int t = threadIdx.x; t < dim; t += blockDim.x) dst[t] = __ldcg(src + t);
 }
+
+// Staged query served as query j of a launch, and the output slot its answer goes to.
+__device__ __forceinline__ int scan_query_of(const ScanParams& p, int j) { return p.use_qsel ? p.qsel[j] : p.q_first + j; }
+__device__ __forceinline__ int scan_slot_of(const ScanParams& p, int j) { return p.out_first + (scan_query_of(p, j) - p.q_first); }
 
 // ---- per-row arithmetic ----------------------------------------------------
 template <bool F64> struct Acc;
@@ -406,7 +412,7 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         sel_prune(ms, tid, false);
         if (lstamp && tid == 0 && q == 0) lstamp[3] = globaltimer_ns();
         int m = *ms.cnt;
-        const int o = p.out_first + q;
+        const int o = scan_slot_of(p, q);
         for (int i = tid; i < k; i += kSelThreads) {
             size_t at = (size_t)o * k + i;
             if (i < m) {
@@ -547,7 +553,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             // TMA-stage the queries: one 1-D bulk copy per query
             mbar_arrive_expect_tx(sm.qbar, (uint32_t)(NQ * p.dim * 4));
             for (int q = 0; q < NQ; q++)
-                bulk_load_1d(sm.q + (size_t)q * dpad, p.q + (size_t)(p.q_first + q) * p.dim, (uint32_t)(p.dim * 4),
+                bulk_load_1d(sm.q + (size_t)q * dpad, p.q + (size_t)scan_query_of(p, q) * p.dim, (uint32_t)(p.dim * 4),
                              sm.qbar);
             const uint64_t policy = p.evict_first ? l2_policy_evict_first() : l2_policy_evict_normal();
             int stage = 0;
@@ -607,7 +613,7 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 
     double mag1[NQ];
 #pragma unroll
-    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[scan_query_of(p, q)].mag1 : 0.0;
 
     if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 0] = globaltimer_ns();
     unsigned long long dbg_tiles = 0;
@@ -703,7 +709,7 @@ scan_generic_kernel(const __grid_constant__ ScanParams p) {
     named_bar_sync(kSelBarrier, kSelThreads);
     double mag1[NQ];
 #pragma unroll
-    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[p.q_first + q].mag1 : 0.0;
+    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[scan_query_of(p, q)].mag1 : 0.0;
     const uint32_t n_tiles = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
     unsigned long long last_pub = 0ull;
     for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -719,7 +725,7 @@ scan_generic_kernel(const __grid_constant__ ScanParams p) {
             for (int i = 0; i < p.dim; i++) {
                 const float kv = kr[i];
 #pragma unroll
-                for (int q = 0; q < NQ; q++) acc[q].add(__ldg(p.q + (size_t)(p.q_first + q) * p.dim + i), kv);
+                for (int q = 0; q < NQ; q++) acc[q].add(__ldg(p.q + (size_t)scan_query_of(p, q) * p.dim + i), kv);
             }
         }
         float score[NQ];

@@ -1225,11 +1225,11 @@ static int mma_pass_launch(tfp_find_ctx* c, const ScanParams& sp, const int* h_q
 // has to be good enough to leave few rows to re-score exactly; when it is not -- scores so close together that the
 // single-TF32 error band holds more rows than can be re-scored, or a candidate list that overflowed -- the flagged
 // queries go, TOGETHER, through one more pass with the 3xTF32 filter (error ~1e-6 instead of ~2e-3), and only what
-// that cannot settle either is re-run, query by query, on the exact scan kernel.  `exact_one` launches that kernel.
+// that cannot settle either is re-run on the exact scan kernel, up to 8 queries per pass (`exact_some`).
 // The status words decide the escalation, so this is the one place a launch waits for the GPU.
-template <class ExactOne>
+template <class ExactSome>
 static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o0, int g, bool norm, int grid,
-                            ExactOne&& exact_one) {
+                            ExactSome&& exact_some) {
     std::vector<int> idx((size_t)g);
     for (int j = 0; j < g; j++) idx[(size_t)j] = q0 + j;
     int terms = tuning().mma_terms;
@@ -1248,12 +1248,8 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
             terms = 3;
             continue;
         }
-        for (int qi : flagged) {
-            c->mma_fallbacks++;
-            rc = exact_one(qi, o0 + (qi - q0));
-            if (rc) return rc;
-        }
-        return 0;
+        c->mma_fallbacks += (int64_t)flagged.size();
+        return exact_some(flagged.data(), (int)flagged.size());
     }
 }
 
@@ -1349,7 +1345,9 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
 
     // Launch the exact scan for staged queries [qf, qf+g) (same path, g in {1,2,4,8} or any g: it is
     // reduced to what fits) writing output slots [of, ...).  Returns the group size actually launched.
-    auto launch_exact = [&](int qf, int of, int g, bool norm, int* launched) -> int {
+    // sel != nullptr: the g queries are sel[0..g) (any staged queries of this launch's range) and their answers go to
+    // their own slots, of + (sel[j] - qf); such launches do not push records to peers (the caller does, afterwards).
+    auto launch_exact = [&](int qf, int of, int g, bool norm, int* launched, const int* sel = nullptr) -> int {
         // pick the kernel flavour and the stage count that fits shared memory
         bool use_tma = s->tmap_ok;
         int n_stages = 0;
@@ -1380,6 +1378,8 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
         p.n_stages = n_stages;
         p.q_first = qf;
         p.out_first = of;
+        p.use_qsel = sel ? 1 : 0;
+        for (int j = 0; j < kMaxNQ; j++) p.qsel[j] = sel ? sel[j < g ? j : g - 1] : 0;
         p.xchg.raise = (of + g == count) ? 1 : 0;   // the launch that finishes the find raises the peers' words
         int rc;
         if (fused) rc = norm ? launch_scan_nq<false, false>(c, g, p, use_tma, grid, smem)
@@ -1429,8 +1429,19 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
         while (i + run < count && path_of(first + i + run) == norm) run++;
         if (mma_ok && run >= tuning().mma_min_queries) {
             const int g = std::min(run, kMmaMaxNQ);
-            int rc = mma_group_launch(c, p, first + i, i, g, norm, grid,
-                                      [&](int qf, int of) { return launch_exact(qf, of, 1, norm, nullptr); });
+            // what neither filter settles is re-run on the exact kernel, up to 8 queries per pass over the keys
+            auto exact_some = [&](const int* sel, int n_sel) -> int {
+                int done = 0;
+                while (done < n_sel) {
+                    const int left = n_sel - done;
+                    int gg = left >= 8 ? 8 : (left >= 4 ? 4 : (left >= 2 ? 2 : 1)), launched = 0;
+                    int rc2 = launch_exact(first + i, i, gg, norm, &launched, sel + done);
+                    if (rc2) return rc2;
+                    done += launched;
+                }
+                return 0;
+            };
+            int rc = mma_group_launch(c, p, first + i, i, g, norm, grid, exact_some);
             if (rc) return rc;
             i += g;
             continue;
