@@ -5,10 +5,20 @@ package main
 // Same type name, same embedded mixin idea, same methods and error texts as the
 // reference Store; every loop over keys happens behind cgo in libtfpstore.so
 // (include/tfp_store.h).  Values stay in Go: the library hands out int64 ids and
-// this file keeps id -> []byte.
+// this file keeps id -> []byte.  The reference's main.go is kept as it is
+// (backend/go/stores/main.go:18-26: flag --addr, grpc.StartServer(addr, NewStore())).
 //
-// NOT COMPILED in the build image (no Go toolchain, no generated pb.go): the
-// Python host localai_tfp_b200/store.py is the tested mirror of this file.
+// What this host adds over the reference, all through the unchanged gRPC surface:
+//   - the store spans every GPU named in TFP_DEVICES ("0,1,2,3" or "all"): the loader hands a
+//     backend only --addr and its environment (pkg/model/process.go:112-113);
+//   - concurrent StoresFind calls are drained by one goroutine and served by ONE
+//     tfp_store_find_batch (3 or more queries ride the tensor cores);
+//   - Load(opts) restores a snapshot from opts.ModelFile (the loader already passes it,
+//     pkg/model/initializers.go:397-404) and SIGTERM saves one there;
+//   - Status lists HBM bytes per GPU in the memory breakdown (pkg/grpc/base/base.go:77-81).
+//
+// NOT COMPILED in the build image (no Go toolchain, no generated pb.go): the Python host
+// localai_tfp_b200/store.py + server.py is the tested mirror of this file, call for call.
 
 /*
 #cgo CFLAGS: -I${SRCDIR}/../../include
@@ -19,37 +29,127 @@ package main
 import "C"
 
 import (
+	"bufio"
+	"crypto/rand"
+	"encoding/binary"
+	"errors"
 	"fmt"
+	"io"
+	"os"
+	"os/signal"
+	"path/filepath"
+	"runtime"
+	"strconv"
+	"strings"
 	"sync"
+	"syscall"
 	"unsafe"
 
 	"github.com/mudler/LocalAI/pkg/grpc/base"
 	pb "github.com/mudler/LocalAI/pkg/grpc/proto"
 )
 
+type findReq struct {
+	key  []float32
+	topk int
+	done chan findRes
+}
+type findRes struct {
+	res pb.StoresFindResult
+	err error
+}
+
 type Store struct {
 	// base.Base (Locking() == false) instead of the reference's base.SingleThread:
 	// the library serialises mutations itself and lets finds overlap.
 	base.Base
 
-	mu     sync.RWMutex
-	h      *C.tfp_store
-	values map[int64][]byte
+	mu       sync.RWMutex // guards values (and keeps a find's id -> value lookups consistent with mutations)
+	h        *C.tfp_store
+	values   map[int64][]byte
+	finds    chan findReq
+	snapshot string // opts.ModelFile of Load, "" = no persistence
+}
+
+// devices reads TFP_DEVICES: "" -> GPU 0, "all" -> every visible GPU, "0,2,3" -> those.
+func devices() []C.int {
+	spec := strings.TrimSpace(os.Getenv("TFP_DEVICES"))
+	if spec == "" {
+		return []C.int{0}
+	}
+	if strings.EqualFold(spec, "all") {
+		n := 0
+		for ; n < 8; n++ { // /proc/driver/nvidia/gpus has one entry per GPU; CUDA_VISIBLE_DEVICES narrows it
+			if _, err := os.Stat(fmt.Sprintf("/dev/nvidia%d", n)); err != nil {
+				break
+			}
+		}
+		if v := os.Getenv("CUDA_VISIBLE_DEVICES"); v != "" {
+			n = len(strings.Split(v, ","))
+		}
+		if n < 1 {
+			n = 1
+		}
+		out := make([]C.int, n)
+		for i := range out {
+			out[i] = C.int(i)
+		}
+		return out
+	}
+	var out []C.int
+	for _, f := range strings.Split(spec, ",") {
+		if v, err := strconv.Atoi(strings.TrimSpace(f)); err == nil {
+			out = append(out, C.int(v))
+		}
+	}
+	if len(out) == 0 {
+		out = []C.int{0}
+	}
+	return out
 }
 
 func NewStore() *Store {
-	s := &Store{values: map[int64][]byte{}}
-	cfg := C.tfp_cfg{device: 0}
-	if rc := C.tfp_store_open(&cfg, &s.h); rc != 0 {
-		panic("tfp_store_open: " + C.GoString(C.tfp_last_error()))
+	s := &Store{values: map[int64][]byte{}, finds: make(chan findReq, 1024)}
+	devs := devices()
+	cfg := C.tfp_cfg{device: devs[0]}
+	// tfp_last_error is thread-local: keep the goroutine on its OS thread between a failing call and the read
+	runtime.LockOSThread()
+	rc := C.tfp_store_open_devices(&cfg, &devs[0], C.int(len(devs)), &s.h)
+	msg := C.GoString(C.tfp_last_error())
+	runtime.UnlockOSThread()
+	if rc != 0 {
+		panic("tfp_store_open_devices: " + msg)
 	}
+	go s.batcher()
+	// the watchdog stops backends with SIGTERM (pkg/model/process.go): save before leaving
+	sig := make(chan os.Signal, 1)
+	signal.Notify(sig, syscall.SIGTERM)
+	go func() {
+		<-sig
+		s.mu.Lock()
+		if s.snapshot != "" {
+			_ = s.save(s.snapshot)
+		}
+		C.tfp_store_close(s.h)
+		os.Exit(0)
+	}()
 	return s
 }
 
-func lastErr() error { return fmt.Errorf("%s", C.GoString(C.tfp_last_error())) }
+// call runs one C entry point and, on failure, returns its message.  The error text is thread-local
+// in the library and goroutines move between OS threads from one cgo call to the next, so the pair
+// (call, tfp_last_error) runs with the goroutine pinned to its thread.
+func call(f func() C.int) error {
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	if rc := f(); rc != 0 {
+		return errors.New(C.GoString(C.tfp_last_error()))
+	}
+	return nil
+}
 
-// pack copies the request's keys into one C block (cgo forbids lending Go
-// pointers to Go pointers; the library copies again into pinned staging).
+// pack copies the request's keys into one page-locked C block (cgo forbids lending Go pointers to Go
+// pointers; from pinned memory the library's copy to the GPU runs at the PCIe rate).
 func pack(keys []*pb.StoresKey) (*C.float, int, func(), error) {
 	if len(keys) == 0 {
 		return nil, 0, func() {}, nil
@@ -61,15 +161,37 @@ func pack(keys []*pb.StoresKey) (*C.float, int, func(), error) {
 		}
 	}
 	n := len(keys)
-	buf := (*C.float)(C.malloc(C.size_t(n*dim*4 + 4)))
+	p := C.tfp_host_alloc(C.size_t(n*dim*4 + 4))
+	if p == nil {
+		return nil, 0, func() {}, errors.New(C.GoString(C.tfp_last_error()))
+	}
+	buf := (*C.float)(p)
 	dst := unsafe.Slice((*float32)(unsafe.Pointer(buf)), n*dim)
 	for i, k := range keys {
 		copy(dst[i*dim:(i+1)*dim], k.Floats)
 	}
-	return buf, dim, func() { C.free(unsafe.Pointer(buf)) }, nil
+	return buf, dim, func() { C.tfp_host_free(p) }, nil
 }
 
-func (s *Store) Load(opts *pb.ModelOptions) error { return nil }
+// Load: the reference's is a no-op (store.go:101-103).  Here opts.ModelFile, when it names an existing
+// snapshot, is restored; the path is remembered for the save on SIGTERM.  A snapshot that cannot be restored
+// is logged and ignored: the backend must come up (the loader retries a backend that fails LoadModel).
+func (s *Store) Load(opts *pb.ModelOptions) error {
+	if opts == nil || opts.ModelFile == "" {
+		return nil
+	}
+	s.mu.Lock()
+	defer s.mu.Unlock()
+	s.snapshot = opts.ModelFile
+	if _, err := os.Stat(s.snapshot); err != nil {
+		return nil
+	}
+	if err := s.restore(s.snapshot); err != nil {
+		fmt.Fprintf(os.Stderr, "local-store: snapshot %s not restored (%v); starting empty\n", s.snapshot, err)
+		s.values = map[int64][]byte{}
+	}
+	return nil
+}
 
 func (s *Store) StoresSet(opts *pb.StoresSetOptions) error {
 	buf, dim, free, err := pack(opts.Keys)
@@ -81,10 +203,11 @@ func (s *Store) StoresSet(opts *pb.StoresSetOptions) error {
 	ids := make([]int64, n+1)
 	s.mu.Lock()
 	defer s.mu.Unlock()
-	rc := C.tfp_store_set(s.h, buf, C.int64_t(n), C.int(dim), C.int64_t(len(opts.Values)),
-		(*C.int64_t)(unsafe.Pointer(&ids[0])), nil)
-	if rc != 0 {
-		return lastErr()
+	if err := call(func() C.int {
+		return C.tfp_store_set(s.h, buf, C.int64_t(n), C.int(dim), C.int64_t(len(opts.Values)),
+			(*C.int64_t)(unsafe.Pointer(&ids[0])), nil)
+	}); err != nil {
+		return err
 	}
 	for i := 0; i < n; i++ {
 		s.values[ids[i]] = opts.Values[i].Bytes
@@ -102,8 +225,10 @@ func (s *Store) StoresDelete(opts *pb.StoresDeleteOptions) error {
 	ids := make([]int64, n+1)
 	s.mu.Lock()
 	defer s.mu.Unlock()
-	if rc := C.tfp_store_delete(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0]))); rc != 0 {
-		return lastErr()
+	if err := call(func() C.int {
+		return C.tfp_store_delete(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0])))
+	}); err != nil {
+		return err
 	}
 	for i := 0; i < n; i++ {
 		if ids[i] >= 0 {
@@ -125,10 +250,11 @@ func (s *Store) StoresGet(opts *pb.StoresGetOptions) (pb.StoresGetResult, error)
 	var found C.int64_t
 	s.mu.RLock()
 	defer s.mu.RUnlock()
-	rc := C.tfp_store_get(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0])),
-		(*C.int64_t)(unsafe.Pointer(&order[0])), &found)
-	if rc != 0 {
-		return pb.StoresGetResult{}, lastErr()
+	if err := call(func() C.int {
+		return C.tfp_store_get(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0])),
+			(*C.int64_t)(unsafe.Pointer(&order[0])), &found)
+	}); err != nil {
+		return pb.StoresGetResult{}, err
 	}
 	res := pb.StoresGetResult{}
 	for j := 0; j < int(found); j++ {
@@ -139,42 +265,199 @@ func (s *Store) StoresGet(opts *pb.StoresGetOptions) (pb.StoresGetResult, error)
 	return res, nil
 }
 
+// StoresFind hands the request to the batcher and waits for its answer.
 func (s *Store) StoresFind(opts *pb.StoresFindOptions) (pb.StoresFindResult, error) {
-	q := opts.Key.Floats
-	dim := len(q)
-	topk := int(opts.TopK)
+	var key []float32
+	if opts.Key != nil {
+		key = opts.Key.Floats
+	}
+	req := findReq{key: key, topk: int(opts.TopK), done: make(chan findRes, 1)}
+	s.finds <- req
+	r := <-req.done
+	return r.res, r.err
+}
+
+// batcher: whatever has queued up while the previous batch ran is served together, grouped by (top-k, key
+// length).  A lone request is served at once: nothing waits for company.  (server.py _FindBatcher.)
+func (s *Store) batcher() {
+	for first := range s.finds {
+		group := []findReq{first}
+	drain:
+		for len(group) < 256 {
+			select {
+			case r := <-s.finds:
+				group = append(group, r)
+			default:
+				break drain
+			}
+		}
+		type gk struct{ topk, dim int }
+		by := map[gk][]findReq{}
+		for _, r := range group {
+			k := gk{r.topk, len(r.key)}
+			by[k] = append(by[k], r)
+		}
+		for k, reqs := range by {
+			s.findBatch(k.topk, k.dim, reqs)
+		}
+	}
+}
+
+func (s *Store) findBatch(topk, dim int, reqs []findReq) {
+	nq := len(reqs)
 	s.mu.RLock()
 	defer s.mu.RUnlock()
 	var st C.tfp_stats
 	C.tfp_store_stats(s.h, &st)
 	slots := topk
 	if int64(slots) > int64(st.rows) {
-		slots = int(st.rows) // the result holds min(TopK, rows) entries
+		slots = int(st.rows) // a result holds min(TopK, rows) entries (store.go:386-388)
 	}
 	if slots < 1 {
 		slots = 1
 	}
-	call := topk
+	callK := topk
 	if topk >= 1 {
-		call = slots
+		callK = slots
 	}
-	ids := make([]int64, slots)
-	sims := make([]float32, slots)
-	keys := make([]float32, slots*dim+1)
-	var n C.int
-	var qp *C.float
-	if dim > 0 {
-		qp = (*C.float)(unsafe.Pointer(&q[0]))
+	q := make([]float32, nq*dim+1)
+	for i, r := range reqs {
+		copy(q[i*dim:(i+1)*dim], r.key)
 	}
-	rc := C.tfp_store_find(s.h, qp, C.int(dim), C.int(call), &n, (*C.int64_t)(unsafe.Pointer(&ids[0])),
-		(*C.float)(unsafe.Pointer(&sims[0])), (*C.float)(unsafe.Pointer(&keys[0])), nil)
-	if rc != 0 {
-		return pb.StoresFindResult{}, lastErr()
+	ns := make([]C.int, nq)
+	ids := make([]int64, nq*slots)
+	sims := make([]float32, nq*slots)
+	keys := make([]float32, nq*slots*dim+1)
+	err := call(func() C.int {
+		return C.tfp_store_find_batch(s.h, (*C.float)(unsafe.Pointer(&q[0])), C.int(nq), C.int(dim), C.int(callK), &ns[0],
+			(*C.int64_t)(unsafe.Pointer(&ids[0])), (*C.float)(unsafe.Pointer(&sims[0])), (*C.float)(unsafe.Pointer(&keys[0])))
+	})
+	for i, r := range reqs {
+		if err != nil {
+			r.done <- findRes{err: err} // same text for every request of the group: they share top-k and key length
+			continue
+		}
+		n := int(ns[i])
+		res := pb.StoresFindResult{Similarities: sims[i*slots : i*slots+n]}
+		for j := 0; j < n; j++ {
+			at := i*slots + j
+			res.Keys = append(res.Keys, &pb.StoresKey{Floats: keys[at*dim : (at+1)*dim]})
+			res.Values = append(res.Values, &pb.StoresValue{Bytes: s.values[ids[at]]})
+		}
+		r.done <- findRes{res: res}
 	}
-	res := pb.StoresFindResult{Similarities: sims[:int(n)]}
-	for i := 0; i < int(n); i++ {
-		res.Keys = append(res.Keys, &pb.StoresKey{Floats: keys[i*dim : (i+1)*dim]})
-		res.Values = append(res.Values, &pb.StoresValue{Bytes: s.values[ids[i]]})
+}
+
+// Status: the base mixin's process figures plus HBM bytes per GPU.
+func (s *Store) Status() (pb.StatusResponse, error) {
+	resp, err := s.Base.Status()
+	if err != nil || resp.Memory == nil {
+		return resp, err
 	}
-	return res, nil
+	n := int(C.tfp_store_shard_count(s.h))
+	var rows uint64
+	for g := 0; g < n; g++ {
+		var st C.tfp_stats
+		if C.tfp_store_shard_stats(s.h, C.int(g), &st) == 0 {
+			resp.Memory.Breakdown[fmt.Sprintf("hbm-bytes-gpu%d", int(st.device))] += uint64(st.hbm_bytes)
+			rows += uint64(st.rows)
+		}
+	}
+	resp.Memory.Breakdown["rows"] = rows
+	resp.State = pb.StatusResponse_READY
+	return resp, nil
+}
+
+// ---- snapshot: keys / ids / flags by the library, id -> value by this host --------------------------------
+// Values file `<path>.values.<tag as 16 hex digits>`, little endian:
+//     "TFPVALS1" | u64 tag | u64 count | count x (i64 id | u32 len | bytes)
+// Order of a save: values under a NEW tag, then the library's keys file carrying that tag (its rename is the commit
+// point), then older values files are removed.  A kill at any moment leaves a pair that belongs together.
+// Caller holds s.mu.
+func (s *Store) save(path string) error {
+	var tb [8]byte
+	if _, err := rand.Read(tb[:]); err != nil {
+		return err
+	}
+	tag := binary.LittleEndian.Uint64(tb[:]) | 1
+	vpath := fmt.Sprintf("%s.values.%016x", path, tag)
+	f, err := os.Create(vpath + ".tmp")
+	if err != nil {
+		return err
+	}
+	w := bufio.NewWriter(f)
+	w.WriteString("TFPVALS1")
+	binary.Write(w, binary.LittleEndian, tag)
+	binary.Write(w, binary.LittleEndian, uint64(len(s.values)))
+	for id, v := range s.values {
+		binary.Write(w, binary.LittleEndian, id)
+		binary.Write(w, binary.LittleEndian, uint32(len(v)))
+		w.Write(v)
+	}
+	if err := w.Flush(); err != nil {
+		f.Close()
+		return err
+	}
+	if err := f.Sync(); err != nil {
+		f.Close()
+		return err
+	}
+	f.Close()
+	if err := os.Rename(vpath+".tmp", vpath); err != nil {
+		return err
+	}
+	cpath := C.CString(path)
+	defer C.free(unsafe.Pointer(cpath))
+	if err := call(func() C.int { return C.tfp_store_save_tagged(s.h, cpath, C.uint64_t(tag)) }); err != nil {
+		return err
+	}
+	old, _ := filepath.Glob(path + ".values.*")
+	for _, o := range old {
+		if o != vpath {
+			os.Remove(o)
+		}
+	}
+	return nil
+}
+
+// Caller holds s.mu; the store must be empty.
+func (s *Store) restore(path string) error {
+	cpath := C.CString(path)
+	defer C.free(unsafe.Pointer(cpath))
+	var tag C.uint64_t
+	if err := call(func() C.int { return C.tfp_snapshot_tag(cpath, &tag) }); err != nil {
+		return err
+	}
+	f, err := os.Open(fmt.Sprintf("%s.values.%016x", path, uint64(tag)))
+	if err != nil {
+		return err
+	}
+	defer f.Close()
+	r := bufio.NewReader(f)
+	head := make([]byte, 24)
+	if _, err := io.ReadFull(r, head); err != nil || string(head[:8]) != "TFPVALS1" {
+		return errors.New("not a values file")
+	}
+	if binary.LittleEndian.Uint64(head[8:16]) != uint64(tag) {
+		return errors.New("the values file does not belong to this snapshot")
+	}
+	count := binary.LittleEndian.Uint64(head[16:24])
+	values := make(map[int64][]byte, count)
+	rec := make([]byte, 12)
+	for i := uint64(0); i < count; i++ {
+		if _, err := io.ReadFull(r, rec); err != nil {
+			return errors.New("values file truncated")
+		}
+		id := int64(binary.LittleEndian.Uint64(rec[:8]))
+		v := make([]byte, binary.LittleEndian.Uint32(rec[8:12]))
+		if _, err := io.ReadFull(r, v); err != nil {
+			return errors.New("values file truncated")
+		}
+		values[id] = v
+	}
+	if err := call(func() C.int { return C.tfp_store_load(s.h, cpath) }); err != nil {
+		return err
+	}
+	s.values = values
+	return nil
 }

@@ -247,11 +247,16 @@ static int multi_open(const tfp_cfg* cfg, const int* devices, int n_devices, tfp
 // store.go:115-116 / :209-210 / :275-276: the first Set, Delete or Get fixes the key length -- of every shard, so
 // that a shard which owns no key yet answers finds with an empty list instead of a length error.
 static int multi_latch(tfp_store* top, int dim, const char* fmt) {
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    {   // the usual case -- the length is fixed and matches -- needs no exclusive lock (finds hold this lock shared
+        // for their whole duration: an exclusive request per StoresSet would queue behind all of them)
+        std::shared_lock<RwMutex> lk(top->rw);
+        if (top->dim == dim) return 0;
+    }
+    std::unique_lock<RwMutex> lk(top->rw);
     if (top->dim == -1) {
         top->dim = dim;
         for (tfp_store* sh : top->multi->shards) {
-            std::unique_lock<std::shared_mutex> lk(sh->rw);
+            std::unique_lock<RwMutex> lk(sh->rw);
             if (sh->dim == -1) sh->dim = dim;
         }
     } else if (dim != top->dim) {
@@ -313,9 +318,9 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
         }
     // the sticky flag (store.go:27,126-127) belongs to the whole store: all shards leave the normalised path together
     bool all_norm = true;
-    for (tfp_store* sh : m->shards) { std::shared_lock<std::shared_mutex> l2(sh->rw); all_norm = all_norm && sh->normalized; }
+    for (tfp_store* sh : m->shards) { std::shared_lock<RwMutex> l2(sh->rw); all_norm = all_norm && sh->normalized; }
     if (!all_norm) {
-        std::unique_lock<std::shared_mutex> lk(top->rw);
+        std::unique_lock<RwMutex> lk(top->rw);
         top->normalized = false;
         for (tfp_store* sh : m->shards) store_mark_not_normalized(sh);
     }
@@ -383,7 +388,7 @@ static int multi_get(tfp_store* top, const float* keys, int64_t n, int dim, int6
 
 static int multi_stats(tfp_store* top, tfp_stats* out) {
     tfp_multi* m = top->multi;
-    std::shared_lock<std::shared_mutex> lk(top->rw);
+    std::shared_lock<RwMutex> lk(top->rw);
     memset(out, 0, sizeof(*out));
     for (tfp_store* sh : m->shards) {
         tfp_stats st;
@@ -398,7 +403,7 @@ static int multi_stats(tfp_store* top, tfp_stats* out) {
 }
 
 static int multi_mark_not_normalized(tfp_store* top) {
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::unique_lock<RwMutex> lk(top->rw);
     top->normalized = false;
     for (tfp_store* sh : top->multi->shards) store_mark_not_normalized(sh);
     return 0;
@@ -427,7 +432,7 @@ static int multi_find_device(tfp_multi* m, MultiLane& L, const float* q, int nq,
     int rc = run_shards(m, all_shards(m), [&](int g) -> int {
         tfp_store* sh = m->shards[(size_t)g];
         tfp_find_ctx* c = L.ctx[(size_t)g];
-        std::shared_lock<std::shared_mutex> lk(sh->rw);
+        std::shared_lock<RwMutex> lk(sh->rw);
         if (set_device(sh)) return -1;
         int r = ctx_upload_locked(c, q, nq, dim, qi);
         if (r) return r;
@@ -448,7 +453,7 @@ static int multi_find_device(tfp_multi* m, MultiLane& L, const float* q, int nq,
     // every shard's scan is in its stream: now the merge kernel, which waits for their records, can go in
     if (set_device(m->shards[0])) return -1;
     {
-        std::shared_lock<std::shared_mutex> lk(m->shards[0]->rw);
+        std::shared_lock<RwMutex> lk(m->shards[0]->rw);
         rc = p2p_merge_locked(root);
         if (rc) return rc;
     }
@@ -467,7 +472,7 @@ static int multi_find_general(tfp_multi* m, MultiLane& L, const float* q, int nq
     int rc = run_shards(m, all_shards(m), [&](int g) -> int {
         tfp_store* sh = m->shards[(size_t)g];
         tfp_find_ctx* c = L.ctx[(size_t)g];
-        std::shared_lock<std::shared_mutex> lk(sh->rw);
+        std::shared_lock<RwMutex> lk(sh->rw);
         if (set_device(sh)) return -1;
         Part& P = parts[(size_t)g];
         P.k = (int)std::min<int64_t>((int64_t)topk, std::max<int64_t>(sh->n, 1));   // a shard cannot return more than it holds
@@ -514,7 +519,7 @@ static int multi_find_general(tfp_multi* m, MultiLane& L, const float* q, int nq
 static int multi_find_batch(tfp_store* top, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
                             float* out_sims, float* out_keys, int* out_path) {
     tfp_multi* m = top->multi;
-    std::shared_lock<std::shared_mutex> lk(top->rw);
+    std::shared_lock<RwMutex> lk(top->rw);
     if (dim != top->dim)                                                             // store.go:480-482 (fires on -1 too)
         return fail(1, "Try to find key with length %d when existing length is %d", dim, top->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
@@ -568,7 +573,7 @@ static int multi_save(tfp_store* top, const char* path, uint64_t tag) {
 static int multi_load(tfp_store* top, const char* path) {
     tfp_multi* m = top->multi;
     std::lock_guard<std::mutex> mut(top->mut_mu);
-    std::unique_lock<std::shared_mutex> lk(top->rw);
+    std::unique_lock<RwMutex> lk(top->rw);
     if (top->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
     FILE* f = fopen(path, "rb");
     if (!f) return fail(2, "tfp_store_load: cannot open %s", path);
@@ -592,7 +597,7 @@ static int multi_load(tfp_store* top, const char* path) {
     top->dim = mf.dim;
     top->normalized = mf.normalized != 0;
     for (tfp_store* sh : m->shards) {
-        std::unique_lock<std::shared_mutex> l2(sh->rw);
+        std::unique_lock<RwMutex> l2(sh->rw);
         if (sh->dim == -1) sh->dim = mf.dim;
         if (!top->normalized) sh->normalized = false;
     }

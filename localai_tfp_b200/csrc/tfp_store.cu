@@ -19,6 +19,7 @@
 #include <fcntl.h>
 #include <unistd.h>
 #include <mutex>
+#include <pthread.h>
 #include <shared_mutex>
 #include <string>
 #include <unordered_set>
@@ -55,6 +56,33 @@ static int fail(int code, const char* fmt, ...) {
 
 extern "C" const char* tfp_last_error(void) { return g_err.c_str(); }
 extern "C" const char* tfp_version(void) { return "libtfpstore 0.1 (sm_100a; TMA scan, fused top-k)"; }
+
+// ---------------------------------------------------------------------------
+// Reader-writer lock that lets a waiting writer in ahead of new readers.  Finds take the store's lock shared, one
+// after the other and from many threads at once; std::shared_mutex (glibc's default rwlock) prefers readers, and a
+// StoresSet that only needs the lock for an instant to publish its rows would wait for as long as finds keep coming.
+// Non-recursive: a thread never takes the same lock shared twice.
+// ---------------------------------------------------------------------------
+class RwMutex {
+    pthread_rwlock_t l_;
+public:
+    RwMutex() {
+        pthread_rwlockattr_t a;
+        pthread_rwlockattr_init(&a);
+        pthread_rwlockattr_setkind_np(&a, PTHREAD_RWLOCK_PREFER_WRITER_NONRECURSIVE_NP);
+        pthread_rwlock_init(&l_, &a);
+        pthread_rwlockattr_destroy(&a);
+    }
+    ~RwMutex() { pthread_rwlock_destroy(&l_); }
+    RwMutex(const RwMutex&) = delete;
+    RwMutex& operator=(const RwMutex&) = delete;
+    void lock() { pthread_rwlock_wrlock(&l_); }
+    bool try_lock() { return pthread_rwlock_trywrlock(&l_) == 0; }
+    void unlock() { pthread_rwlock_unlock(&l_); }
+    void lock_shared() { pthread_rwlock_rdlock(&l_); }
+    bool try_lock_shared() { return pthread_rwlock_tryrdlock(&l_) == 0; }
+    void unlock_shared() { pthread_rwlock_unlock(&l_); }
+};
 
 // ---------------------------------------------------------------------------
 // small RAII-less buffers (explicit release; the store owns them)
@@ -272,7 +300,7 @@ struct tfp_store {
     std::string last_err;         // text of the last failing call on this handle, from any thread (tfp_store_last_error)
     int device = 0;
     std::mutex mut_mu;         // one mutation (set / delete / get / save / load) at a time: owns the staging buffers, the host index and its mirrors
-    std::shared_mutex rw;      // finds: shared while enqueueing.  Mutations take it exclusively only to PUBLISH (row count, flags,
+    RwMutex rw;      // finds: shared while enqueueing.  Mutations take it exclusively only to PUBLISH (row count, flags,
                                // capacity, tensor maps) and, for overwrites and compaction, to fence the finds; taken after mut_mu
     int dim = -1;              // store.go:29,44 keyLen
     bool normalized = true;    // store.go:27,43 keysAreNormalized (sticky)
@@ -518,7 +546,7 @@ static void store_close(tfp_store* s) {
 
 static int store_stats(tfp_store* s, tfp_stats* out) {
     if (!s || !out) return fail(2, "tfp_store_stats: NULL argument");
-    std::shared_lock<std::shared_mutex> lk(s->rw);
+    std::shared_lock<RwMutex> lk(s->rw);
     out->rows = s->n;
     out->capacity_rows = s->cap;
     out->hbm_bytes = s->vm_keys.active() ? (int64_t)(s->vm_keys.mapped + s->vm_ids.mapped + s->vm_knorm.mapped)
@@ -532,7 +560,7 @@ static int store_stats(tfp_store* s, tfp_stats* out) {
 
 static int store_mark_not_normalized(tfp_store* s) {
     if (!s) return fail(2, "tfp_store_mark_not_normalized: store is NULL");
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    std::unique_lock<RwMutex> lk(s->rw);
     s->normalized = false;
     return 0;
 }
@@ -660,14 +688,14 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
     }
     const bool overwrites = n_new != n;
     const bool must_move = s->n + n_new > s->cap && !(vmm_api() && (s->vm_keys.active() || s->cap == 0));
-    std::unique_lock<std::shared_mutex> fence(s->rw, std::defer_lock);
+    std::unique_lock<RwMutex> fence(s->rw, std::defer_lock);
     if (overwrites || must_move) {
         fence.lock();
         if (quiesce_finds(s)) return -1;
     }
     if (s->n + n_new > s->cap) {
         // growing changes what finds read when they launch (capacity, tensor maps, the first time the base addresses)
-        std::unique_lock<std::shared_mutex> grow(s->rw, std::defer_lock);
+        std::unique_lock<RwMutex> grow(s->rw, std::defer_lock);
         if (!fence.owns_lock()) grow.lock();
         if (ensure_capacity(s, s->n + n_new)) return -1;
     }
@@ -694,7 +722,7 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
     }
     CU_OK(cudaStreamSynchronize(s->s_mut));   // the rows are in HBM ...
     {                                         // ... now finds may see them
-        std::unique_lock<std::shared_mutex> pub(s->rw, std::defer_lock);
+        std::unique_lock<RwMutex> pub(s->rw, std::defer_lock);
         if (!fence.owns_lock()) pub.lock();
         s->n += n_new;
         s->next_id += n_new;
@@ -705,7 +733,11 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
 
 // store.go:115-116 / :209-210 / :275-276: the first Set, Delete or Get fixes the key length.
 static int latch_dim(tfp_store* s, int dim, const char* fmt) {
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    {   // the usual case -- the length is fixed and matches -- needs no exclusive lock
+        std::shared_lock<RwMutex> lk(s->rw);
+        if (s->dim == dim) return 0;
+    }
+    std::unique_lock<RwMutex> lk(s->rw);
     if (s->dim == -1) s->dim = dim;
     else if (dim != s->dim) return fail(1, fmt, dim, s->dim);
     return 0;
@@ -809,7 +841,7 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
     }
     if (holes.empty()) return 0;
     // compaction moves rows that running scans read, and shrinks the row count: fence the finds (the look-up above did not)
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    std::unique_lock<RwMutex> lk(s->rw);
     if (quiesce_finds(s)) return -1;
     const int64_t new_n = s->n - (int64_t)holes.size();
     std::vector<uint8_t> dead((size_t)(s->n - new_n), 0);   // marks deleted slots in the tail [new_n, n)
@@ -884,7 +916,7 @@ static int write_file_atomically(const char* path, Body&& body) {
 static int store_save(tfp_store* s, const char* path, uint64_t tag) {
     if (!s || !path) return fail(2, "tfp_store_save: NULL argument");
     std::lock_guard<std::mutex> mut(s->mut_mu);
-    std::shared_lock<std::shared_mutex> lk(s->rw);   // finds only read: they may go on while the rows are copied out
+    std::shared_lock<RwMutex> lk(s->rw);   // finds only read: they may go on while the rows are copied out
     if (set_device(s)) return -1;
     SnapHeader h;
     memcpy(h.magic, "TFPSTOR2", 8);
@@ -913,7 +945,7 @@ static int store_save(tfp_store* s, const char* path, uint64_t tag) {
 static int store_load(tfp_store* s, const char* path) {
     if (!s || !path) return fail(2, "tfp_store_load: NULL argument");
     std::lock_guard<std::mutex> mut(s->mut_mu);
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    std::unique_lock<RwMutex> lk(s->rw);
     if (s->n != 0 || s->dim != -1) return fail(2, "tfp_store_load: the store is not empty");
     if (set_device(s)) return -1;
     FILE* f = fopen(path, "rb");
@@ -1013,14 +1045,14 @@ extern "C" int tfp_find_ctx_create(tfp_store* s, tfp_find_ctx** out) {
     if (s->multi)
         return fail(2, "tfp_find_ctx_create: a multi-GPU store runs its own find lanes; call tfp_store_find / "
                        "tfp_store_find_batch from several threads instead");
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    std::unique_lock<RwMutex> lk(s->rw);
     if (set_device(s)) return -1;
     return ctx_create(s, out);
 }
 extern "C" void tfp_find_ctx_destroy(tfp_find_ctx* c) {
     if (!c) return;
     tfp_store* s = c->st;
-    std::unique_lock<std::shared_mutex> lk(s->rw);
+    std::unique_lock<RwMutex> lk(s->rw);
     cudaSetDevice(s->device);
     if (c == s->default_ctx) return;   // owned by the store
     ctx_destroy(c);
@@ -1069,7 +1101,7 @@ static int ctx_upload_locked(tfp_find_ctx* c, const float* q, int nq, int dim, c
 
 extern "C" int tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int dim) {
     if (!c || !q || nq <= 0 || dim <= 0) return fail(2, "tfp_find_ctx_upload: bad argument");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     CU_OK(cudaStreamSynchronize(c->stream));   // the pinned staging buffer is reused
     return ctx_upload_locked(c, q, nq, dim);
@@ -1461,7 +1493,7 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
 
 extern "C" int tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int topk) {
     if (!c) return fail(2, "tfp_find_ctx_launch: ctx is NULL");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     return ctx_launch_locked(c, first, count, topk);
 }
@@ -1482,7 +1514,7 @@ static int ctx_gather_locked(tfp_find_ctx* c) {
 extern "C" int tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys) {
     if (!c || !d_keys) return fail(2, "tfp_find_ctx_gather_keys: NULL argument");
     if (c->last_count <= 0) return fail(2, "tfp_find_ctx_gather_keys: nothing was launched on this context");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     int rc = ctx_gather_locked(c);
     if (rc) return rc;
@@ -1517,7 +1549,7 @@ static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, fl
 
 extern "C" int tfp_find_ctx_download(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys) {
     if (!c) return fail(2, "tfp_find_ctx_download: ctx is NULL");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     return ctx_download_locked(c, out_n, out_ids, out_sims, out_keys);
 }
@@ -1576,7 +1608,7 @@ extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, i
 static int store_find_batch(tfp_store* s, const float* q, int nq, int dim, int topk, int* out_n, int64_t* out_ids,
                             float* out_sims, float* out_keys, int* out_path) {
     if (!s) return fail(2, "tfp_store_find: store is NULL");
-    std::shared_lock<std::shared_mutex> lk(s->rw);
+    std::shared_lock<RwMutex> lk(s->rw);
     if (dim != s->dim)                                                               // store.go:480-482 (fires on -1 too)
         return fail(1, "Try to find key with length %d when existing length is %d", dim, s->dim);
     if (topk < 1) return fail(1, "opts.TopK = %d, must be >= 1", topk);             // store.go:484-486
@@ -1864,7 +1896,7 @@ extern "C" int tfp_find_ctx_p2p_export(tfp_find_ctx* c, int world, size_t slot_b
     if (!c || !handle_out || handle_bytes < sizeof(cudaIpcMemHandle_t)) return fail(2, "tfp_find_ctx_p2p_export: bad argument");
     if (world < 2 || world > kXchgMaxWorld) return fail(2, "tfp_find_ctx_p2p_export: world = %d outside [2, %d]", world, kXchgMaxWorld);
     if (slot_bytes < 256 || slot_bytes > ((size_t)64 << 20)) return fail(2, "tfp_find_ctx_p2p_export: slot_bytes outside [256, 64 MiB]");
-    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    std::unique_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st) || wait32_api()) return -1;
     CU_OK(cudaStreamSynchronize(c->stream));
     p2p_detach(c);
@@ -1886,7 +1918,7 @@ extern "C" int tfp_find_ctx_p2p_attach(tfp_find_ctx* c, const void* handles, int
     if (!c || !handles) return fail(2, "tfp_find_ctx_p2p_attach: NULL argument");
     if (!c->xbuf.p || world != c->x_world || rank < 0 || rank >= world)
         return fail(2, "tfp_find_ctx_p2p_attach: call tfp_find_ctx_p2p_export with the same world first");
-    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    std::unique_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st) || wait32_api()) return -1;
     c->x_me = rank;
     for (int r = 0; r < world; r++) {
@@ -1913,7 +1945,7 @@ extern "C" int tfp_find_ctx_p2p_attach(tfp_find_ctx* c, const void* handles, int
 
 extern "C" int tfp_find_ctx_p2p_detach(tfp_find_ctx* c) {
     if (!c) return fail(2, "tfp_find_ctx_p2p_detach: ctx is NULL");
-    std::unique_lock<std::shared_mutex> lk(c->st->rw);
+    std::unique_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     CU_OK(cudaStreamSynchronize(c->stream));
     p2p_detach(c);
@@ -2057,7 +2089,7 @@ extern "C" int tfp_find_ctx_launch_sharded_batch(tfp_find_ctx* c, int first, int
     if (!c) return fail(2, "tfp_find_ctx_launch_sharded: ctx is NULL");
     if (!c->nccl_comm && !c->x_ready)
         return fail(2, "tfp_find_ctx_launch_sharded: call tfp_find_ctx_p2p_attach or tfp_find_ctx_comm_init first");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     const int world = c->x_ready ? c->x_world : c->comm_world;
     if (sharded_check(c, topk, world)) return 2;
@@ -2085,7 +2117,7 @@ extern "C" size_t tfp_p2p_slot_bytes_with_keys(int count, int topk, int dim) {
 extern "C" int tfp_find_ctx_launch_sharded_keys(tfp_find_ctx* c, int first, int count, int topk) {
     if (!c) return fail(2, "tfp_find_ctx_launch_sharded_keys: ctx is NULL");
     if (!c->x_ready) return fail(2, "tfp_find_ctx_launch_sharded_keys: call tfp_find_ctx_p2p_attach first");
-    std::shared_lock<std::shared_mutex> lk(c->st->rw);
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
     if (sharded_check(c, topk, c->x_world)) return 2;
     if (count < 1 || c->st->dim < 1 || tfp_p2p_slot_bytes_with_keys(count, std::max(topk, 1), c->st->dim) > c->x_slot)
