@@ -48,9 +48,9 @@ class _FindBatcher:
         self.batches = 0
         self.largest = 0
 
-    def submit(self, key, topk):
+    def submit(self, key, topk, no_keys=False):
         fut = futures.Future()
-        self.q.put((key, topk, fut))
+        self.q.put((key, (topk, bool(no_keys)), fut))
         return fut
 
     def _run(self):
@@ -67,27 +67,31 @@ class _FindBatcher:
             for topk, group in by_k.items():
                 self._serve(topk, group)
 
-    def _serve(self, topk, group):
+    def _serve(self, topk_nokeys, group):
         b = self.backend
+        topk, no_keys = topk_nokeys
         with b.lock:
             b.busy = True
             try:
                 dims = {len(g[0]) for g in group}
                 if len(group) == 1 or len(dims) != 1 or topk < 1 or b.store.key_len != next(iter(dims)) or len(b.store) == 0:
-                    for key, k, fut in group:        # singles and anything that will error: the plain call, per request
+                    for key, _, fut in group:        # singles and anything that will error: the plain call, per request
                         try:
-                            fut.set_result(b.store.StoresFind(key, k))
+                            fut.set_result(b.find_one(key, topk, no_keys))
                         except Exception as e:
                             fut.set_exception(e)
                     return
                 import numpy as np
                 qs = np.stack([g[0] for g in group]).astype(np.float32)
-                res, keys = b.store.find_batch(qs, topk, with_keys=True)
+                if no_keys:
+                    res, keys = b.store.find_batch(qs, topk), None
+                else:
+                    res, keys = b.store.find_batch(qs, topk, with_keys=True)
                 self.batches += 1
                 self.largest = max(self.largest, len(group))
                 for i, (key, k, fut) in enumerate(group):
                     ids, sims = res[i]
-                    fut.set_result(([keys[i, j, :].copy() for j in range(len(ids))],
+                    fut.set_result(([] if no_keys else [keys[i, j, :].copy() for j in range(len(ids))],
                                     [b.store.values.get(int(x)) for x in ids], sims))
             except Exception as e:
                 for _, _, fut in group:
@@ -176,13 +180,29 @@ class Backend:
         ks, vs = self._run(context, lambda: self.store.StoresGet(keys))
         return wire.enc_get_result(ks, vs)
 
+    def StoresSetPacked(self, request: bytes, context) -> bytes:
+        """Extension: the keys of one call as ONE block of n x Dim floats -- handed to the library as it
+        arrived, no per-key message, no gather copy.  Same semantics and reply as StoresSet."""
+        try:
+            keys, values = wire.dec_set_packed(request)
+        except ValueError as e:
+            context.abort(grpc.StatusCode.UNKNOWN, str(e))
+        self._run(context, lambda: self.store.StoresSet(keys, values))
+        return wire.enc_result("Set key", True)
+
+    def find_one(self, key, topk, no_keys):
+        if not no_keys:
+            return self.store.StoresFind(key, topk)
+        ids, sims = self.store.find_ids(key, topk)        # no key rows gathered, copied or encoded
+        return [], [self.store.values.get(int(x)) for x in ids], sims
+
     def StoresFind(self, request: bytes, context) -> bytes:
-        key, topk = wire.dec_find(request)
+        key, topk, no_keys = wire.dec_find_ext(request)
         if self.batcher is None:
-            ks, vs, sims = self._run(context, lambda: self.store.StoresFind(key, topk))
+            ks, vs, sims = self._run(context, lambda: self.find_one(key, topk, no_keys))
         else:
             try:
-                ks, vs, sims = self.batcher.submit(key, topk).result()
+                ks, vs, sims = self.batcher.submit(key, topk, no_keys).result()
             except StoreError as e:
                 context.abort(grpc.StatusCode.UNKNOWN, str(e))
         return wire.enc_find_result(ks, vs, sims)
@@ -223,7 +243,7 @@ def make_server(addr: str, device: int = 0, workers: int = 64, snapshot: str | N
     methods = {name: grpc.unary_unary_rpc_method_handler(getattr(backend, name), request_deserializer=_ident,
                                                          response_serializer=_ident)
                for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind",
-                            "StoresFindBatch")}
+                            "StoresFindBatch", "StoresSetPacked")}
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=workers),
                          options=[("grpc.max_receive_message_length", wire.MAX_MESSAGE),
                                   ("grpc.max_send_message_length", wire.MAX_MESSAGE)])
@@ -243,7 +263,7 @@ class Client:
         self._m = {name: self.ch.unary_unary(f"/{SERVICE}/{name}", request_serializer=_ident,
                                              response_deserializer=_ident)
                    for name in ("Health", "LoadModel", "Status", "StoresSet", "StoresDelete", "StoresGet", "StoresFind",
-                                "StoresFindBatch")}
+                                "StoresFindBatch", "StoresSetPacked")}
 
     def health(self) -> bytes:
         return wire.dec_reply(self._m["Health"](b"", timeout=10))
@@ -263,8 +283,11 @@ class Client:
     def get(self, keys):
         return wire.dec_get_result(self._m["StoresGet"](wire.enc_keys(keys)))
 
-    def find(self, key, topk: int):
-        return wire.dec_find_result(self._m["StoresFind"](wire.enc_find(key, topk)))
+    def set_packed(self, keys, values):
+        return wire.dec_result(self._m["StoresSetPacked"](wire.enc_set_packed(keys, values)))
+
+    def find(self, key, topk: int, no_keys: bool = False):
+        return wire.dec_find_result(self._m["StoresFind"](wire.enc_find(key, topk, no_keys)))
 
     def find_batch(self, keys, topk: int):
         return wire.dec_find_batch_result(self._m["StoresFindBatch"](wire.enc_find_batch(keys, topk)))

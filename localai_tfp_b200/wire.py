@@ -9,6 +9,14 @@ One extension the reference does not have ("batch Find on the wir
     message StoresFindBatchResult  { repeated StoresFindResult Results = 1; }
     rpc StoresFindBatch(StoresFindBatchOptions) returns (StoresFindBatchResult) {}
 Result i is what StoresFind(Keys[i], TopK) returns; one client can feed the tensor-core path directly.
+Two more (no key echo, no per-key sub-messages):
+    StoresFindOptions  { ...; bool NoKeys = 3; }      a decoder that predates the field skips it (proto3), so the
+        request stays valid for the reference backend; this backend then leaves StoresFindResult.Keys empty --
+        Values and Similarities identify the hits -- and the reply shrinks from k x (D x 4 + value) to k x (4 + value) bytes
+        (core/http/endpoints/localai/stores.go:108-125 echoes the keys only because the backend returns them).
+    message StoresSetPackedOptions { bytes Keys = 1; int32 Dim = 2; repeated StoresValue Values = 3; }
+    rpc StoresSetPacked(StoresSetPackedOptions) returns (Result) {}
+        Keys is n x Dim little-endian fp32 in one run: one memcpy instead of n sub-messages on both sides.
 `repeated float` is packed (one length-delimited run of little-endian fp32), which numpy reads and
 writes without a per-element loop; unpacked floats (legal on the wire) are accepted too.
 Unknown fields are skipped, as a protobuf decoder must.
@@ -133,15 +141,17 @@ def dec_keys(data: bytes) -> List[np.ndarray]:
     return [dec_key(v) for field, wt, v in _fields(memoryview(data)) if field == 1 and wt == 2]
 
 
-def enc_find(key, topk: int) -> bytes:
+def enc_find(key, topk: int, no_keys: bool = False) -> bytes:
     out = _ld(1, enc_key(key))
     if topk:
         out += _varint((2 << 3) | 0) + _varint(int(topk))
+    if no_keys:
+        out += _varint((3 << 3) | 0) + b"\x01"
     return out
 
 
-def dec_find(data: bytes) -> Tuple[np.ndarray, int]:
-    key, topk = np.zeros(0, np.float32), 0
+def dec_find_ext(data: bytes) -> Tuple[np.ndarray, int, bool]:
+    key, topk, no_keys = np.zeros(0, np.float32), 0, False
     for field, wt, v in _fields(memoryview(data)):
         if field == 1 and wt == 2:
             key = dec_key(v)
@@ -149,7 +159,38 @@ def dec_find(data: bytes) -> Tuple[np.ndarray, int]:
             topk = v & 0xFFFFFFFF
             if topk & 0x80000000:
                 topk -= 1 << 32      # int32
-    return key, topk
+        elif field == 3 and wt == 0:
+            no_keys = bool(v)
+    return key, topk, no_keys
+
+
+def dec_find(data: bytes) -> Tuple[np.ndarray, int]:
+    return dec_find_ext(data)[:2]
+
+
+def enc_set_packed(keys, values) -> bytes:
+    a = np.ascontiguousarray(keys, dtype="<f4")
+    if a.ndim != 2:
+        raise ValueError("packed keys are one [n, dim] block")
+    out = _ld(1, a.tobytes()) if a.size else b""
+    if a.shape[1]:
+        out += _varint((2 << 3) | 0) + _varint(int(a.shape[1]))
+    return out + b"".join(_ld(3, enc_value(v)) for v in values)
+
+
+def dec_set_packed(data: bytes):
+    """(keys [n, dim] fp32 -- a view of the message's bytes, no copy --, values)."""
+    raw, dim, values = memoryview(b""), 0, []
+    for field, wt, v in _fields(memoryview(data)):
+        if field == 1 and wt == 2:
+            raw = v
+        elif field == 2 and wt == 0:
+            dim = v & 0xFFFFFFFF
+        elif field == 3 and wt == 2:
+            values.append(dec_value(v))
+    if dim <= 0 or len(raw) % (4 * dim):
+        raise ValueError(f"packed keys: {len(raw)} bytes is not a whole number of {dim}-float keys")
+    return np.frombuffer(raw, dtype="<f4").reshape(-1, dim), values
 
 
 def enc_find_batch(keys, topk: int) -> bytes:

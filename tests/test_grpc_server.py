@@ -198,3 +198,21 @@ def test_find_batch_rpc_equals_single_finds(client):
         with pytest.raises(grpc.RpcError) as e:
             client.find_batch(keys, topk)
         assert e.value.code() == grpc.StatusCode.UNKNOWN and e.value.details() == text
+
+
+def test_find_without_key_echo_and_packed_set(client):
+    """SURVEY §8f.3 on the wire: StoresSetPacked stores what StoresSet would; StoresFind with NoKeys returns the same
+    values and similarities with no keys in the reply."""
+    rng = np.random.default_rng(3)
+    K = rng.standard_normal((200, 48)).astype(f32)
+    vals = [b"v%d" % i for i in range(len(K))]
+    assert client.set_packed(K, vals) == ("Set key", True)
+    assert client.set_packed(K[:5], [b"w%d" % i for i in range(5)]) == ("Set key", True)      # overwrite, like StoresSet
+    ks, vs = client.get([K[3], K[100]])
+    assert sorted(vs) == [b"v100", b"w3"]
+    full = client.find(K[7], 10)
+    lean = client.find(K[7], 10, no_keys=True)
+    assert lean[0] == [] and lean[1] == full[1] and np.array_equal(lean[2], full[2]) and len(full[0]) == 10
+    with pytest.raises(grpc.RpcError) as e:
+        client.set_packed(K[:2, :7], [b"a", b"b"])
+    assert e.value.details() == "Try to add key with length 7 when existing length is 48"

@@ -35,6 +35,11 @@ def build_messages():
     # the batch-find extension (not in the reference proto)
     msg("StoresFindBatchOptions", ("Keys", 1, F.TYPE_MESSAGE, R, "StoresKey"), ("TopK", 2, F.TYPE_INT32, O, None))
     msg("StoresFindBatchResult", ("Results", 1, F.TYPE_MESSAGE, R, "StoresFindResult"))
+    # the no-key-echo / packed-keys extensions (not in the reference proto)
+    msg("StoresFindOptionsExt", ("Key", 1, F.TYPE_MESSAGE, O, "StoresKey"), ("TopK", 2, F.TYPE_INT32, O, None),
+        ("NoKeys", 3, F.TYPE_BOOL, O, None))
+    msg("StoresSetPackedOptions", ("Keys", 1, F.TYPE_BYTES, O, None), ("Dim", 2, F.TYPE_INT32, O, None),
+        ("Values", 3, F.TYPE_MESSAGE, R, "StoresValue"))
     msg("Result", ("message", 1, F.TYPE_STRING, O, None), ("success", 2, F.TYPE_BOOL, O, None))   # :260-263
     msg("Reply", ("message", 1, F.TYPE_BYTES, O, None), ("tokens", 2, F.TYPE_INT32, O, None))     # :159-165
     pool = descriptor_pool.DescriptorPool()
@@ -130,3 +135,33 @@ def test_unpacked_floats_are_accepted():
 def test_status_roundtrip():
     data = wire.enc_status(2, 12345, {"hbm-bytes-gpu0": 12345, "rows": 7})
     assert wire.dec_status(data) == (2, 12345, {"hbm-bytes-gpu0": 12345, "rows": 7})
+
+
+@pytest.mark.parametrize("no_keys", [False, True])
+def test_find_options_no_keys_extension(no_keys):
+    """Field 3 (NoKeys) encodes like protobuf's bool, and the REFERENCE's message -- which has no such field -- parses
+    the same bytes to the same key and top-k: the extension does not break an old backend."""
+    ref = PB["StoresFindOptionsExt"](Key=pb_key(KEYS[1]), TopK=10, NoKeys=no_keys)
+    data = wire.enc_find(KEYS[1], 10, no_keys)
+    assert data == ref.SerializeToString()
+    k, t, nk = wire.dec_find_ext(data)
+    assert t == 10 and nk == no_keys and np.array_equal(k, KEYS[1])
+    old = PB["StoresFindOptions"]()
+    old.ParseFromString(data)
+    assert old.TopK == 10 and np.array_equal(np.array(old.Key.Floats, np.float32), KEYS[1])
+    k2, t2 = wire.dec_find(data)
+    assert t2 == 10 and np.array_equal(k2, KEYS[1])
+
+
+def test_set_packed_options():
+    block = np.stack(KEYS)
+    ref = PB["StoresSetPackedOptions"](Keys=block.astype("<f4").tobytes(), Dim=block.shape[1],
+                                       Values=[PB["StoresValue"](Bytes=v) for v in VALS])
+    data = wire.enc_set_packed(block, VALS)
+    assert data == ref.SerializeToString()
+    keys, vals = wire.dec_set_packed(data)
+    assert vals == VALS and keys.shape == block.shape and np.array_equal(keys, block)
+    with pytest.raises(ValueError):
+        wire.dec_set_packed(PB["StoresSetPackedOptions"](Keys=b"\x00" * 10, Dim=7).SerializeToString())
+    with pytest.raises(ValueError):
+        wire.dec_set_packed(PB["StoresSetPackedOptions"](Keys=b"\x00" * 28).SerializeToString())     # Dim missing
