@@ -708,8 +708,10 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     tfp_build.build()
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+        cpu_group = dist.new_group(backend="gloo")     # a barrier that keeps no kernel spinning on the waiting ranks' GPUs
     env = {"torch": torch, "dist": dist, "rank": rank, "local_rank": local_rank, "world": world, "device": device}
     cache = {}
     wl = WORKLOADS[args.workload]
@@ -735,12 +737,16 @@ def run_ours(args, rank: int, local_rank: int, world: int):
     cache.clear()
     torch.cuda.empty_cache()
     if world > 1 and args.inproc and args.workload == "c2" and not any("error" in v for v in also.values()):
+        # The other ranks wait on the CPU (gloo): an NCCL barrier would leave a kernel spinning on their GPUs, and a GPU
+        # time-slices between processes -- rank 0's kernels there would get every other millisecond.
+        torch.cuda.synchronize(device)
+        dist.barrier(group=cpu_group)
         if rank == 0:
             try:
                 also["inproc"] = measure_inproc(env, wl, args)
             except Exception as e:
                 also["inproc"] = {"error": f"{type(e).__name__}: {e}"[:300]}
-        dist.barrier()
+        dist.barrier(group=cpu_group)
 
     ok = head["parity"]["ok"] and all(v.get("parity", {}).get("ok", True) for v in also.values())
     if rank == 0:

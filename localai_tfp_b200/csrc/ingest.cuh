@@ -39,11 +39,12 @@ __host__ __device__ __forceinline__ uint64_t hash_finish(uint64_t sum, int dim) 
 // Per staged row: hash, isNormalized (store.go:313-324), and sqrt(mag2) in the reference's arithmetic
 // (store.go:420: fp64 sum of fp32-rounded squares, index order).  The sums of one row are sequential on purpose --
 // they must round exactly as the Go loops do -- so one THREAD owns one row; but the rows are read the way HBM
-// likes: a CTA of 128 threads owns 128 rows and walks them in [128 rows x 32 columns] tiles that its warps load
+// likes: a CTA of 64 threads owns 64 rows and walks them in [64 rows x 32 columns] tiles that its warps load
 // with coalesced 128-byte row segments into shared memory (row stride 33 floats: thread t then reads its own row
 // bank-conflict free).  The first version let every thread stride through its own row in global memory:
-// 54 GB/s at dim 1536, under 1 % of HBM.
-constexpr int kStatRows = 128;
+// 54 GB/s at dim 1536, under 1 % of HBM.  64 rows, not 128: the tile (8.4 KB) must fit into the shared memory a
+// persistent scan CTA leaves free on its SM (~13 KB), or every StoresSet waits for the running finds to end.
+constexpr int kStatRows = 64;
 constexpr int kStatCols = 32;
 __global__ void __launch_bounds__(kStatRows)
 row_stats_kernel(const float* __restrict__ rows, int64_t n, int dim, uint64_t* __restrict__ hash,

@@ -518,7 +518,12 @@ static int store_open(const tfp_cfg* cfg, tfp_store** out) {
     s->sm_count = prop.multiProcessorCount;
     s->max_smem = (int)prop.sharedMemPerBlockOptin;
     if (optin_all(s->max_smem)) { delete s; return -1; }
-    if (cudaStreamCreateWithFlags(&s->s_mut, cudaStreamNonBlocking) != cudaSuccess) { delete s; return fail(-1, "cudaStreamCreate failed"); }
+    {   // the mutation stream outranks the find streams: its small kernels slot in as scan CTAs retire instead of
+        // queueing behind every find in flight
+        int prio_lo = 0, prio_hi = 0;
+        cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if (cudaStreamCreateWithPriority(&s->s_mut, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { delete s; return fail(-1, "cudaStreamCreate failed"); }
+    }
     if (ctx_create(s, &s->default_ctx)) { cudaStreamDestroy(s->s_mut); delete s; return -1; }
     *out = s;
     return 0;

@@ -89,29 +89,31 @@ deleted = []                               # (writer, block, tag, rows) of what 
 
 
 def deleter():
+    """Removes a uniformly random 10 % of every batch written, staying two batches behind the writers.  A delete
+    compacts the shards it touches and so fences the finds for a moment: the victims of all batches that have
+    piled up meanwhile (up to 16) go into ONE StoresDelete call."""
     r = np.random.default_rng(9)
     done = 0
     try:
         while not stop.is_set():
             with lock:
-                todo = written[done:max(done, len(written) - 2)]     # stay two batches behind the writers
+                todo = written[done:max(done, len(written) - 2)][:16]
             if not todo:
                 time.sleep(0.002)
                 continue
-            for (w, j, tag, ids) in todo:
-                rows = np.sort(r.choice(B, size=B // 10, replace=False))
-                k = batch_rows(w, j, tag, rows)
-                out = np.empty(len(rows), np.int64)
-                store._check(L.tfp_store_delete(H, k.ctypes.data_as(fp), len(rows), D, out.ctypes.data_as(i64p)))
-                if not np.array_equal(out, ids[rows]):
-                    errors.append("deleter: the ids removed are not the ids the set call handed out")
-                    stop.set()
-                with lock:
-                    counts["del"] += len(rows)
+            picks = [np.sort(r.choice(B, size=B // 10, replace=False)) for _ in todo]
+            k = np.concatenate([batch_rows(w, j, tag, rows) for (w, j, tag, ids), rows in zip(todo, picks)])
+            want = np.concatenate([ids[rows] for (w, j, tag, ids), rows in zip(todo, picks)])
+            out = np.empty(len(k), np.int64)
+            store._check(L.tfp_store_delete(H, k.ctypes.data_as(fp), len(k), D, out.ctypes.data_as(i64p)))
+            if not np.array_equal(out, want):
+                errors.append("deleter: the ids removed are not the ids the set calls handed out")
+                stop.set()
+            with lock:
+                counts["del"] += len(k)
+                for (w, j, tag, ids), rows in zip(todo, picks):
                     deleted.append((w, j, tag, rows))
-                done += 1
-                if stop.is_set():
-                    break
+            done += len(todo)
     except Exception as e:      # noqa: BLE001
         errors.append(f"deleter: {e!r}")
         stop.set()
