@@ -193,7 +193,11 @@ void tfp_find_ctx_destroy(tfp_find_ctx* c);
  * query's path and |q| on the host exactly as store.go:313-324,435-439. */
 int  tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int dim);
 /* Enqueue the scan + top-k for staged queries [first, first+count).  Results
- * stay in HBM.  Returns without waiting. */
+ * stay in HBM.  Returns without waiting for the GPU -- with one exception: a batch
+ * that takes the tensor-core path (>= 3 same-path queries on a large store) waits
+ * for that pass, because its per-query status words decide whether some queries
+ * need a second pass (3xTF32 filter, then the exact kernel) before the launch is
+ * complete. */
 int  tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int topk);
 /* Wait, then copy results of the last launch to the host (same layout as
  * tfp_store_find_batch for `count` queries). */

@@ -3,8 +3,10 @@
 // Replaces the reference's "keys are kept sorted, look up by binary search"
 // (backend/go/stores/store.go:60-64 findInSortedSlice, used by StoresDelete
 // :226 and StoresGet :286, and the merge in StoresSet :150-189).  Hashes come
-// from the device (ingest.cuh row_stats_kernel); the host never reads key
-// bytes.  Several slots may share a hash (true duplicates stored by one
+// from the device (ingest.cuh row_stats_kernel); the index itself never reads
+// key bytes (the host only compares the keys of ONE request with each other, to
+// put them in the reference's sorted order: tfp_store.cu sorted_order).
+// Several slots may share a hash (true duplicates stored by one
 // StoresSet call, or a 64-bit collision); callers confirm every candidate on
 // the device before trusting it.
 #pragma once

@@ -158,6 +158,9 @@ static std::vector<int> all_shards(const tfp_multi* m) {
 static void multi_close(tfp_store* top) {
     tfp_multi* m = top->multi;
     if (!m) return;
+    if (tuning().set_trace && top->tr_calls > 0)
+        fprintf(stderr, "tfp multi set trace (%lld calls, us per call): routing %.0f | slowest shard's gather %.0f | all shards %.0f\n",
+                (long long)top->tr_calls, top->tr_us[0] / top->tr_calls, top->tr_us[1] / top->tr_calls, top->tr_us[2] / top->tr_calls);
     for (Worker* w : m->workers) if (w) { w->shutdown(); delete w; }
     for (size_t g = 0; g < m->shards.size(); g++) {
         if (!m->shards[g]) continue;
@@ -296,20 +299,29 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     if (check_scatter_grid(n)) return 2;
     std::lock_guard<std::mutex> mut(top->mut_mu);   // one mutation at a time; finds go on (the shards publish appends themselves)
     if (multi_latch(top, dim, "Try to add key with length %d when existing length is %d")) return 1;
+    const double t0 = now_us();
     Routed r;
     route_rows(m, keys, n, dim, r);
+    const double t1 = now_us();
     std::vector<std::vector<int64_t>> ids(m->shards.size());
     std::vector<std::vector<uint8_t>> isnew(m->shards.size());
+    std::vector<double> t_stage(m->shards.size(), 0.0);
     int rc = run_shards(m, r.active, [&](int g) -> int {
         const std::vector<int64_t>& idx = r.idx[(size_t)g];
         const float* rows = nullptr;
+        const double a = now_us();
         if (stage_routed(m, g, keys, dim, idx, &rows)) return -1;
+        t_stage[(size_t)g] = now_us() - a;
         ids[(size_t)g].resize(idx.size());
         isnew[(size_t)g].resize(idx.size());
         return store_set(m->shards[(size_t)g], rows, (int64_t)idx.size(), dim, (int64_t)idx.size(), ids[(size_t)g].data(),
                          isnew[(size_t)g].data());
     });
     if (rc) return rc;
+    top->tr_us[0] += t1 - t0;                                             // routing
+    top->tr_us[1] += *std::max_element(t_stage.begin(), t_stage.end());   // slowest shard's gather into pinned staging
+    top->tr_us[2] += now_us() - t1;                                       // all shards, start to finish
+    top->tr_calls++;
     for (int g : r.active)
         for (size_t j = 0; j < r.idx[(size_t)g].size(); j++) {
             const int64_t i = r.idx[(size_t)g][j];

@@ -10,6 +10,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstddef>
@@ -153,6 +154,7 @@ struct Tuning {
     bool mma_trace = false;        // print the tensor-core launch shape
     bool scan_times = false;       // per-CTA time stamps of every exact scan, printed by tfp_find_ctx_sync
     int scan_stages = 0;           // cap on the exact scan's TMA ring depth (0 = as many as fit): fewer stages let two CTAs share an SM
+    bool set_trace = false;        // print where StoresSet spends its time when the store closes
     bool xchg_stream_wait = false; // peer exchange: wait for the peers' words with stream memory operations instead of inside the merge kernel
 };
 static const Tuning& tuning() {
@@ -168,6 +170,7 @@ static const Tuning& tuning() {
         x.mma_trace = getenv("TFP_MMA_TRACE") != nullptr;
         x.scan_times = getenv("TFP_SCAN_TIMES") != nullptr;
         if (const char* e = getenv("TFP_SCAN_STAGES")) x.scan_stages = atoi(e);
+        x.set_trace = getenv("TFP_SET_TRACE") != nullptr;
         if (const char* e = getenv("TFP_XCHG_STREAM_WAIT")) x.xchg_stream_wait = atoi(e) != 0;
         return x;
     }();
@@ -323,6 +326,8 @@ struct tfp_store {
     std::mutex find_mu;                // the built-in context serves one synchronous find at a time
     int sm_count = 148;
     int max_smem = 0;
+    double tr_us[6] = {0, 0, 0, 0, 0, 0};   // TFP_SET_TRACE: hash + D2H, index probe, verify, grow / fence, scatter + sync, publish
+    int64_t tr_calls = 0;
 };
 
 struct tfp_find_ctx {
@@ -531,6 +536,11 @@ static int store_open(const tfp_cfg* cfg, tfp_store** out) {
 
 static void store_close(tfp_store* s) {
     if (!s) return;
+    if (tuning().set_trace && s->tr_calls > 0)
+        fprintf(stderr, "tfp set trace (device %d, %lld calls, us per call): hash + D2H %.0f | index probe %.0f | verify %.0f | grow / fence %.0f | "
+                        "scatter + sync %.0f | publish %.0f\n", s->device, (long long)s->tr_calls, s->tr_us[0] / s->tr_calls,
+                s->tr_us[1] / s->tr_calls, s->tr_us[2] / s->tr_calls, s->tr_us[3] / s->tr_calls, s->tr_us[4] / s->tr_calls,
+                s->tr_us[5] / s->tr_calls);
     cudaSetDevice(s->device);
     cudaDeviceSynchronize();
     std::vector<tfp_find_ctx*> ctxs = s->ctxs;
@@ -601,8 +611,13 @@ struct Lookup {
 // the device.  `order` gives the sequence in which rows claim stored slots (each
 // stored slot is claimed at most once per call, like the reference's walks over
 // a sorted batch: store.go:154-189, :225-238, :285-301).
+static inline double now_us() {
+    return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::vector<int64_t>& order, Lookup& L) {
     const int dim = s->dim;
+    const double t0 = now_us();
     if (s->st_hash.reserve((size_t)n * 8) || s->st_knorm.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
     int threads = kStatRows;
     int64_t blocks = (n + threads - 1) / threads;
@@ -614,6 +629,8 @@ static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::
     CU_OK(cudaMemcpyAsync(L.hash.data(), s->st_hash.p, (size_t)n * 8, cudaMemcpyDeviceToHost, s->s_mut));
     CU_OK(cudaMemcpyAsync(L.is_norm.data(), s->st_isnorm.p, (size_t)n, cudaMemcpyDeviceToHost, s->s_mut));
     CU_OK(cudaStreamSynchronize(s->s_mut));
+    const double t1 = now_us();
+    s->tr_us[0] += t1 - t0;
 
     // candidate pairs (row, slot)
     std::vector<uint32_t> pr, ps;
@@ -623,6 +640,8 @@ static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::
         s->index.for_each(L.hash[(size_t)i], [&](uint32_t slot) { pr.push_back((uint32_t)i); ps.push_back(slot); });
     }
     first[(size_t)n] = pr.size();
+    const double t2 = now_us();
+    s->tr_us[1] += t2 - t1;
     std::vector<uint8_t> eq(pr.size(), 0);
     if (!pr.empty()) {
         size_t m = pr.size();
@@ -637,6 +656,7 @@ static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::
         CU_OK(cudaMemcpyAsync(eq.data(), s->st_pair_eq.p, m, cudaMemcpyDeviceToHost, s->s_mut));
         CU_OK(cudaStreamSynchronize(s->s_mut));
     }
+    s->tr_us[2] += now_us() - t2;
     L.match.assign((size_t)n, -1);
     std::unordered_set<uint32_t> claimed;
     for (int64_t oi = 0; oi < n; oi++) {
@@ -691,6 +711,7 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         }
         if (out_ids) out_ids[i] = ids[(size_t)i];
     }
+    const double t3 = now_us();
     const bool overwrites = n_new != n;
     const bool must_move = s->n + n_new > s->cap && !(vmm_api() && (s->vm_keys.active() || s->cap == 0));
     std::unique_lock<RwMutex> fence(s->rw, std::defer_lock);
@@ -704,6 +725,8 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         if (!fence.owns_lock()) grow.lock();
         if (ensure_capacity(s, s->n + n_new)) return -1;
     }
+    const double t4 = now_us();
+    s->tr_us[3] += t4 - t3;
     if (s->st_src.reserve((size_t)n * 4) || s->st_dst.reserve((size_t)n * 4) || s->st_ids.reserve((size_t)n * 8)) return -1;
     CU_OK(cudaMemcpyAsync(s->st_src.p, src.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
     CU_OK(cudaMemcpyAsync(s->st_dst.p, dst.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s->s_mut));
@@ -726,6 +749,8 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         }
     }
     CU_OK(cudaStreamSynchronize(s->s_mut));   // the rows are in HBM ...
+    const double t5 = now_us();
+    s->tr_us[4] += t5 - t4;
     {                                         // ... now finds may see them
         std::unique_lock<RwMutex> pub(s->rw, std::defer_lock);
         if (!fence.owns_lock()) pub.lock();
@@ -733,6 +758,8 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         s->next_id += n_new;
         if (!all_norm) s->normalized = false;
     }
+    s->tr_us[5] += now_us() - t5;
+    s->tr_calls++;
     return 0;
 }
 
@@ -785,6 +812,7 @@ static int store_set_device(tfp_store* s, const float* d_keys, int64_t n, int di
 static void sorted_order(const float* keys, int64_t n, int dim, std::vector<int64_t>& order) {
     order.resize((size_t)n);
     for (int64_t i = 0; i < n; i++) order[(size_t)i] = i;
+    if (n < 2) return;
     std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) {
         return cmp_rows(keys + (size_t)a * dim, keys + (size_t)b * dim, dim) < 0;
     });

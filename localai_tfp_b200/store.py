@@ -196,8 +196,8 @@ class Store:
         q = np.ascontiguousarray(np.asarray(key, dtype=np.float32).reshape(-1))
         k = int(topk)
         kk = max(k, 1)
-        rows = len(self)
-        kk = min(kk, max(rows, 1))  # the result holds min(topk, rows) entries (store.go:386-388)
+        if kk > 1024:               # (a small top-k needs no look at the row count: the buffers are cheap either way)
+            kk = min(kk, max(len(self), 1))  # the result holds min(topk, rows) entries (store.go:386-388)
         n = C.c_int()
         path = C.c_int(-1)
         ids = np.empty(kk, np.int64)

@@ -200,6 +200,28 @@ def test_c1_shape_10k_by_384(tfp, oracle):
     s.close()
 
 
+def test_c2_shape_full_store_oracle_scan(tfp, oracle):
+    """BASELINE.json configs[1] at full size against the oracle's scan of the WHOLE store ("full-N oracle
+    is run for C1/C2"): 1M x 768 normalised, top-10, three queries; similarities bit for bit, ids position by
+    position (exactly equal scores exempt)."""
+    import torch
+    n, d = 1_000_000, 768
+    g = torch.Generator(device="cuda").manual_seed(0x5EED0002)
+    K = torch.randn((n, d), generator=g, device="cuda", dtype=torch.float32)
+    K /= K.norm(dim=1, keepdim=True)
+    s = tfp.Store(capacity_rows=n)
+    s.set_device(K.data_ptr(), n, d)
+    Kh = K.cpu().numpy()
+    Q = make_keys(2, d, seed=99, normalized=True)
+    for q in (Q[0], Q[1], Kh[777_777]):
+        ids, sims = s.find_ids(q, 10)
+        check_find_against_scores(ids, sims, oracle.scores_block(Kh, q, True), 10)
+    res = s.find_batch(np.stack([Q[0], Q[1], Kh[5], Kh[6]]), 10)          # the tensor-core path over the same store
+    for (ids, sims), q in zip(res, (Q[0], Q[1])):
+        check_find_against_scores(ids, sims, oracle.scores_block(Kh, q, True), 10)
+    s.close()
+
+
 def test_c2_shape_subsample_1m_by_768(tfp, oracle):
     """BASELINE.json configs[1] at full size: 1M x 768 normalised, top-10.  The oracle scores the rows
     the GPU returned plus a 20k-row slice; size-independent properties cover the rest."""
