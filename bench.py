@@ -645,17 +645,19 @@ def measure_inproc(env, wl: Workload, args):
     Q = gen_queries(wl)
     k = wl.topk
 
-    def finder(nfinds, first, out):
+    def finder(nfinds, first, out, with_keys):
         n = C.c_int()
         ids = np.empty(k, np.int64); sims = np.empty(k, np.float32)
+        rows = np.empty((k, wl.dim), np.float32) if with_keys else None
         for i in range(nfinds):
             q = Q[(first + i) % N_QUERIES]
-            st._check(L.tfp_store_find(st._h, q.ctypes.data, wl.dim, k, C.byref(n), ids.ctypes.data, sims.ctypes.data, None, None))
+            st._check(L.tfp_store_find(st._h, q.ctypes.data, wl.dim, k, C.byref(n), ids.ctypes.data, sims.ctypes.data,
+                                       rows.ctypes.data if with_keys else None, None))
         out.append((ids.copy(), sims.copy(), (first + nfinds - 1) % N_QUERIES))
 
-    def run(threads, nfinds):
+    def run(threads, nfinds, with_keys=False):
         outs = []
-        ts = [threading.Thread(target=finder, args=(nfinds, 7 * t, outs)) for t in range(threads)]
+        ts = [threading.Thread(target=finder, args=(nfinds, 7 * t, outs, with_keys)) for t in range(threads)]
         t0 = time.perf_counter()
         [t.start() for t in ts]
         [t.join() for t in ts]
@@ -663,11 +665,12 @@ def measure_inproc(env, wl: Workload, args):
 
     lanes = 4
     run(lanes, 8)
+    run(1, 8, True)
     per_thread = max(args.steps, 50)
-    reps = [run(lanes, per_thread)[0] for _ in range(5)]
-    qps = lanes * per_thread / float(np.median(reps))
-    lat = [run(1, per_thread)[0] for _ in range(3)]
-    single_ms = float(np.median(lat)) / per_thread * 1e3
+    qps = lanes * per_thread / float(np.median([run(lanes, per_thread)[0] for _ in range(5)]))
+    qps_keys = lanes * per_thread / float(np.median([run(lanes, per_thread, True)[0] for _ in range(5)]))
+    single_ms = float(np.median([run(1, per_thread)[0] for _ in range(3)])) / per_thread * 1e3
+    single_keys_ms = float(np.median([run(1, per_thread, True)[0] for _ in range(3)])) / per_thread * 1e3
     # parity: returned rows re-scored by the oracle, and a sample of the store scanned by it
     order = np.argsort(all_ids)
     problems = []
@@ -690,7 +693,9 @@ def measure_inproc(env, wl: Workload, args):
     out = {"what": "C2 as ONE logical store over %d GPUs in ONE process (tfp_store_open_devices), driven through tfp_store_find "
                    "with host buffers from %d host threads" % (world, lanes),
            "value": qps, "unit": "queries/s", "timing": "wall clock, median of 5 runs of %d finds per thread" % per_thread,
-           "single_find_ms": single_ms, "shard_rows": shard_rows,
+           "value_with_key_rows": qps_keys,
+           "single_find_ms": single_ms, "single_find_with_key_rows_ms": single_keys_ms, "shard_rows": shard_rows,
+           "h2d_bytes_per_find": world * (wl.dim * 4 + 16), "d2h_bytes_per_find_with_key_rows": 16 + k * 20 + k * wl.dim * 4,
            "parity": {"ok": not problems, "checked_queries": len(outs), "sample_rows_scanned_by_oracle": int(len(sample))}}
     if problems:
         out["parity"]["problems"] = problems[:6]
@@ -748,6 +753,17 @@ def run_ours(args, rank: int, local_rank: int, world: int):
                 also["inproc"] = {"error": f"{type(e).__name__}: {e}"[:300]}
         dist.barrier(group=cpu_group)
 
+    if rank == 0 and "inproc" in also and "error" not in also["inproc"]:
+        # The call a user of the drop-in makes at N GPUs is tfp_store_find on ONE store handle in ONE process (LocalAI runs
+        # one backend process): that is the end-to-end figure -- one caller, one find after the other, host query in, host
+        # ids + similarities + key rows out, like the one-GPU e2e.  The SPMD host's figure stays beside it.
+        ip = also["inproc"]
+        head["e2e_spmd_host"] = dict(head["e2e"], path="ShardedStore.StoresFind, one process per GPU (torch.distributed bootstrap)")
+        head["e2e"] = {"value": 1e3 / ip["single_find_with_key_rows_ms"], "unit": "queries/s",
+                       "h2d_bytes_per_step": ip["h2d_bytes_per_find"], "d2h_bytes_per_step": ip["d2h_bytes_per_find_with_key_rows"],
+                       "path": "tfp_store_find on one logical store over %d GPUs in one process, one caller thread, "
+                               "wall clock; %.0f queries/s with 4 caller threads" % (world, ip["value_with_key_rows"])}
+
     ok = head["parity"]["ok"] and all(v.get("parity", {}).get("ok", True) for v in also.values())
     if rank == 0:
         line = {
@@ -756,7 +772,7 @@ def run_ours(args, rank: int, local_rank: int, world: int):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         }
         for k in ("repeats", "repeat_ms", "timing", "single_find_ms", "config", "clocks", "tensor_core_path", "e2e",
-                  "gpu_launches", "roofline", "parity", "cpu_baseline"):
+                  "e2e_spmd_host", "gpu_launches", "roofline", "parity", "cpu_baseline"):
             if k in head:
                 line[k] = head[k]
         if also:

@@ -159,8 +159,9 @@ static void multi_close(tfp_store* top) {
     tfp_multi* m = top->multi;
     if (!m) return;
     if (tuning().set_trace && top->tr_calls > 0)
-        fprintf(stderr, "tfp multi set trace (%lld calls, us per call): routing %.0f | slowest shard's gather %.0f | all shards %.0f\n",
-                (long long)top->tr_calls, top->tr_us[0] / top->tr_calls, top->tr_us[1] / top->tr_calls, top->tr_us[2] / top->tr_calls);
+        fprintf(stderr, "tfp multi set trace (%lld calls, us per call): wait for the mutation lock %.0f | routing %.0f | slowest shard's gather %.0f | "
+                        "all shards %.0f\n", (long long)top->tr_calls, top->tr_us[3] / top->tr_calls, top->tr_us[0] / top->tr_calls,
+                top->tr_us[1] / top->tr_calls, top->tr_us[2] / top->tr_calls);
     for (Worker* w : m->workers) if (w) { w->shutdown(); delete w; }
     for (size_t g = 0; g < m->shards.size(); g++) {
         if (!m->shards[g]) continue;
@@ -275,7 +276,18 @@ struct Routed {
 static void route_rows(const tfp_multi* m, const float* keys, int64_t n, int dim, Routed& r) {
     const int G = (int)m->shards.size();
     r.idx.assign((size_t)G, {});
-    for (int64_t i = 0; i < n; i++) r.idx[(size_t)route_of(keys + (size_t)i * dim, dim, G)].push_back(i);
+    // The 16 sampled elements of a row sit in 16 different cache lines of memory nobody has touched yet: without
+    // help the loop runs at one DRAM latency per sample (measured 2.1 ms for 8192 rows of 1536 floats, as long as
+    // everything the GPUs do for the call).  Prefetch the samples of the row a few iterations ahead.
+    const int samples = dim < 16 ? dim : 16;
+    constexpr int kAhead = 6;
+    for (int64_t i = 0; i < n; i++) {
+        if (i + kAhead < n) {
+            const float* nxt = keys + (size_t)(i + kAhead) * dim;
+            for (int j = 0; j < samples; j++) __builtin_prefetch(nxt + (int64_t)j * dim / samples, 0, 0);
+        }
+        r.idx[(size_t)route_of(keys + (size_t)i * dim, dim, G)].push_back(i);
+    }
     for (int g = 0; g < G; g++) if (!r.idx[(size_t)g].empty()) r.active.push_back(g);
 }
 
@@ -297,9 +309,11 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     if (n != n_values) return fail(1, "len(keys) = %lld, len(values) = %lld", (long long)n, (long long)n_values);
     if (!keys || dim <= 0) return fail(2, "tfp_store_set: keys is NULL or dim <= 0");
     if (check_scatter_grid(n)) return 2;
+    const double t_wait = now_us();
     std::lock_guard<std::mutex> mut(top->mut_mu);   // one mutation at a time; finds go on (the shards publish appends themselves)
     if (multi_latch(top, dim, "Try to add key with length %d when existing length is %d")) return 1;
     const double t0 = now_us();
+    top->tr_us[3] += t0 - t_wait;
     Routed r;
     route_rows(m, keys, n, dim, r);
     const double t1 = now_us();

@@ -29,6 +29,7 @@ ap.add_argument("--writers", type=int, default=4)
 ap.add_argument("--readers", type=int, default=16)
 ap.add_argument("--dim", type=int, default=1536)
 ap.add_argument("--batch", type=int, default=8192)
+ap.add_argument("--delete-group", type=int, default=16, help="batches whose victims go into one StoresDelete call")
 args = ap.parse_args()
 
 import torch
@@ -36,6 +37,7 @@ import localai_tfp_b200 as tfp
 from oracle import oracle as orc
 
 D, B = args.dim, args.batch
+DEL_GROUP = max(1, args.delete_group)
 devs = list(range(torch.cuda.device_count())) if args.devices == "all" else [int(x) for x in args.devices.split(",")]
 if len(devs) == 1:
     devs = devs * 2            # one GPU: two shards on it, so that the multi-GPU code path is the one that runs
@@ -91,16 +93,18 @@ deleted = []                               # (writer, block, tag, rows) of what 
 def deleter():
     """Removes a uniformly random 10 % of every batch written, staying two batches behind the writers.  A delete
     compacts the shards it touches and so fences the finds for a moment: the victims of all batches that have
-    piled up meanwhile (up to 16) go into ONE StoresDelete call."""
+    piled up meanwhile (DEL_GROUP of them) go into ONE StoresDelete call."""
     r = np.random.default_rng(9)
     done = 0
     try:
         while not stop.is_set():
             with lock:
-                todo = written[done:max(done, len(written) - 2)][:16]
-            if not todo:
-                time.sleep(0.002)
+                todo = written[done:max(done, len(written) - 2)][:DEL_GROUP]
+            if len(todo) < DEL_GROUP and not stop.is_set():
+                time.sleep(0.002)            # let a full group pile up: one fence per DEL_GROUP batches
                 continue
+            if not todo:
+                break
             picks = [np.sort(r.choice(B, size=B // 10, replace=False)) for _ in todo]
             k = np.concatenate([batch_rows(w, j, tag, rows) for (w, j, tag, ids), rows in zip(todo, picks)])
             want = np.concatenate([ids[rows] for (w, j, tag, ids), rows in zip(todo, picks)])
