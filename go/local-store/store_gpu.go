@@ -64,7 +64,8 @@ type Store struct {
 	// the library serialises mutations itself and lets finds overlap.
 	base.Base
 
-	mu       sync.RWMutex // guards values (and keeps a find's id -> value lookups consistent with mutations)
+	mu       sync.RWMutex // guards the values map, for the instant a lookup or an update takes
+	setMu    sync.Mutex   // one mutation at a time, from its library call until its values are in the map
 	h        *C.tfp_store
 	values   map[int64][]byte
 	finds    chan findReq
@@ -126,6 +127,7 @@ func NewStore() *Store {
 	signal.Notify(sig, syscall.SIGTERM)
 	go func() {
 		<-sig
+		s.setMu.Lock()
 		s.mu.Lock()
 		if s.snapshot != "" {
 			_ = s.save(s.snapshot)
@@ -180,6 +182,8 @@ func (s *Store) Load(opts *pb.ModelOptions) error {
 	if opts == nil || opts.ModelFile == "" {
 		return nil
 	}
+	s.setMu.Lock()
+	defer s.setMu.Unlock()
 	s.mu.Lock()
 	defer s.mu.Unlock()
 	s.snapshot = opts.ModelFile
@@ -201,18 +205,46 @@ func (s *Store) StoresSet(opts *pb.StoresSetOptions) error {
 	}
 	n := len(opts.Keys)
 	ids := make([]int64, n+1)
-	s.mu.Lock()
-	defer s.mu.Unlock()
+	// Finds are NOT held up by a StoresSet: the library appends beside them and this host takes the map's lock only
+	// to insert the values.  (A find that already sees a new row but not yet its value waits for setMu: valuesOf.)
+	s.setMu.Lock()
+	defer s.setMu.Unlock()
 	if err := call(func() C.int {
 		return C.tfp_store_set(s.h, buf, C.int64_t(n), C.int(dim), C.int64_t(len(opts.Values)),
 			(*C.int64_t)(unsafe.Pointer(&ids[0])), nil)
 	}); err != nil {
 		return err
 	}
+	s.mu.Lock()
 	for i := 0; i < n; i++ {
 		s.values[ids[i]] = opts.Values[i].Bytes
 	}
+	s.mu.Unlock()
 	return nil
+}
+
+// valuesOf looks up the values of the ids a find returned.  An id whose value is not in the map yet belongs to a
+// StoresSet that has published its rows but not finished: wait for it (setMu), then look again.
+func (s *Store) valuesOf(ids []int64) [][]byte {
+	out := make([][]byte, len(ids))
+	missing := false
+	s.mu.RLock()
+	for i, id := range ids {
+		v, ok := s.values[id]
+		out[i] = v
+		missing = missing || !ok
+	}
+	s.mu.RUnlock()
+	if missing {
+		s.setMu.Lock()
+		s.setMu.Unlock()
+		s.mu.RLock()
+		for i, id := range ids {
+			out[i] = s.values[id]
+		}
+		s.mu.RUnlock()
+	}
+	return out
 }
 
 func (s *Store) StoresDelete(opts *pb.StoresDeleteOptions) error {
@@ -223,18 +255,20 @@ func (s *Store) StoresDelete(opts *pb.StoresDeleteOptions) error {
 	}
 	n := len(opts.Keys)
 	ids := make([]int64, n+1)
-	s.mu.Lock()
-	defer s.mu.Unlock()
+	s.setMu.Lock()
+	defer s.setMu.Unlock()
 	if err := call(func() C.int {
 		return C.tfp_store_delete(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0])))
 	}); err != nil {
 		return err
 	}
+	s.mu.Lock()
 	for i := 0; i < n; i++ {
 		if ids[i] >= 0 {
 			delete(s.values, ids[i])
 		}
 	}
+	s.mu.Unlock()
 	return nil
 }
 
@@ -248,8 +282,6 @@ func (s *Store) StoresGet(opts *pb.StoresGetOptions) (pb.StoresGetResult, error)
 	ids := make([]int64, n+1)
 	order := make([]int64, n+1)
 	var found C.int64_t
-	s.mu.RLock()
-	defer s.mu.RUnlock()
 	if err := call(func() C.int {
 		return C.tfp_store_get(s.h, buf, C.int64_t(n), C.int(dim), (*C.int64_t)(unsafe.Pointer(&ids[0])),
 			(*C.int64_t)(unsafe.Pointer(&order[0])), &found)
@@ -257,10 +289,14 @@ func (s *Store) StoresGet(opts *pb.StoresGetOptions) (pb.StoresGetResult, error)
 		return pb.StoresGetResult{}, err
 	}
 	res := pb.StoresGetResult{}
+	hit := make([]int64, 0, int(found))
 	for j := 0; j < int(found); j++ {
-		i := order[j]
-		res.Keys = append(res.Keys, &pb.StoresKey{Floats: opts.Keys[i].Floats})
-		res.Values = append(res.Values, &pb.StoresValue{Bytes: s.values[ids[i]]})
+		hit = append(hit, ids[order[j]])
+	}
+	vals := s.valuesOf(hit)
+	for j := 0; j < int(found); j++ {
+		res.Keys = append(res.Keys, &pb.StoresKey{Floats: opts.Keys[order[j]].Floats})
+		res.Values = append(res.Values, &pb.StoresValue{Bytes: vals[j]})
 	}
 	return res, nil
 }
@@ -305,8 +341,6 @@ func (s *Store) batcher() {
 
 func (s *Store) findBatch(topk, dim int, reqs []findReq) {
 	nq := len(reqs)
-	s.mu.RLock()
-	defer s.mu.RUnlock()
 	var st C.tfp_stats
 	C.tfp_store_stats(s.h, &st)
 	slots := topk
@@ -339,10 +373,11 @@ func (s *Store) findBatch(topk, dim int, reqs []findReq) {
 		}
 		n := int(ns[i])
 		res := pb.StoresFindResult{Similarities: sims[i*slots : i*slots+n]}
+		vals := s.valuesOf(ids[i*slots : i*slots+n])
 		for j := 0; j < n; j++ {
 			at := i*slots + j
 			res.Keys = append(res.Keys, &pb.StoresKey{Floats: keys[at*dim : (at+1)*dim]})
-			res.Values = append(res.Values, &pb.StoresValue{Bytes: s.values[ids[at]]})
+			res.Values = append(res.Values, &pb.StoresValue{Bytes: vals[j]})
 		}
 		r.done <- findRes{res: res}
 	}

@@ -237,6 +237,14 @@ static int multi_open(const tfp_cfg* cfg, const int* devices, int n_devices, tfp
             c->x_seq = 0;
             c->x_peer[0] = root->xbuf.as<uint8_t>();
             c->x_ready = m->p2p;
+            if (m->shared_device) {
+                // Two shards on one GPU (a test configuration): a merge kernel that spins until the other shard's scan
+                // has run would be one launch waiting for another on the SAME GPU, and nothing guarantees that the two
+                // run at the same time.  There the merge is ordered behind the scans with events instead.
+                c->x_no_spin = true;
+                if (set_device(m->shards[(size_t)g])) return bail(-1);
+                if (cudaEventCreateWithFlags(&c->x_done_ev, cudaEventDisableTiming) != cudaSuccess) return bail(fail(-1, "cudaEventCreate failed"));
+            }
         }
     }
     for (int g = 1; g < n_devices; g++) {
@@ -464,6 +472,7 @@ static int multi_find_device(tfp_multi* m, MultiLane& L, const float* q, int nq,
         if (r) return r;
         r = p2p_launch_locked(c, 0, nq, topk, with_keys, /*defer_merge=*/true);
         if (r) return r;
+        if (c->x_done_ev) CU_OK(cudaEventRecord(c->x_done_ev, c->stream));
         launched[(size_t)g] = 1;
         return 0;
     });
@@ -478,6 +487,8 @@ static int multi_find_device(tfp_multi* m, MultiLane& L, const float* q, int nq,
     }
     // every shard's scan is in its stream: now the merge kernel, which waits for their records, can go in
     if (set_device(m->shards[0])) return -1;
+    if (root->x_no_spin)
+        for (int g = 1; g < G; g++) CU_OK(cudaStreamWaitEvent(root->stream, L.ctx[(size_t)g]->x_done_ev, 0));
     {
         std::shared_lock<RwMutex> lk(m->shards[0]->rw);
         rc = p2p_merge_locked(root);
@@ -559,10 +570,7 @@ static int multi_find_batch(tfp_store* top, const float* q, int nq, int dim, int
         qi[(size_t)i].pad = 0;
     }
     const size_t need = out_keys ? tfp_p2p_slot_bytes_with_keys(nq, topk, dim) : record_bytes(topk) * (size_t)nq;
-    // Shards that share a GPU: the waiting merge CTA and the scan it waits for then compete for the same SMs, and a
-    // merge with a large sort buffer could keep the scan's last CTA from ever starting.  Keep the merge tiny there.
-    const int64_t merge_cap = m->shared_device ? 512 : 16384;
-    const bool on_device = m->p2p && (int64_t)G * topk <= merge_cap && need <= m->slot_bytes;
+    const bool on_device = m->p2p && (int64_t)G * topk <= 16384 && need <= m->slot_bytes;
     const int lane = multi_lane_acquire(m);
     MultiLane& L = m->lanes[(size_t)lane];
     int rc = on_device ? multi_find_device(m, L, q, nq, dim, topk, qi.data(), out_n, out_ids, out_sims, out_keys, out_path)

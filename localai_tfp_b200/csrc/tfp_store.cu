@@ -362,6 +362,8 @@ struct tfp_find_ctx {
     bool x_root_mode = false;            // one process over several GPUs: records are gathered on shard 0 only
     int x_m_count = 0;                   // the pending peer-exchange merge: queries, and whether key rows travel too
     bool x_m_with_keys = false;
+    bool x_no_spin = false;              // the merge must not wait inside the kernel (shards sharing one GPU): the caller orders it with events
+    cudaEvent_t x_done_ev = nullptr;     // ... recorded on this context's stream after its scan and pushes
     bool x_pushed = false;               // the last launch pushed its records from the scan kernel itself
     bool keys_gathered = false;          // the last launch's scan kernels wrote the winning key rows themselves
     int64_t mma_passes = 0, mma_fallbacks = 0, mma_escalated = 0;
@@ -1060,6 +1062,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     for (int r = 0; r < kXchgMaxWorld; r++)
         if (c->x_peer[r] && r != c->x_me && !c->x_root_mode) cudaIpcCloseMemHandle(c->x_peer[r]);
     c->xbuf.release();
+    if (c->x_done_ev) cudaEventDestroy(c->x_done_ev);
     if (c->stream) cudaStreamDestroy(c->stream);
     DevBuf* bufs[] = {&c->d_in, &c->part, &c->part_cnt, &c->sync_words, &c->all_cand, &c->sorted_cand,
                       &c->cub_tmp, &c->out_block, &c->dbg_times, &c->mma_qsplit, &c->mma_cand, &c->mma_small, &c->gathered, &c->merged};
@@ -2081,8 +2084,8 @@ static int p2p_merge_locked(tfp_find_ctx* c) {
     unsigned int* words = (unsigned int*)(c->xbuf.as<uint8_t>() + flags_off);
     // The merge kernel waits for the peers' words itself (default).  TFP_XCHG_STREAM_WAIT=1 keeps the wait in the
     // stream instead: one cuStreamWaitValue32 per peer, measured 7 driver calls + a late kernel launch per find.
-    const bool kernel_wait = !tuning().xchg_stream_wait;
-    if (!kernel_wait) {
+    const bool kernel_wait = !tuning().xchg_stream_wait && !c->x_no_spin;
+    if (!kernel_wait && !c->x_no_spin) {
         if (wait32_api()) return -7;
         for (int r = 0; r < c->x_world; r++) {
             if (r == c->x_me) continue;

@@ -92,7 +92,7 @@ class _FindBatcher:
                 for i, (key, k, fut) in enumerate(group):
                     ids, sims = res[i]
                     fut.set_result(([] if no_keys else [keys[i, j, :].copy() for j in range(len(ids))],
-                                    [b.store.values.get(int(x)) for x in ids], sims))
+                                    b.store._values_of([int(x) for x in ids]), sims))
             except Exception as e:
                 for _, _, fut in group:
                     if not fut.done():
@@ -194,7 +194,7 @@ class Backend:
         if not no_keys:
             return self.store.StoresFind(key, topk)
         ids, sims = self.store.find_ids(key, topk)        # no key rows gathered, copied or encoded
-        return [], [self.store.values.get(int(x)) for x in ids], sims
+        return [], self.store._values_of([int(x) for x in ids]), sims
 
     def StoresFind(self, request: bytes, context) -> bytes:
         key, topk, no_keys = wire.dec_find_ext(request)
@@ -230,7 +230,7 @@ class Backend:
                 res, rows = st.find_batch(qs, topk, with_keys=True)
                 for i, (ids, sims) in enumerate(res):
                     out.append(([rows[i, j, :].copy() for j in range(len(ids))],
-                                [st.values.get(int(x)) for x in ids], sims))
+                                st._values_of([int(x) for x in ids]), sims))
             return out
         return wire.enc_find_batch_result(self._run(context, serve))
 

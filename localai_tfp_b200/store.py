@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from typing import List, Sequence, Tuple
 
 import numpy as np
@@ -90,6 +91,7 @@ class Store:
         self.device = device
         self.devices = list(devices) if devices is not None else [device]
         self.values = {}  # id -> bytes; values never cross the C ABI (store.go:23)
+        self._set_mu = threading.Lock()   # held by a StoresSet from its library call until its values are in the map
         self.last_path = None
 
     # -- plumbing ----------------------------------------------------------
@@ -150,10 +152,22 @@ class Store:
         n = len(ks)
         ids = np.empty(max(n, 1), np.int64)
         new = np.empty(max(n, 1), np.uint8)
-        self._check(self._L.tfp_store_set(self._h, _p(ks, fp), n, d, len(values), _p(ids, i64p), _p(new, u8p)))
-        for i in range(n):
-            self.values[int(ids[i])] = bytes(values[i])
+        with self._set_mu:      # finds are not held up by this lock; see _values_of
+            self._check(self._L.tfp_store_set(self._h, _p(ks, fp), n, d, len(values), _p(ids, i64p), _p(new, u8p)))
+            for i in range(n):
+                self.values[int(ids[i])] = bytes(values[i])
         return ids[:n], new[:n]
+
+    def _values_of(self, ids):
+        """Values of the ids a find returned.  An append publishes its rows to the finds before this host has put the
+        values into the map (finds never wait for an append), so a find can come back with an id whose value is a few
+        microseconds away: only then does the find wait for the StoresSet in progress to finish."""
+        vs = [self.values.get(i) for i in ids]
+        if any(v is None for v in vs):
+            with self._set_mu:
+                pass
+            vs = [self.values.get(i) for i in ids]
+        return vs
 
     def set_device(self, d_ptr: int, n: int, dim: int, values: Sequence[bytes] | None = None):
         """Bulk load rows that already sit in this GPU's HBM (d_ptr = device address of [n, dim] fp32)."""
@@ -170,10 +184,11 @@ class Store:
         ks, d = _rows(keys)
         n = len(ks)
         ids = np.empty(max(n, 1), np.int64)
-        self._check(self._L.tfp_store_delete(self._h, _p(ks, fp), n, d, _p(ids, i64p)))
-        for i in range(n):
-            if ids[i] >= 0:
-                self.values.pop(int(ids[i]), None)
+        with self._set_mu:
+            self._check(self._L.tfp_store_delete(self._h, _p(ks, fp), n, d, _p(ids, i64p)))
+            for i in range(n):
+                if ids[i] >= 0:
+                    self.values.pop(int(ids[i]), None)
         return ids[:n]
 
     # -- StoresGet -----------------------------------------------------------
@@ -184,12 +199,9 @@ class Store:
         order = np.empty(max(n, 1), np.int64)
         nf = C.c_int64()
         self._check(self._L.tfp_store_get(self._h, _p(ks, fp), n, d, _p(ids, i64p), _p(order, i64p), C.byref(nf)))
-        out_k, out_v = [], []
-        for j in range(nf.value):
-            i = int(order[j])
-            out_k.append(ks[i].copy())  # the reference echoes the request's key (store.go:289-291)
-            out_v.append(self.values.get(int(ids[i])))
-        return out_k, out_v
+        hit = [int(order[j]) for j in range(nf.value)]
+        out_k = [ks[i].copy() for i in hit]  # the reference echoes the request's key (store.go:289-291)
+        return out_k, self._values_of([int(ids[i]) for i in hit])
 
     # -- StoresFind ----------------------------------------------------------
     def StoresFind(self, key, topk: int):
@@ -208,7 +220,7 @@ class Store:
         m = n.value
         self.last_path = "normalized" if path.value == 1 else "fallback"
         # outk / sims are this call's own buffers: hand out views, not copies
-        return (list(outk[:m, :len(q)]), [self.values.get(i) for i in ids[:m].tolist()], sims[:m])
+        return (list(outk[:m, :len(q)]), self._values_of(ids[:m].tolist()), sims[:m])
 
     def find_ids(self, key, topk: int):
         """StoresFind without the key echo: (ids, similarities)."""

@@ -269,3 +269,57 @@ def test_snapshot_and_restore(tfp, oracle, tmp_path):
     with pytest.raises(tfp.StoreError):
         b.load(path)                                            # only an empty store can be restored into
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("kind", ["one-gpu", "multi"])
+def test_finds_run_while_keys_are_appended(tfp, oracle, kind):
+    """Appends do not fence the finds ("Finds are fenced ... never on an append"): reader threads keep
+    finding while a writer appends and a deleter compacts; every answer must be the exact top-k of SOME state the store
+    went through -- here checked as: similarities bit-identical to the oracle's score of each returned row, descending,
+    no row twice -- and the final state must equal the oracle's."""
+    import threading
+    from conftest import make_keys, two_devices
+    d, per, batches = 96, 1500, 24
+    K = make_keys(per * batches, d, seed=41, normalized=True)
+    Q = make_keys(8, d, seed=42, normalized=True)
+    s = tfp.Store() if kind == "one-gpu" else tfp.Store(devices=two_devices())
+    o = oracle.OracleStore()
+    vals = [b"%d" % i for i in range(len(K))]
+    s.StoresSet(K[:per], vals[:per]); o.StoresSet(K[:per], vals[:per])
+    stop = threading.Event()
+    errors, finds = [], [0]
+
+    def reader(t):
+        try:
+            while not stop.is_set():
+                q = Q[(t + finds[0]) % len(Q)]
+                ks, vs, sims = s.StoresFind(q, 10)
+                finds[0] += 1
+                assert len(sims) == 10 and (np.diff(sims.astype(np.float64)) <= 0).all()
+                assert len(set(vs)) == 10
+                rows = np.stack(ks)
+                assert np.array_equal(rows, K[[int(v) for v in vs]])             # the key rows are the stored rows of those values
+                assert np.array_equal(oracle.scores_block(rows, q, True), sims)  # and the similarities are exact
+        except Exception as e:      # noqa: BLE001
+            errors.append(repr(e))
+            stop.set()
+
+    ts = [threading.Thread(target=reader, args=(t,)) for t in range(3)]
+    [t.start() for t in ts]
+    try:
+        for b in range(1, batches):
+            lo, hi = b * per, (b + 1) * per
+            s.StoresSet(K[lo:hi], vals[lo:hi]); o.StoresSet(K[lo:hi], vals[lo:hi])
+            if b % 6 == 0:                                                       # a compaction now and then (this one does fence)
+                s.StoresDelete(K[lo - per:lo - per + 200]); o.StoresDelete(K[lo - per:lo - per + 200])
+            if stop.is_set():
+                break
+    finally:
+        stop.set()
+        [t.join() for t in ts]
+    assert not errors, errors[:2]
+    assert finds[0] > 0 and len(s) == len(o)
+    for q in Q[:3]:
+        a, b2 = s.StoresFind(q, 10), o.StoresFind(q, 10)
+        assert np.array_equal(a[2], b2[2]) and a[1] == b2[1]
+    s.close()
