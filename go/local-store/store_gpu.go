@@ -225,7 +225,7 @@ func (s *Store) StoresSet(opts *pb.StoresSetOptions) error {
 
 // valuesOf looks up the values of the ids a find returned.  An id whose value is not in the map yet belongs to a
 // StoresSet that has published its rows but not finished: wait for it (setMu), then look again.
-func (s *Store) valuesOf(ids []int64) [][]byte {
+func (s *Store) valuesOf(ids []int64) ([][]byte, bool) {
 	out := make([][]byte, len(ids))
 	missing := false
 	s.mu.RLock()
@@ -238,13 +238,16 @@ func (s *Store) valuesOf(ids []int64) [][]byte {
 	if missing {
 		s.setMu.Lock()
 		s.setMu.Unlock()
+		missing = false
 		s.mu.RLock()
 		for i, id := range ids {
-			out[i] = s.values[id]
+			v, ok := s.values[id]
+			out[i] = v
+			missing = missing || !ok // still missing: the row was deleted after the find saw it
 		}
 		s.mu.RUnlock()
 	}
-	return out
+	return out, !missing
 }
 
 func (s *Store) StoresDelete(opts *pb.StoresDeleteOptions) error {
@@ -293,7 +296,7 @@ func (s *Store) StoresGet(opts *pb.StoresGetOptions) (pb.StoresGetResult, error)
 	for j := 0; j < int(found); j++ {
 		hit = append(hit, ids[order[j]])
 	}
-	vals := s.valuesOf(hit)
+	vals, _ := s.valuesOf(hit)
 	for j := 0; j < int(found); j++ {
 		res.Keys = append(res.Keys, &pb.StoresKey{Floats: opts.Keys[order[j]].Floats})
 		res.Values = append(res.Values, &pb.StoresValue{Bytes: vals[j]})
@@ -339,7 +342,9 @@ func (s *Store) batcher() {
 	}
 }
 
-func (s *Store) findBatch(topk, dim int, reqs []findReq) {
+func (s *Store) findBatch(topk, dim int, reqs []findReq) { s.findBatchN(topk, dim, reqs, 0) }
+
+func (s *Store) findBatchN(topk, dim int, reqs []findReq, attempt int) {
 	nq := len(reqs)
 	var st C.tfp_stats
 	C.tfp_store_stats(s.h, &st)
@@ -373,7 +378,13 @@ func (s *Store) findBatch(topk, dim int, reqs []findReq) {
 		}
 		n := int(ns[i])
 		res := pb.StoresFindResult{Similarities: sims[i*slots : i*slots+n]}
-		vals := s.valuesOf(ids[i*slots : i*slots+n])
+		vals, complete := s.valuesOf(ids[i*slots : i*slots+n])
+		if !complete && attempt < 3 {
+			// a row deleted between the find and the look-up has no value any more: answer this request from the
+			// state after the delete instead of handing out a row without its value
+			s.findBatchN(topk, dim, []findReq{r}, attempt+1)
+			continue
+		}
 		for j := 0; j < n; j++ {
 			at := i*slots + j
 			res.Keys = append(res.Keys, &pb.StoresKey{Floats: keys[at*dim : (at+1)*dim]})

@@ -215,12 +215,18 @@ class Store:
         ids = np.empty(kk, np.int64)
         sims = np.empty(kk, np.float32)
         outk = np.empty((kk, max(len(q), 1)), np.float32)
-        self._check(self._L.tfp_store_find(self._h, _addr(q), len(q), k if k < 1 else kk, C.byref(n), _addr(ids),
-                                           _addr(sims), _addr(outk), C.byref(path)))
-        m = n.value
+        for attempt in range(4):
+            self._check(self._L.tfp_store_find(self._h, _addr(q), len(q), k if k < 1 else kk, C.byref(n), _addr(ids),
+                                               _addr(sims), _addr(outk), C.byref(path)))
+            m = n.value
+            values = self._values_of(ids[:m].tolist())
+            # A row deleted between the find and the look-up has no value any more: answer from the state after the
+            # delete instead of handing out a row without its value.
+            if all(v is not None for v in values):
+                break
         self.last_path = "normalized" if path.value == 1 else "fallback"
         # outk / sims are this call's own buffers: hand out views, not copies
-        return (list(outk[:m, :len(q)]), self._values_of(ids[:m].tolist()), sims[:m])
+        return (list(outk[:m, :len(q)]), values, sims[:m])
 
     def find_ids(self, key, topk: int):
         """StoresFind without the key echo: (ids, similarities)."""
