@@ -92,6 +92,7 @@ class Store:
         self.devices = list(devices) if devices is not None else [device]
         self.values = {}  # id -> bytes; values never cross the C ABI (store.go:23)
         self._set_mu = threading.Lock()   # held by a StoresSet from its library call until its values are in the map
+        self._every_id_has_a_value = True  # False once rows were loaded without values (set_device(values=None))
         self.last_path = None
 
     # -- plumbing ----------------------------------------------------------
@@ -163,7 +164,7 @@ class Store:
         values into the map (finds never wait for an append), so a find can come back with an id whose value is a few
         microseconds away: only then does the find wait for the StoresSet in progress to finish."""
         vs = [self.values.get(i) for i in ids]
-        if any(v is None for v in vs):
+        if self._every_id_has_a_value and any(v is None for v in vs):
             with self._set_mu:
                 pass
             vs = [self.values.get(i) for i in ids]
@@ -177,6 +178,8 @@ class Store:
         if values is not None:
             for i in range(n):
                 self.values[int(ids[i])] = bytes(values[i])
+        else:
+            self._every_id_has_a_value = False
         return ids[:n], new[:n]
 
     # -- StoresDelete --------------------------------------------------------
@@ -222,7 +225,7 @@ class Store:
             values = self._values_of(ids[:m].tolist())
             # A row deleted between the find and the look-up has no value any more: answer from the state after the
             # delete instead of handing out a row without its value.
-            if all(v is not None for v in values):
+            if not self._every_id_has_a_value or all(v is not None for v in values):
                 break
         self.last_path = "normalized" if path.value == 1 else "fallback"
         # outk / sims are this call's own buffers: hand out views, not copies
@@ -308,6 +311,7 @@ class Store:
                 values[i] = v
         self._check(self._L.tfp_store_load(self._h, os.fsencode(path)))
         self.values = values
+        self._every_id_has_a_value = len(values) == len(self)
 
     def mark_not_normalized(self):
         self._check(self._L.tfp_store_mark_not_normalized(self._h))
