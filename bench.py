@@ -193,7 +193,11 @@ def run_reference(args, rank: int, world: int):
         "impl": "reference", "metric": wl.metric, "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        # same keys as our arm's `config` (same workload, shape and top-k), with this arm's own values where they differ
         "config": {"workload": wl.label, "keys": wl.n_keys, "dim": wl.dim, "topk": wl.topk, "queries_per_step": 1,
+                   "path": "normalized", "rows_per_gpu": None, "finds_in_flight": 1, "warmup_finds": args.warmup,
+                   "exchange": None, "l2": "host memory; %d-row sample per step, scaled by rows" % rows,
+                   "parallelism": "CPU, one thread (the reference serialises every store call, store.go:18)",
                    "sample_rows_per_step": rows},
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": 1, "kind": "port", "sample": sample,
                          "host_cores": os.cpu_count()},
