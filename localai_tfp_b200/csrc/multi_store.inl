@@ -162,6 +162,9 @@ static void multi_close(tfp_store* top) {
         fprintf(stderr, "tfp multi set trace (%lld calls, us per call): wait for the mutation lock %.0f | routing %.0f | slowest shard's gather %.0f | "
                         "all shards %.0f\n", (long long)top->tr_calls, top->tr_us[3] / top->tr_calls, top->tr_us[0] / top->tr_calls,
                 top->tr_us[1] / top->tr_calls, top->tr_us[2] / top->tr_calls);
+    if (tuning().set_trace && top->trd_calls > 0)
+        fprintf(stderr, "tfp multi delete trace (%lld calls, us per call): wait for the mutation lock %.0f | the call %.0f\n",
+                (long long)top->trd_calls, top->trd_us[0] / top->trd_calls, top->trd_us[1] / top->trd_calls);
     for (Worker* w : m->workers) if (w) { w->shutdown(); delete w; }
     for (size_t g = 0; g < m->shards.size(); g++) {
         if (!m->shards[g]) continue;
@@ -365,7 +368,9 @@ static int multi_delete(tfp_store* top, const float* keys, int64_t n, int dim, i
     tfp_multi* m = top->multi;
     if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203
     if (!keys || dim <= 0) return fail(2, "tfp_store_delete: keys is NULL or dim <= 0");
+    const double td_wait = now_us();
     std::lock_guard<std::mutex> mut(top->mut_mu);
+    const double td0 = now_us();
     if (multi_latch(top, dim, "Trying to delete key with length %d when existing length is %d")) return 1;
     if (out_ids) for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     Routed r;
@@ -382,6 +387,9 @@ static int multi_delete(tfp_store* top, const float* keys, int64_t n, int dim, i
     if (out_ids)
         for (int g : r.active)
             for (size_t j = 0; j < r.idx[(size_t)g].size(); j++) out_ids[r.idx[(size_t)g][j]] = ids[(size_t)g][j];
+    top->trd_us[0] += td0 - td_wait;      // wait for the mutation lock
+    top->trd_us[1] += now_us() - td0;     // the call itself
+    top->trd_calls++;
     return 0;
 }
 
@@ -409,14 +417,15 @@ static int multi_get(tfp_store* top, const float* keys, int64_t n, int dim, int6
     for (int g : r.active)
         for (size_t j = 0; j < r.idx[(size_t)g].size(); j++) out_ids[r.idx[(size_t)g][j]] = ids[(size_t)g][j];
     // found keys in the reference's sorted-key order (store.go:269,285-301); equal keys keep request order
-    std::vector<int64_t> order;
-    sorted_order(keys, n, dim, order);
-    int64_t found = 0;
-    for (int64_t oi = 0; oi < n; oi++) {
-        const int64_t i = order[(size_t)oi];
-        if (out_ids[i] >= 0) { if (out_order) out_order[found] = i; found++; }
+    std::vector<int64_t> hit;
+    for (int64_t i = 0; i < n; i++) if (out_ids[i] >= 0) hit.push_back(i);
+    if (out_order) {
+        std::stable_sort(hit.begin(), hit.end(), [&](int64_t a, int64_t b) {
+            return cmp_rows(keys + (size_t)a * dim, keys + (size_t)b * dim, dim) < 0;
+        });
+        for (size_t j = 0; j < hit.size(); j++) out_order[j] = hit[j];
     }
-    if (out_n_found) *out_n_found = found;
+    if (out_n_found) *out_n_found = (int64_t)hit.size();
     return 0;
 }
 

@@ -328,6 +328,8 @@ struct tfp_store {
     int max_smem = 0;
     double tr_us[6] = {0, 0, 0, 0, 0, 0};   // TFP_SET_TRACE: hash + D2H, index probe, verify, grow / fence, scatter + sync, publish
     int64_t tr_calls = 0;
+    double trd_us[5] = {0, 0, 0, 0, 0};     // ... of StoresDelete: sort + look-up, wait for the lock, wait for the finds, host index, move + sync
+    int64_t trd_calls = 0;
 };
 
 struct tfp_find_ctx {
@@ -543,6 +545,10 @@ static void store_close(tfp_store* s) {
                         "scatter + sync %.0f | publish %.0f\n", s->device, (long long)s->tr_calls, s->tr_us[0] / s->tr_calls,
                 s->tr_us[1] / s->tr_calls, s->tr_us[2] / s->tr_calls, s->tr_us[3] / s->tr_calls, s->tr_us[4] / s->tr_calls,
                 s->tr_us[5] / s->tr_calls);
+    if (tuning().set_trace && s->trd_calls > 0)
+        fprintf(stderr, "tfp delete trace (device %d, %lld calls, us per call): sort + look-up %.0f | wait for the store lock %.0f | wait for the finds in flight %.0f | "
+                        "host index %.0f | move + sync %.0f\n", s->device, (long long)s->trd_calls, s->trd_us[0] / s->trd_calls, s->trd_us[1] / s->trd_calls,
+                s->trd_us[2] / s->trd_calls, s->trd_us[3] / s->trd_calls, s->trd_us[4] / s->trd_calls);
     cudaSetDevice(s->device);
     cudaDeviceSynchronize();
     std::vector<tfp_find_ctx*> ctxs = s->ctxs;
@@ -609,15 +615,22 @@ struct Lookup {
     std::vector<int64_t> match;     // stored slot confirmed equal and not yet consumed, or -1
 };
 
+static void sorted_order(const float* keys, int64_t n, int dim, std::vector<int64_t>& order);
+
 // Hash the staged rows on the device, probe the host index, confirm candidates on
-// the device.  `order` gives the sequence in which rows claim stored slots (each
-// stored slot is claimed at most once per call, like the reference's walks over
-// a sorted batch: store.go:154-189, :225-238, :285-301).
+// the device.  Rows claim stored slots in a fixed sequence (each stored slot is
+// claimed at most once per call, like the reference's walks over a sorted batch:
+// store.go:154-189, :225-238, :285-301).  That sequence only matters when the request
+// holds the same key more than once, so the reference's sorted order is worked out
+// -- from `host_keys`, the request's rows in host memory -- only when two rows share a
+// hash; otherwise rows claim in request order.  (Sorting every request cost more than
+// everything else a StoresDelete does: 35 ms for 6.5k keys of 1536 floats, each
+// comparison two cache misses.)
 static inline double now_us() {
     return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::vector<int64_t>& order, Lookup& L) {
+static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const float* host_keys, Lookup& L) {
     const int dim = s->dim;
     const double t0 = now_us();
     if (s->st_hash.reserve((size_t)n * 8) || s->st_knorm.reserve((size_t)n * 8) || s->st_isnorm.reserve((size_t)n)) return -1;
@@ -660,6 +673,12 @@ static int lookup_rows(tfp_store* s, const float* d_rows, int64_t n, const std::
     }
     s->tr_us[2] += now_us() - t2;
     L.match.assign((size_t)n, -1);
+    std::vector<int64_t> order;
+    if (host_keys && n > 1) {
+        std::vector<uint64_t> hs(L.hash);
+        std::sort(hs.begin(), hs.end());
+        if (std::adjacent_find(hs.begin(), hs.end()) != hs.end()) sorted_order(host_keys, n, dim, order);
+    }
     std::unordered_set<uint32_t> claimed;
     for (int64_t oi = 0; oi < n; oi++) {
         int64_t i = order.empty() ? oi : order[(size_t)oi];
@@ -691,8 +710,7 @@ static int stage_rows(tfp_store* s, const float* keys, int64_t n, int dim, const
 static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_ids, uint8_t* out_was_new) {
     const int dim = s->dim;
     Lookup L;
-    std::vector<int64_t> order;
-    if (lookup_rows(s, d_rows, n, order, L)) return -1;
+    if (lookup_rows(s, d_rows, n, nullptr, L)) return -1;
     bool all_norm = true;                                  // sticky flag (store.go:125-135)
     for (int64_t i = 0; i < n; i++) if (!L.is_norm[(size_t)i]) { all_norm = false; break; }
 
@@ -829,22 +847,22 @@ static int store_get(tfp_store* s, const float* keys, int64_t n, int dim, int64_
     std::lock_guard<std::mutex> mut(s->mut_mu);      // uses the mutation staging buffers and the host index; finds go on
     if (latch_dim(s, dim, "Try to get a key with length %d when existing length is %d")) return 1;   // :275-280
     if (set_device(s)) return -1;
-    std::vector<int64_t> order;
-    sorted_order(keys, n, dim, order);
     for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     int64_t found = 0;
     if (s->n > 0) {
         const float* d_rows = nullptr;
         if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
         Lookup L;
-        if (lookup_rows(s, d_rows, n, order, L)) return -1;
-        for (int64_t oi = 0; oi < n; oi++) {
-            int64_t i = order[(size_t)oi];
-            if (L.match[(size_t)i] >= 0) {
-                out_ids[i] = s->slot_id[(size_t)L.match[(size_t)i]];
-                if (out_order) out_order[found] = i;
-                found++;
-            }
+        if (lookup_rows(s, d_rows, n, keys, L)) return -1;
+        std::vector<int64_t> hit;
+        for (int64_t i = 0; i < n; i++)
+            if (L.match[(size_t)i] >= 0) { out_ids[i] = s->slot_id[(size_t)L.match[(size_t)i]]; hit.push_back(i); }
+        found = (int64_t)hit.size();
+        if (out_order) {   // the found keys in the reference's sorted-key order (store.go:269,285-301); equal keys keep request order
+            std::stable_sort(hit.begin(), hit.end(), [&](int64_t a, int64_t b) {
+                return cmp_rows(keys + (size_t)a * dim, keys + (size_t)b * dim, dim) < 0;
+            });
+            for (int64_t j = 0; j < found; j++) out_order[j] = hit[(size_t)j];
         }
     }
     if (out_n_found) *out_n_found = found;
@@ -860,12 +878,12 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
     if (out_ids) for (int64_t i = 0; i < n; i++) out_ids[i] = -1;
     if (s->n == 0) return 0;
     if (set_device(s)) return -1;
-    std::vector<int64_t> order;
-    sorted_order(keys, n, dim, order);
+    const double td0 = now_us();
+    const double saved_set[3] = {s->tr_us[0], s->tr_us[1], s->tr_us[2]};   // (the look-up below also feeds the set trace: undo that)
     const float* d_rows = nullptr;
     if (stage_rows(s, keys, n, dim, &d_rows)) return -1;
     Lookup L;
-    if (lookup_rows(s, d_rows, n, order, L)) return -1;
+    if (lookup_rows(s, d_rows, n, keys, L)) return -1;
     std::vector<uint32_t> holes;
     for (int64_t i = 0; i < n; i++) {
         if (L.match[(size_t)i] >= 0) {
@@ -874,10 +892,14 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
             if (out_ids) out_ids[i] = s->slot_id[slot];
         }
     }
+    s->tr_us[0] = saved_set[0]; s->tr_us[1] = saved_set[1]; s->tr_us[2] = saved_set[2];
     if (holes.empty()) return 0;
     // compaction moves rows that running scans read, and shrinks the row count: fence the finds (the look-up above did not)
+    const double td1 = now_us();
     std::unique_lock<RwMutex> lk(s->rw);
+    const double td2 = now_us();
     if (quiesce_finds(s)) return -1;
+    const double td3 = now_us();
     const int64_t new_n = s->n - (int64_t)holes.size();
     std::vector<uint8_t> dead((size_t)(s->n - new_n), 0);   // marks deleted slots in the tail [new_n, n)
     for (uint32_t h : holes) {
@@ -897,6 +919,7 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
         s->slot_id[h] = s->slot_id[(size_t)t];
         t++;
     }
+    const double td4 = now_us();
     if (!src.empty()) {
         size_t m = src.size();
         if (s->st_src.reserve(m * 4) || s->st_dst.reserve(m * 4)) return -1;
@@ -911,6 +934,8 @@ static int store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int
     s->slot_hash.resize((size_t)new_n);
     s->slot_id.resize((size_t)new_n);
     s->n = new_n;
+    s->trd_us[0] += td1 - td0; s->trd_us[1] += td2 - td1; s->trd_us[2] += td3 - td2; s->trd_us[3] += td4 - td3; s->trd_us[4] += now_us() - td4;
+    s->trd_calls++;
     return 0;
 }
 
