@@ -15,12 +15,21 @@ pytestmark = pytest.mark.gpu
 f32 = np.float32
 
 
-@pytest.fixture()
-def client(tfp):
+@pytest.fixture(params=["one-gpu", "TFP_DEVICES"])
+def client(request, tfp):
+    """The backend process the way LocalAI's loader starts it: `--addr` and the environment, nothing else.  Every case
+    runs twice: against the default one-GPU store, and with TFP_DEVICES naming two devices (the second GPU when the box
+    has one, else GPU 0 twice), i.e. ONE logical store over two shards inside the one backend process."""
+    import os
+    from conftest import two_devices
     from localai_tfp_b200.server import Client
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     addr = f"127.0.0.1:{port}"
-    proc = subprocess.Popen([sys.executable, "-m", "localai_tfp_b200.server", "--addr", addr])
+    env = dict(os.environ)
+    env.pop("TFP_DEVICES", None)
+    if request.param == "TFP_DEVICES":
+        env["TFP_DEVICES"] = ",".join(str(d) for d in two_devices())
+    proc = subprocess.Popen([sys.executable, "-m", "localai_tfp_b200.server", "--addr", addr], env=env)
     c = Client(addr)
     try:
         for attempt in range(60):                       # the loader polls Health up to 20 x 2 s
