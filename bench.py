@@ -21,7 +21,9 @@ Prints ONE JSON line (rank 0).
              C2 store) that must not hold a better row than the k-th returned one.  A mismatch fails the run.
   also       the same measurement (ms, roofline, parity) on the north star's target shape (10M x 1024,
              top-10, batch 1), on C3 (10M x 1024, 256 queries, top-100, tensor cores) and, on 8 GPUs,
-             on C4 (100M x 384).  `--also none` skips them.
+             on C4 (100M x 384); on one GPU C1 (10k x 384 through the gRPC backend process, microseconds
+             per StoresFind); on several GPUs `inproc`: the same store as ONE process over all N GPUs
+             (tfp_store_open_devices), which is also where `e2e` comes from there.  `--also none` skips them.
   cpu_baseline  the CPU oracle (a port of the reference's Go code) timed on this box (N = 1).
 `--impl reference` times that CPU port as its own arm.
 """
@@ -622,6 +624,101 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
     return out
 
 
+def measure_c1(env):
+    """C1 (BASELINE.json configs[0]): 10k keys x 384-d, single-query top-10 THROUGH gRPC -- the reference's own
+    CPU-runnable case.  The backend process is spawned the way LocalAI's loader spawns `local-store` (binary + --addr),
+    loaded over the wire, and timed from the client: microseconds per StoresFind in the reference's wire format, with the
+    NoKeys extension, and -- in this process -- through the C ABI and on the device alone.  Every answer is checked
+    against the oracle's scan of the whole store."""
+    import socket
+    import subprocess
+    import grpc
+    from oracle import oracle as orc
+    from localai_tfp_b200 import Store
+    from localai_tfp_b200.server import Client
+    n, d, k, reps = 10_000, 384, 10, 300
+    rng = np.random.default_rng(0x5EED0001)
+    K = rng.standard_normal((n, d)).astype(np.float32)
+    K /= np.sqrt((K.astype(np.float64) ** 2).sum(axis=1, keepdims=True)).astype(np.float32)
+    Q = rng.standard_normal((16, d)).astype(np.float32)
+    Q /= np.sqrt((Q.astype(np.float64) ** 2).sum(axis=1, keepdims=True)).astype(np.float32)
+    vals = [b"%d" % i for i in range(n)]
+    want = [orc.scan_block(K, q, k, True) for q in Q]
+
+    def per_call(fn):
+        for i in range(20):
+            fn(i)
+        t0 = time.perf_counter()
+        for i in range(reps):
+            fn(i)
+        return (time.perf_counter() - t0) / reps * 1e6
+
+    problems = []
+
+    def check(tag, i, vs, sims):
+        rows, osims = want[i % 16]
+        if not np.array_equal(np.asarray(sims, np.float32), osims) or [int(v) for v in vs] != [int(r) for r in rows]:
+            problems.append(f"{tag}: query {i % 16} differs from the oracle")
+
+    st = Store(device=env["local_rank"])
+    st.StoresSet(K, vals)
+    c = st.find_context(); c.upload(Q); c.sync()
+
+    def dev_only(i):
+        c.launch(i % 16, 1, k); c.sync()
+    us_dev = per_call(dev_only)
+    us_abi = per_call(lambda i: st.StoresFind(Q[i % 16], k))
+    for i in range(16):
+        ks, vs, sims = st.StoresFind(Q[i], k)
+        check("C ABI", i, vs, sims)
+    c.close(); st.close()
+
+    sock = socket.socket(); sock.bind(("127.0.0.1", 0)); port = sock.getsockname()[1]; sock.close()
+    addr = f"127.0.0.1:{port}"
+    proc = subprocess.Popen([sys.executable, "-m", "localai_tfp_b200.server", "--addr", addr, "--device", str(env["local_rank"])],
+                            cwd=ROOT)
+    cl = Client(addr)
+    try:
+        for _ in range(120):                      # the loader polls Health (pkg/model/initializers.go:375-387)
+            try:
+                if cl.health() == b"OK":
+                    break
+            except grpc.RpcError:
+                time.sleep(0.25)
+        else:
+            raise RuntimeError("the backend process did not become healthy")
+        for lo in range(0, n, 2500):
+            cl.set(K[lo:lo + 2500], vals[lo:lo + 2500])
+        us_grpc = per_call(lambda i: cl.find(Q[i % 16], k))
+        us_lean = per_call(lambda i: cl.find(Q[i % 16], k, no_keys=True))
+        us_health = per_call(lambda i: cl.health())
+        for i in range(16):
+            ks, vs, sims = cl.find(Q[i], k)
+            check("gRPC", i, vs, sims)
+            if not all(np.array_equal(a, K[int(v)]) for a, v in zip(ks, vs)):
+                problems.append(f"gRPC: query {i} echoed a key that is not the stored row")
+    finally:
+        cl.close()
+        proc.terminate()
+        try:
+            proc.wait(timeout=20)
+        except Exception:
+            proc.kill()
+    t0 = time.perf_counter()
+    for i in range(4):
+        orc.scan_block(K, Q[i], k, True)
+    us_cpu = (time.perf_counter() - t0) / 4 * 1e6
+    out = {"workload": "C1 (BASELINE.json configs[0]): 10k keys x 384-d fp32, single query top-10 via gRPC",
+           "unit": "microseconds per StoresFind, one caller",
+           "grpc_reference_wire_format": us_grpc, "grpc_nokeys_extension": us_lean, "grpc_empty_health_rpc": us_health,
+           "c_abi_host_buffers_with_key_rows": us_abi, "device_launch_plus_sync": us_dev,
+           "cpu_port_scan_only_no_rpc": us_cpu, "value": 1e6 / us_grpc, "value_unit": "queries/s through gRPC",
+           "parity": {"ok": not problems, "checked_queries": 32, "rule": "similarities and ids equal to the oracle's scan of the whole store"}}
+    if problems:
+        out["parity"]["problems"] = problems[:6]
+    return out
+
+
 def measure_inproc(env, wl: Workload, args):
     """The same store as ONE logical store over all N GPUs inside ONE process (tfp_store_open_devices) -- the shape
     in which LocalAI's loader runs a backend (one process, pkg/model/process.go:94-124).  Rank 0 drives it through
@@ -745,6 +842,11 @@ def run_ours(args, rank: int, local_rank: int, world: int):
         sh.close()
     cache.clear()
     torch.cuda.empty_cache()
+    if world == 1 and args.also == "auto" and args.workload == "c2":
+        try:
+            also["c1"] = measure_c1(env)
+        except Exception as e:
+            also["c1"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     if world > 1 and args.inproc and args.workload == "c2" and not any("error" in v for v in also.values()):
         # The other ranks wait on the CPU (gloo): an NCCL barrier would leave a kernel spinning on their GPUs, and a GPU
         # time-slices between processes -- rank 0's kernels there would get every other millisecond.

@@ -356,7 +356,7 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     // the sticky flag (store.go:27,126-127) belongs to the whole store: all shards leave the normalised path together
     bool all_norm = true;
     for (tfp_store* sh : m->shards) { std::shared_lock<RwMutex> l2(sh->rw); all_norm = all_norm && sh->normalized; }
-    if (!all_norm) {
+    if (!all_norm && top->normalized) {   // (only the call that flips the flag pays for the exclusive lock: it waits for every find in flight)
         std::unique_lock<RwMutex> lk(top->rw);
         top->normalized = false;
         for (tfp_store* sh : m->shards) store_mark_not_normalized(sh);
