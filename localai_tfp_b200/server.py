@@ -8,7 +8,9 @@ Stand-in for the Go binary of go/local-store/ (the build image has no Go toolcha
 gRPC shell (pkg/grpc/server.go:45-55, 185-240): Health -> Reply{message: "OK"}, LoadModel ->
 Result{success: true}, StoresSet/StoresDelete -> Result{"Set key"/"Deleted key", true} or an error
 whose text is the store's, StoresGet/StoresFind -> their result messages, errors as gRPC UNKNOWN.
-The reference serialises RPCs with a mutex (base.SingleThread); so does this server.
+The reference serialises every RPC with one mutex (base.SingleThread).  Here, like the Go host
+(base.Base, no server mutex), only the mutations are serialised among themselves: finds are drained by the
+batcher and run beside a StoresSet -- the library appends without stopping them.
 """
 from __future__ import annotations
 
@@ -68,37 +70,37 @@ class _FindBatcher:
                 self._serve(topk, group)
 
     def _serve(self, topk_nokeys, group):
+        """One group of finds (same top-k).  No server mutex: finds run beside the mutations."""
         b = self.backend
         topk, no_keys = topk_nokeys
-        with b.lock:
-            b.busy = True
-            try:
-                dims = {len(g[0]) for g in group}
-                if len(group) == 1 or len(dims) != 1 or topk < 1 or b.store.key_len != next(iter(dims)) or len(b.store) == 0:
-                    for key, _, fut in group:        # singles and anything that will error: the plain call, per request
-                        try:
-                            fut.set_result(b.find_one(key, topk, no_keys))
-                        except Exception as e:
-                            fut.set_exception(e)
-                    return
-                import numpy as np
-                qs = np.stack([g[0] for g in group]).astype(np.float32)
-                if no_keys:
-                    res, keys = b.store.find_batch(qs, topk), None
-                else:
-                    res, keys = b.store.find_batch(qs, topk, with_keys=True)
-                self.batches += 1
-                self.largest = max(self.largest, len(group))
-                for i, (key, k, fut) in enumerate(group):
-                    ids, sims = res[i]
-                    fut.set_result(([] if no_keys else [keys[i, j, :].copy() for j in range(len(ids))],
-                                    b.store._values_of([int(x) for x in ids]), sims))
-            except Exception as e:
-                for _, _, fut in group:
-                    if not fut.done():
+        b.busy = True
+        try:
+            dims = {len(g[0]) for g in group}
+            if len(group) == 1 or len(dims) != 1 or topk < 1 or b.store.key_len != next(iter(dims)) or len(b.store) == 0:
+                for key, _, fut in group:        # singles and anything that will error: the plain call, per request
+                    try:
+                        fut.set_result(b.find_one(key, topk, no_keys))
+                    except Exception as e:
                         fut.set_exception(e)
-            finally:
-                b.busy = False
+                return
+            import numpy as np
+            qs = np.stack([g[0] for g in group]).astype(np.float32)
+            if no_keys:
+                res, keys = b.store.find_batch(qs, topk), None
+            else:
+                res, keys = b.store.find_batch(qs, topk, with_keys=True)
+            self.batches += 1
+            self.largest = max(self.largest, len(group))
+            for i, (key, k, fut) in enumerate(group):
+                ids, sims = res[i]
+                fut.set_result(([] if no_keys else [keys[i, j, :].copy() for j in range(len(ids))],
+                                b.store._values_of([int(x) for x in ids]), sims))
+        except Exception as e:
+            for _, _, fut in group:
+                if not fut.done():
+                    fut.set_exception(e)
+        finally:
+            b.busy = False
 
 
 def devices_from_env(default_device: int = 0):
@@ -134,7 +136,7 @@ class Backend:
                 print(f"local-store: snapshot {snapshot} not restored ({e}); starting empty", file=sys.stderr, flush=True)
                 self.store.close()
                 self.store = self._open()
-        self.lock = threading.Lock()          # base.SingleThread (pkg/grpc/base/singlethread.go:13-29)
+        self.lock = threading.Lock()          # mutations (and un-batched finds) one at a time; batched finds do not take it
         self.busy = False
 
     # -- lifecycle ---------------------------------------------------------------------------
