@@ -36,8 +36,20 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
+    # Several processes may get here at once (the ranks of a multi-GPU run on a box whose copy of the library is
+    # older than a source file): one builds, the others wait for it and then find the library up to date.
+    import fcntl
+    with open(os.path.join(HERE, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and not needs_build():
+            return LIB
+        return _build_locked(verbose)
+
+
+def _build_locked(verbose: bool) -> str:
+    tmp = LIB + ".tmp.%d" % os.getpid()
     cmd = [
-        nvcc_path(), "-shared", "-o", LIB, *SOURCES,
+        nvcc_path(), "-shared", "-o", tmp, *SOURCES,
         "-gencode", "arch=compute_100a,code=sm_100a",
         "-O3", "-std=c++17", "-lineinfo",
         "-Xcompiler", "-fPIC,-O3,-ffp-contract=off,-Wall,-Wno-unknown-pragmas",
@@ -49,7 +61,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if verbose or res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode != 0:
+        if os.path.exists(tmp):
+            os.remove(tmp)
         raise RuntimeError("nvcc failed building libtfpstore.so")
+    os.replace(tmp, LIB)      # a process that has the old library mapped keeps its inode; nobody sees a half-written file
     return LIB
 
 

@@ -11,17 +11,19 @@
 // Two filters (template TERMS):
 //   TERMS = 1  one TF32 MMA per K-step on the raw fp32 operands.  TF32 keeps 10 mantissa bits, so
 //              each operand is off by < 2^-10 relative and |approx - exact| <= eps with
-//              eps = (2^-9 + D 2^-23) |q| |k| (Cauchy-Schwarz; the D term covers the reference's
-//              own fp32 rounding).  Every row within 2 eps of the k-th best approximate score is
-//              re-scored: a row outside that band provably cannot be in the exact top-k.  The scan
-//              is then HBM-bound like the single-query path (one MMA per 12 KB of operands).
+//              eps = (2^-9 + 2^-20 + 2 D 2^-23) |q| |k|: the operand term is a bound (Cauchy-Schwarz), the
+//              D term covers the tensor core's own fp32 accumulation and the reference's fp32 rounding
+//              with margin (worst case over what is known of that adder; see tfp_store.cu mma_pass_launch).
+//              Every row within 2 eps of the k-th best approximate score is re-scored: a row outside that
+//              band cannot be in the exact top-k while the bound holds.
 //   TERMS = 3  each operand split into TF32 hi + lo (a = hi + lo to 2^-22), S ~= hi.hi + hi.lo +
 //              lo.hi, error ~1e-6; the best k+48 candidates are re-scored and the query is re-run on
 //              the exact kernel if the first row not re-scored is too close to call.  3x the MMAs
 //              and twice the query traffic: shared-memory-bandwidth bound at half the tensor peak.
-// Per query, candidates are the rows whose approximate score clears a proven lower bound of the
-// 148th best score (minus 2 eps).  A query whose candidate list overflowed or came out short is
-// flagged and re-run by the host on the exact scan kernel -- still on the GPU.
+// Per query, candidates are the rows whose approximate score clears a lower bound (valid by counting) of the
+// need-th best score (minus 2 eps).  A query whose candidate list overflowed, came out short, or whose band holds
+// more rows than may be re-scored is flagged: the host sends the flagged queries of a batch through one 3xTF32
+// pass together, and what that cannot settle through the exact scan kernel, 8 per pass -- all still on the GPU.
 //
 // Kernel anatomy (one persistent CTA per SM, 12 warps):
 //   warp 0      TMA producer: per 16-column chunk one key box [128 rows x 64 B] (HBM, read once)
@@ -708,7 +710,7 @@ mma_finalize_kernel(const FinalizeParams p) {
     if (TERMS == 3) cut = want >= 1 ? s_prefix : 0u;
     else if (n > lim) {
         // every row whose approximate score is within 2 eps of the k-th best approximate score:
-        // a row below that band is provably below the k-th exact score
+        // a row below that band is below the k-th exact score (as long as eps bounds the filter's error)
         cut = score_to_order(order_to_score(s_prefix) - 2.0f * p.eps[q]);
     }
     for (int i = tid; i < n; i += kFinThreads) {

@@ -148,7 +148,7 @@ struct Tuning {
     bool disable_lbest = false;
     int mma_min_queries = 3;       // batches at least this large go to the tensor-core path (measured break-even: 531 us per batch vs 896 us for 2 + 1 exact scans on 1M x 768)
     int64_t mma_min_rows = 65536;
-    int mma_terms = 1;             // 1 = single-TF32 filter with a proven error band, 3 = 3xTF32 split
+    int mma_terms = 1;             // 1 = single-TF32 filter + re-score of its error band (3xTF32 as the second pass), 3 = 3xTF32 split first
     bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)
     int mma_debug = 0;             // development timing only (results wrong): 1 no epilogue hits, 2 no MMAs
     bool mma_trace = false;        // print the tensor-core launch shape
