@@ -130,19 +130,17 @@ struct tfp_multi {
 template <class F>
 static int run_shards(tfp_multi* m, const std::vector<int>& which, F&& fn) {
     if (which.empty()) return 0;
+    // `which` is ascending, so only which[0] can be shard 0 (which has no worker: it runs here, like any first shard)
     std::vector<Job> jobs(which.size());
     for (size_t i = 1; i < which.size(); i++) {
         const int g = which[i];
         jobs[i].fn = [&fn, g]() -> int { return fn(g); };
-        if (g >= 1) m->workers[(size_t)g]->post(&jobs[i]);
+        m->workers[(size_t)g]->post(&jobs[i]);
     }
-    int rc = 0;
-    std::string err;
-    const int rc0 = fn(which[0]);
-    if (rc0) { rc = rc0; err = g_err; }
+    int rc = fn(which[0]);
+    std::string err = rc ? g_err : std::string();
     for (size_t i = 1; i < which.size(); i++) {
-        if (which[i] < 1) { jobs[i].rc = jobs[i].fn(); if (jobs[i].rc) jobs[i].err = g_err; }   // (shard 0 is always first; kept for safety)
-        else job_wait(&jobs[i]);
+        job_wait(&jobs[i]);
         if (jobs[i].rc && !rc) { rc = jobs[i].rc; err = jobs[i].err; }
     }
     if (rc) g_err = err;
