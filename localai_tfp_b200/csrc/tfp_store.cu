@@ -309,6 +309,7 @@ struct tfp_store {
     bool normalized = true;    // store.go:27,43 keysAreNormalized (sticky)
     int64_t n = 0, cap = 0, cap_hint = 0;
     int64_t next_id = 0;
+    int64_t hbm_mapped = 0;    // bytes of HBM mapped behind the three arrays (published with cap)
     VmmArray vm_keys, vm_ids, vm_knorm;   // backing of the three arrays when virtual memory management is available
     float* d_keys = nullptr;
     int64_t* d_ids = nullptr;
@@ -408,25 +409,31 @@ static int encode_tmap(tfp_store* s) {
     return 0;
 }
 
-// Grow the HBM arrays to hold `rows` rows (dim must be latched).
-static int ensure_capacity(tfp_store* s, int64_t rows) {
+// Grow the HBM arrays to hold `rows` rows (dim must be latched).  Caller holds mut_mu.
+// publish: the store lock to take -- exclusively, if the caller does not hold it yet -- for the instant in which what
+// finds read when they launch (capacity, tensor maps, the first time the base addresses) changes.  With virtual
+// memory management the slow part, creating and mapping physical memory (tens of milliseconds for a multi-GB step: the
+// driver zeroes it), happens BEFORE that and stops no find: running kernels keep their own copy of the tensor map and
+// never touch the new pages.
+static int ensure_capacity(tfp_store* s, int64_t rows, std::unique_lock<RwMutex>* publish = nullptr) {
     if (rows <= s->cap) return 0;
     if (rows > 0xFFFFFFF0ll) return fail(-3, "store shard would exceed 2^32 rows");
     const size_t row_bytes = (size_t)s->dim * 4;
+    auto lock_for_publish = [&]() { if (publish && !publish->owns_lock()) publish->lock(); };
     if (vmm_api()) {
         // virtual memory: map more physical memory behind fixed addresses; nothing is copied
-        if (!s->vm_keys.active()) {
+        const bool first = !s->vm_keys.active();
+        if (first) {
             size_t free_b = 0, total_b = 0;
             CU_OK(cudaMemGetInfo(&free_b, &total_b));
             int64_t max_rows = (int64_t)std::min<size_t>((size_t)0xFFFFFFF0ull, total_b / row_bytes + 1);
             if (s->vm_keys.reserve(s->device, (size_t)max_rows * row_bytes + 4096) ||
                 s->vm_ids.reserve(s->device, (size_t)max_rows * 8) || s->vm_knorm.reserve(s->device, (size_t)max_rows * 8))
                 return -6;
-            s->d_keys = (float*)s->vm_keys.base;
-            s->d_ids = (int64_t*)s->vm_ids.base;
-            s->d_knorm = (double*)s->vm_knorm.base;
         }
-        int64_t ncap = std::max<int64_t>({rows, s->cap + s->cap / 4, s->cap_hint, (int64_t)1024});
+        // a quarter more than there is, but no more than 2 GiB of keys at a time: the call that grows pays for the step
+        const int64_t step = std::min<int64_t>(s->cap / 4, (int64_t)(((size_t)2 << 30) / row_bytes));
+        int64_t ncap = std::max<int64_t>({rows, s->cap + step, s->cap_hint, (int64_t)1024});
         ncap = std::min<int64_t>(ncap, 0xFFFFFFF0ll);
         if (s->vm_keys.grow((size_t)ncap * row_bytes + 256) || s->vm_ids.grow((size_t)ncap * 8) || s->vm_knorm.grow((size_t)ncap * 8)) {
             // the generous step did not fit: take exactly what is needed
@@ -436,9 +443,17 @@ static int ensure_capacity(tfp_store* s, int64_t rows) {
         }
         // whatever the mapping granularity added is usable too
         int64_t by_map = (int64_t)std::min({(s->vm_keys.mapped - 256) / row_bytes, s->vm_ids.mapped / 8, s->vm_knorm.mapped / 8});
+        lock_for_publish();
+        if (first) {
+            s->d_keys = (float*)s->vm_keys.base;
+            s->d_ids = (int64_t*)s->vm_ids.base;
+            s->d_knorm = (double*)s->vm_knorm.base;
+        }
         s->cap = std::min<int64_t>(std::max(ncap, by_map), 0xFFFFFFF0ll);
+        s->hbm_mapped = (int64_t)(s->vm_keys.mapped + s->vm_ids.mapped + s->vm_knorm.mapped);
         return encode_tmap(s);
     }
+    lock_for_publish();
     // no virtual memory management: reallocate and copy
     int64_t ncap = std::max<int64_t>({rows, s->cap * 2, s->cap_hint, (int64_t)1024});
     float* nk = nullptr; int64_t* ni = nullptr; double* nn = nullptr;
@@ -572,8 +587,7 @@ static int store_stats(tfp_store* s, tfp_stats* out) {
     std::shared_lock<RwMutex> lk(s->rw);
     out->rows = s->n;
     out->capacity_rows = s->cap;
-    out->hbm_bytes = s->vm_keys.active() ? (int64_t)(s->vm_keys.mapped + s->vm_ids.mapped + s->vm_knorm.mapped)
-                                         : s->cap * ((int64_t)(s->dim > 0 ? s->dim : 0) * 4 + 16);
+    out->hbm_bytes = s->vm_keys.active() ? s->hbm_mapped : s->cap * ((int64_t)(s->dim > 0 ? s->dim : 0) * 4 + 16);
     out->dim = s->dim;
     out->keys_are_normalized = s->normalized ? 1 : 0;
     out->device = s->device;
@@ -740,10 +754,9 @@ static int set_impl(tfp_store* s, const float* d_rows, int64_t n, int64_t* out_i
         if (quiesce_finds(s)) return -1;
     }
     if (s->n + n_new > s->cap) {
-        // growing changes what finds read when they launch (capacity, tensor maps, the first time the base addresses)
+        // growing changes what finds read when they launch; ensure_capacity takes the lock only to publish that
         std::unique_lock<RwMutex> grow(s->rw, std::defer_lock);
-        if (!fence.owns_lock()) grow.lock();
-        if (ensure_capacity(s, s->n + n_new)) return -1;
+        if (ensure_capacity(s, s->n + n_new, fence.owns_lock() ? nullptr : &grow)) return -1;
     }
     const double t4 = now_us();
     s->tr_us[3] += t4 - t3;
