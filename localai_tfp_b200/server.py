@@ -45,6 +45,7 @@ class _FindBatcher:
         self.backend = backend
         self.max_batch = max_batch
         self.q = queue.Queue()
+        self.gate = threading.Lock()      # held while a backlog is collected and served (a test holds it to let one pile up)
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
         self.batches = 0
@@ -58,16 +59,17 @@ class _FindBatcher:
     def _run(self):
         while True:
             items = [self.q.get()]
-            while len(items) < self.max_batch:
-                try:
-                    items.append(self.q.get_nowait())
-                except queue.Empty:
-                    break
-            by_k = {}
-            for it in items:
-                by_k.setdefault(it[1], []).append(it)
-            for topk, group in by_k.items():
-                self._serve(topk, group)
+            with self.gate:
+                while len(items) < self.max_batch:
+                    try:
+                        items.append(self.q.get_nowait())
+                    except queue.Empty:
+                        break
+                by_k = {}
+                for it in items:
+                    by_k.setdefault(it[1], []).append(it)
+                for topk, group in by_k.items():
+                    self._serve(topk, group)
 
     def _serve(self, topk_nokeys, group):
         """One group of finds (same top-k).  No server mutex: finds run beside the mutations."""

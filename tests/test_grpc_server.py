@@ -169,14 +169,14 @@ def test_concurrent_finds_are_batched_onto_the_tensor_cores(tfp, oracle):
                 gate.wait()
                 got[i] = clients[i].find(Q[i], 10)
             ts = [threading.Thread(target=work, args=(i,)) for i in range(len(Q))]
-            # hold the store briefly so that the requests pile up behind it, as they do behind a busy GPU:
-            # the batcher must then take the backlog as one batch
-            backend.lock.acquire()
+            # hold the batcher briefly so that the requests pile up behind it, as they do behind a busy GPU:
+            # it must then take the backlog as one batch
+            backend.batcher.gate.acquire()
             [t.start() for t in ts]
             deadline = time.time() + 10
             while backend.batcher.q.qsize() < len(Q) - 8 and time.time() < deadline:
                 time.sleep(0.01)
-            backend.lock.release()
+            backend.batcher.gate.release()
             [t.join() for t in ts]
             for i in range(len(Q)):
                 ks, vs, sims = got[i]
