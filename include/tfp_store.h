@@ -70,8 +70,10 @@ void tfp_store_close(tfp_store* s);
  * without it the per-shard answers are merged on the host), one merge kernel there
  * produces the answer.  Calls may come from any thread; up to TFP_MULTI_LANES (default 4)
  * finds run at once, further callers wait their turn.  Shard g hands out ids from
- * cfg->id_base + (g << 40).  Not available on such a handle: tfp_store_set_device and
- * the find-context calls (tfp_find_ctx_create fails; the store runs its own lanes). */
+ * cfg->id_base + (g << 40).  tfp_store_set_device works on such a handle but is not
+ * zero-copy there (rows must be routed: the block travels through page-locked host
+ * memory).  Not available: the find-context calls (tfp_find_ctx_create fails; the store
+ * runs its own lanes). */
 int  tfp_store_open_devices(const tfp_cfg* cfg, const int* devices, int n_devices, tfp_store** out);
 /* Number of shards behind a handle (1 for tfp_store_open) and one shard's figures: what a
  * host's Status reply lists per GPU (pkg/grpc/base/base.go:77-81 memory breakdown). */

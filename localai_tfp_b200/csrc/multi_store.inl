@@ -362,6 +362,38 @@ static int multi_set(tfp_store* top, const float* keys, int64_t n, int dim, int6
     return 0;
 }
 
+// Keys that already sit in one GPU's memory.  They still have to be routed, and routing looks at the rows: the block is
+// brought to page-locked host memory in chunks and goes through multi_set -- correct and simple, one PCIe round trip
+// (a device-side route + peer gather would save it; not built).
+static int multi_set_device(tfp_store* top, const float* d_keys, int64_t n, int dim, int64_t* out_ids, uint8_t* out_was_new) {
+    if (n == 0) return fail(1, "no keys to add");
+    if (!d_keys || dim <= 0) return fail(2, "tfp_store_set_device: d_keys is NULL or dim <= 0");
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, d_keys) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
+        cudaGetLastError();
+        return fail(2, "tfp_store_set_device: d_keys is not device memory");
+    }
+    CU_OK(cudaSetDevice(at.device));
+    CU_OK(cudaDeviceSynchronize());   // the caller's producer stream is unknown: order after all of it
+    const int64_t chunk_rows = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)(((size_t)256 << 20) / ((size_t)dim * 4))));
+    PinBuf pin;
+    if (pin.reserve((size_t)chunk_rows * dim * 4)) return -1;
+    int rc = 0;
+    for (int64_t lo = 0; lo < n && !rc; lo += chunk_rows) {
+        const int64_t m = std::min(chunk_rows, n - lo);
+        if (cudaSetDevice(at.device) != cudaSuccess ||
+            cudaMemcpy(pin.p, d_keys + (size_t)lo * dim, (size_t)m * dim * 4, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            rc = fail(-1, "tfp_store_set_device: device-to-host copy failed");
+            break;
+        }
+        rc = multi_set(top, pin.as<float>(), m, dim, m, out_ids ? out_ids + lo : nullptr, out_was_new ? out_was_new + lo : nullptr);
+    }
+    const std::string err = g_err;
+    pin.release();
+    if (rc) g_err = err;
+    return rc;
+}
+
 static int multi_delete(tfp_store* top, const float* keys, int64_t n, int dim, int64_t* out_ids) {
     tfp_multi* m = top->multi;
     if (n == 0) return fail(1, "no keys to delete");                                 // store.go:201-203

@@ -2341,9 +2341,7 @@ extern "C" int tfp_store_set(tfp_store* s, const float* keys, int64_t n, int dim
 extern "C" int tfp_store_set_device(tfp_store* s, const float* d_keys, int64_t n, int dim, int64_t* out_ids,
                                     uint8_t* out_was_new) {
     if (!s) return fail(2, "tfp_store_set_device: store is NULL");
-    if (s->multi)
-        return keep_err(s, fail(2, "tfp_store_set_device: keys in one GPU's memory cannot be routed across a multi-GPU store; "
-                                   "use tfp_store_set"));
+    if (s->multi) return keep_err(s, multi_set_device(s, d_keys, n, dim, out_ids, out_was_new));
     return keep_err(s, store_set_device(s, d_keys, n, dim, out_ids, out_was_new));
 }
 extern "C" int tfp_store_delete(tfp_store* s, const float* keys, int64_t n, int dim, int64_t* out_ids) {

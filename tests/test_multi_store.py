@@ -103,6 +103,25 @@ def test_multi_batch_matches_single_store(tfp, oracle):
 
 
 @gpu
+def test_multi_set_device_routes_rows_that_are_already_in_hbm(tfp, oracle):
+    import torch
+    n, d = 40000, 96
+    K = make_keys(n, d, seed=15, normalized=True)
+    Kd = torch.from_numpy(K).cuda()
+    m = tfp.Store(devices=two_devices())
+    ids, new = m.set_device(Kd.data_ptr(), n, d)
+    assert new.all() and len(set(ids.tolist())) == n and len(m) == n and m.keys_are_normalized
+    assert min(m.shard_stats(0).rows, m.shard_stats(1).rows) > 0.4 * n
+    rows_of = {int(i): j for j, i in enumerate(ids)}
+    q = make_keys(1, d, seed=16, normalized=True)[0]
+    fids, sims = m.find_ids(q, 10)
+    check_find_against_scores([rows_of[int(i)] for i in fids], sims, oracle.scores_block(K, q, True), 10)
+    ids2, new2 = m.set_device(Kd.data_ptr(), 100, d)                     # the same keys again: overwrites, same ids
+    assert not new2.any() and np.array_equal(ids2, ids[:100]) and len(m) == n
+    m.close()
+
+
+@gpu
 def test_multi_concurrent_finds_use_the_lanes(tfp, oracle):
     K = make_keys(20000, 96, seed=11, normalized=True)
     Q = make_keys(16, 96, seed=12, normalized=True)
