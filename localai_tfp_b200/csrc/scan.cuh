@@ -400,10 +400,23 @@ __device__ __forceinline__ void scan_epilogue(const ScanParams& p, SelState* sel
         const int room = ms.room;
         for (int base = 0; base < total; base += room) {
             const int stop = base + room < total ? base + room : total;
-            for (int i = base + tid; i < stop; i += kSelThreads) {
-                int lo = 0, hi = grid;   // largest b with pref[b] <= i
-                while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (pref[mid] <= i) lo = mid; else hi = mid; }
-                sel_offer(ms, __ldcg(p.part + ((size_t)lo * kMaxNQ + q) * k + (i - pref[lo])));
+            // four words per thread and trip: their loads are issued together, so a list of a few hundred words (a
+            // store of one tile per CTA, where no grid-wide bound has formed yet) costs one L2 round trip, not three
+            for (int i0 = base + tid; i0 < stop; i0 += 4 * kSelThreads) {
+                uint64_t w[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int i = i0 + u * kSelThreads;
+                    w[u] = 0ull;
+                    if (i < stop) {
+                        int lo = 0, hi = grid;   // largest b with pref[b] <= i
+                        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (pref[mid] <= i) lo = mid; else hi = mid; }
+                        w[u] = __ldcg(p.part + ((size_t)lo * kMaxNQ + q) * k + (i - pref[lo]));
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (i0 + u * kSelThreads < stop) sel_offer(ms, w[u]);
             }
             named_bar_sync(kSelBarrier, kSelThreads);
             sel_maybe_prune(ms, tid, false);
