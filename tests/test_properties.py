@@ -1,0 +1,119 @@
+"""Property tests on generated stores, for both kinds of handle: whatever keys, values, order of
+insertion and top-k hypothesis comes up with,
+  * a find answers like the oracle -- same similarities bit for bit, same values where scores are not tied;
+  * k' = min(k, N) results, in descending order, no row twice;
+  * the result does not depend on the order the keys were inserted in (as a set of (similarity, value) pairs);
+  * a stored unit key is its own best match;
+  * set over an existing key replaces its value, delete of a missing key changes nothing, and the sticky
+    normalised flag follows the oracle's through all of it."""
+import numpy as np
+import pytest
+from hypothesis import HealthCheck, given, settings, strategies as st
+
+from conftest import normalize_rows, two_devices
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+@st.composite
+def stores(draw):
+    d = draw(st.sampled_from([3, 8, 33, 64]))
+    n = draw(st.integers(1, 120))
+    seed = draw(st.integers(0, 2 ** 31 - 1))
+    rng = np.random.default_rng(seed)
+    K = rng.standard_normal((n, d)).astype(f32)
+    unit = draw(st.booleans())
+    if unit:
+        K = normalize_rows(K)
+    else:
+        K = (normalize_rows(K) * rng.uniform(0.3, 3.0, size=(n, 1)).astype(f32)).astype(f32)
+    if draw(st.booleans()) and n > 3:                       # exact duplicates of a stored key, signed zeros
+        K[n // 2] = K[0]
+        K[n - 1, 0] = f32(-0.0) if K[n - 1, 0] == 0 else K[n - 1, 0]
+    q = rng.standard_normal(d).astype(f32)
+    if draw(st.booleans()):
+        q = normalize_rows(q[None])[0]
+    k = draw(st.integers(1, 2 * n + 3))
+    perm = rng.permutation(n)
+    return K, q, k, perm, unit
+
+
+def open_store(tfp, kind):
+    return tfp.Store() if kind == "one-gpu" else tfp.Store(devices=two_devices())
+
+
+@pytest.mark.parametrize("kind", ["one-gpu", "multi"])
+@settings(max_examples=30, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+@given(case=stores())
+def test_find_properties(tfp, oracle, kind, case):
+    K, q, k, perm, unit = case
+    n = len(K)
+    vals = [b"v%d" % i for i in range(n)]
+    s, o = open_store(tfp, kind), oracle.OracleStore()
+    try:
+        s.StoresSet(K, vals); o.StoresSet(K, vals)
+        assert len(s) == len(o) and s.keys_are_normalized == o.keys_are_normalized
+        ks, vs, sims = s.StoresFind(q, k)
+        oks, ovs, osims = o.StoresFind(q, k)
+        assert s.last_path == o.last_path
+        assert len(sims) == min(k, len(o)) == len(osims)                     # k' = min(k, N)
+        assert np.array_equal(sims, osims)                                     # bit for bit
+        assert (np.diff(sims.astype(np.float64)) <= 0).all() or np.isnan(sims).any()
+        for i in range(len(sims)):                                             # values where the score is not tied
+            tied = (i > 0 and osims[i - 1] == osims[i]) or (i + 1 < len(osims) and osims[i + 1] == osims[i])
+            if not tied:
+                assert vs[i] == ovs[i] and np.array_equal(ks[i], oks[i])
+        # the same keys inserted in another order (and in two calls): the same answer as a set
+        s2 = open_store(tfp, kind)
+        try:
+            half = n // 2
+            s2.StoresSet(K[perm[:half + 1]], [vals[i] for i in perm[:half + 1]])
+            if half + 1 < n:
+                s2.StoresSet(K[perm[half + 1:]], [vals[i] for i in perm[half + 1:]])
+            if len(s2) == len(s):                                              # (duplicate keys may collapse differently)
+                _, _, sims2 = s2.StoresFind(q, k)
+                assert np.array_equal(sims2, sims)
+        finally:
+            s2.close()
+        if unit and n > 1:                                                     # a stored unit key is its own best match
+            j = int(perm[0])
+            _, vj, sj = s.StoresFind(K[j], 1)
+            assert sj[0] >= f32(0.99) and np.array_equal(sj, o.StoresFind(K[j], 1)[2])
+    finally:
+        s.close()
+
+
+@pytest.mark.parametrize("kind", ["one-gpu", "multi"])
+@settings(max_examples=20, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+@given(case=stores(), data=st.data())
+def test_mutation_properties(tfp, oracle, kind, case, data):
+    K, q, k, perm, unit = case
+    # distinct keys only: which of two EQUAL stored keys an overwrite or a delete hits is an artefact of the reference's
+    # unstable sort, not a property (the semantics tests pin the cases the reference's own tests pin)
+    K = K[np.sort(np.unique(K, axis=0, return_index=True)[1])]
+    n = len(K)
+    perm = np.random.default_rng(n).permutation(n)
+    s, o = open_store(tfp, kind), oracle.OracleStore()
+    try:
+        vals = [b"a%d" % i for i in range(n)]
+        s.StoresSet(K, vals); o.StoresSet(K, vals)
+        # overwrite some stored keys (store.go:183-187), add a non-unit key (sticky flag), delete present and absent keys
+        over = perm[: data.draw(st.integers(0, min(n, 5)))]
+        if len(over):
+            s.StoresSet(K[over], [b"new%d" % i for i in over]); o.StoresSet(K[over], [b"new%d" % i for i in over])
+        if data.draw(st.booleans()):
+            big = (K[0] * f32(5)).astype(f32)[None]
+            s.StoresSet(big, [b"big"]); o.StoresSet(big, [b"big"])
+        gone = perm[: data.draw(st.integers(0, min(n, 7)))]
+        absent = (K[:2] + f32(7.5)).astype(f32)
+        victims = np.concatenate([K[gone], absent])
+        s.StoresDelete(victims); o.StoresDelete(victims)
+        assert len(s) == len(o) and s.keys_are_normalized == o.keys_are_normalized and s.key_len == o.key_len
+        gk, gv = s.StoresGet(K); ok_, ov = o.StoresGet(K)
+        assert gv == ov and len(gk) == len(ok_) and all(np.array_equal(a, b) for a, b in zip(gk, ok_))
+        if len(o):
+            a, b = s.StoresFind(q, k), o.StoresFind(q, k)
+            assert np.array_equal(a[2], b[2]) and s.last_path == o.last_path
+    finally:
+        s.close()
