@@ -404,18 +404,20 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
 
     Q = gen_queries(wl)
     ctx = ops.ctx
-    in_flight = lanes if not batched else 1
+    # batches: tfp_find_ctx_launch returns once a batch's first tensor-core pass is enqueued, so on one GPU two contexts
+    # take the batches in turn and the next batch is queued while the host looks at the previous one's status words
+    in_flight = lanes if not batched else (min(2, lanes, max(1, args.batch_lanes)) if world == 1 else 1)
     for ln in ops.lanes:
         ln.ctx.upload(Q)       # queries resident in HBM before the timed region
         ln.ctx.sync()
     stream = torch.cuda.ExternalStream(ctx.stream, device=device)
     lane_ctx = [ln.ctx for ln in ops.lanes]
-    side_streams = [ln.stream for ln in ops.lanes[1:]] if not batched else []
+    side_streams = [ln.stream for ln in ops.lanes[1:in_flight]]
 
     def step_device(i: int):
         if batched:          # one batch of QPS queries per step (tensor-core path)
             if world == 1:
-                ctx.launch(0, QPS, TOPK)
+                lane_ctx[i % in_flight].launch(0, QPS, TOPK)
             else:
                 ctx.launch_sharded(0, TOPK, count=QPS)
         elif world == 1:
@@ -428,6 +430,13 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(device)
+
+    def finish_batches():
+        # a batch's later passes (taken only when its first pass flags queries) are enqueued by the context's next call:
+        # make that call inside the timed region
+        if batched and world == 1:
+            for c in lane_ctx[:in_flight]:
+                c.sync()
 
     def launches_now():
         return sum(c.launch_count for c in lane_ctx)
@@ -451,6 +460,7 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
                 sb.wait_event(e0)                # every lane's stream starts after e0 ...
             for i in range(args.steps):
                 step_device(i)
+            finish_batches()
             for sb in side_streams:
                 eb = torch.cuda.Event()
                 eb.record(sb)
@@ -479,6 +489,8 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
                 ctx.launch(0, QPS, TOPK)
             else:
                 ctx.launch(i % N_QUERIES, 1, TOPK)
+        if batched:
+            ctx.sync()
         s1.record(stream)
         torch.cuda.synchronize(device)
         scan_ms = s0.elapsed_time(s1) / k
@@ -492,6 +504,8 @@ def measure(env, wl: Workload, args, shard_cache: dict, with_cpu: bool, full_par
                 ctx.launch_sharded(0, TOPK, count=QPS)
             else:
                 sharded.find_device(i % N_QUERIES, TOPK, with_keys=False, lane=0)
+            if batched and world == 1:
+                ctx.sync()           # one batch at a time: the whole answer, status words included
         s1.record(stream)
         torch.cuda.synchronize(device)
         single_ms = s0.elapsed_time(s1) / k
@@ -906,6 +920,8 @@ def main():
     ap.add_argument("--lanes", type=int, default=0,
                     help="single-query finds kept in flight per GPU (find contexts); default 2 on one GPU, 4 on several "
                          "(a sharded find waits for its slowest peer: more finds in flight absorb the skew between ranks)")
+    ap.add_argument("--batch-lanes", type=int, default=2,
+                    help="one GPU, batched workloads: contexts that take the batches in turn (1 or 2)")
     ap.add_argument("--exchange", choices=["p2p", "torch", "native", "native-per-lane"], default="p2p",
                     help="N>1: records pushed to the peers by the scan kernel (p2p), ncclAllGather inside libtfpstore "
                          "(native), or torch.distributed (torch)")

@@ -195,20 +195,32 @@ void tfp_find_ctx_destroy(tfp_find_ctx* c);
  * query's path and |q| on the host exactly as store.go:313-324,435-439. */
 int  tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int dim);
 /* Enqueue the scan + top-k for staged queries [first, first+count).  Results
- * stay in HBM.  Returns without waiting for the GPU -- with one exception: a batch
- * that takes the tensor-core path (>= 3 same-path queries on a large store) waits
- * for that pass, because its per-query status words decide whether some queries
- * need a second pass (3xTF32 filter, then the exact kernel) before the launch is
- * complete. */
+ * stay in HBM.  Returns without waiting for the GPU.  A batch that takes the
+ * tensor-core path (>= 3 same-path queries on a large store) is finished in two
+ * steps: its per-query status words decide whether some queries need a second
+ * pass (3xTF32 filter, then the exact kernel), and somebody has to read them.
+ * When the launch is ONE such batch (count <= 256, one path) this call enqueues
+ * the first pass and returns; the NEXT call on the context -- upload, launch,
+ * gather_keys, download, sync, device_results, device_records -- waits for the
+ * status words and enqueues what is left, before it does its own work.  So the
+ * answer is final after any of those calls has returned and the stream has
+ * drained; a host that orders other work after the context's stream must call
+ * tfp_find_ctx_sync (not only wait for the stream) first.  A StoresSet /
+ * StoresDelete that has to move rows finishes such batches itself, on the rows
+ * as they were.  Launches made of several batches, and the synchronous and
+ * sharded entry points, read the status words before they return.
+ * (TFP_MMA_DEFER=0: always read them before returning.) */
 int  tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int topk);
 /* Wait, then copy results of the last launch to the host (same layout as
  * tfp_store_find_batch for `count` queries). */
 int  tfp_find_ctx_download(tfp_find_ctx* c, int* out_n, int64_t* out_ids, float* out_sims, float* out_keys);
+/* Wait for everything the last launch needs, later tensor-core passes included. */
 int  tfp_find_ctx_sync(tfp_find_ctx* c);
 /* The context's cudaStream_t, for event timing and for ordering collectives. */
 void* tfp_find_ctx_stream(tfp_find_ctx* c);
 /* Device pointers of the last launch's results: cand[count x topk] packed
- * (score-order word << 32 | ~slot), ids[count x topk], sims[count x topk], n[count]. */
+ * (score-order word << 32 | ~slot), ids[count x topk], sims[count x topk], n[count].
+ * Returns the entries per query in those arrays (min(topk, rows)), negative on failure. */
 int  tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids,
                                  float** d_sims, int** d_n);
 /* Enqueue the gather of the last launch's winning key rows and return their device

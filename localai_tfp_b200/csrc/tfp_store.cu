@@ -19,6 +19,7 @@
 #include <dlfcn.h>
 #include <fcntl.h>
 #include <unistd.h>
+#include <memory>
 #include <mutex>
 #include <pthread.h>
 #include <shared_mutex>
@@ -150,6 +151,7 @@ struct Tuning {
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter + re-score of its error band (3xTF32 as the second pass), 3 = 3xTF32 split first
     bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)
+    bool mma_defer = true;         // tfp_find_ctx_launch leaves a tensor-core batch's status words to the context's next call
     int mma_debug = 0;             // development timing only (results wrong): 1 no epilogue hits, 2 no MMAs
     bool mma_trace = false;        // print the tensor-core launch shape
     bool scan_times = false;       // per-CTA time stamps of every exact scan, printed by tfp_find_ctx_sync
@@ -166,6 +168,7 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_MMA_MIN_ROWS")) x.mma_min_rows = atoll(e);
         if (const char* e = getenv("TFP_MMA_TERMS")) x.mma_terms = atoi(e) == 3 ? 3 : 1;
         if (const char* e = getenv("TFP_MMA_PAIR")) x.mma_pair = atoi(e) != 0;
+        if (const char* e = getenv("TFP_MMA_DEFER")) x.mma_defer = atoi(e) != 0;
         if (const char* e = getenv("TFP_MMA_DEBUG")) x.mma_debug = atoi(e);
         x.mma_trace = getenv("TFP_MMA_TRACE") != nullptr;
         x.scan_times = getenv("TFP_SCAN_TIMES") != nullptr;
@@ -379,6 +382,7 @@ struct tfp_find_ctx {
     int last_count = 0, last_topk = 0, last_stride = 0, last_path = 0;
     int last_topk_host = 0;              // the topk the caller passed (host arrays are strided by it; last_topk may be clamped)
     int64_t launches = 0;
+    struct MmaPending* pend = nullptr;   // a tensor-core launch whose status words have not been read yet (ctx_resolve_locked)
 };
 
 static int set_device(const tfp_store* s) {
@@ -517,6 +521,8 @@ static int optin_all(int bytes) {
 // ---------------------------------------------------------------------------
 static int ctx_create(tfp_store* s, tfp_find_ctx** out);
 static void ctx_destroy(tfp_find_ctx* c);
+static int ctx_resolve_locked(tfp_find_ctx* c);
+static void ctx_drop_pending(tfp_find_ctx* c);
 
 static int store_open(const tfp_cfg* cfg, tfp_store** out) {
     if (!out) return fail(2, "tfp_store_open: out is NULL");
@@ -605,8 +611,13 @@ static int store_mark_not_normalized(tfp_store* s) {
 // ---------------------------------------------------------------------------
 // mutation plumbing
 // ---------------------------------------------------------------------------
+// Caller holds the exclusive lock.  A context whose tensor-core batch still waits for its status words gets the
+// rest of that find enqueued first: it must read the rows the first pass read, before they move.
 static int quiesce_finds(tfp_store* s) {
-    for (tfp_find_ctx* c : s->ctxs) CU_OK(cudaStreamSynchronize(c->stream));
+    for (tfp_find_ctx* c : s->ctxs) {
+        if (ctx_resolve_locked(c)) return -1;
+        CU_OK(cudaStreamSynchronize(c->stream));
+    }
     return 0;
 }
 
@@ -1095,6 +1106,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     if (!c) return;
     tfp_store* s = c->st;
     if (c->stream) cudaStreamSynchronize(c->stream);
+    ctx_drop_pending(c);
     if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     c->nccl_comm = nullptr;
     for (int r = 0; r < kXchgMaxWorld; r++)
@@ -1177,6 +1189,7 @@ extern "C" int tfp_find_ctx_upload(tfp_find_ctx* c, const float* q, int nq, int 
     if (!c || !q || nq <= 0 || dim <= 0) return fail(2, "tfp_find_ctx_upload: bad argument");
     std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
+    if (int rc = ctx_resolve_locked(c)) return rc;   // a re-run would read the queries this call replaces
     CU_OK(cudaStreamSynchronize(c->stream));   // the pinned staging buffer is reused
     return ctx_upload_locked(c, q, nq, dim);
 }
@@ -1204,6 +1217,81 @@ static int launch_scan_nq(tfp_find_ctx* c, int nq, const ScanParams& p, bool use
         }
         return fail(-4, "internal: bad query group size %d", nq);
     }
+}
+
+// What one launch worked out about the store and the request: kept by value, so that the part of a tensor-core launch
+// that runs after its status words arrive (ctx_resolve_locked) scans exactly the rows and slots the first pass did.
+struct LaunchPlan {
+    ScanParams p;
+    bool fused = false;
+    int dpad = 0, cap = 0, grid = 0, ksel = 0, count = 0, first = 0;
+    uint32_t n_tiles = 0;
+    int64_t n = 0;
+};
+
+// Launch the exact scan for staged queries [qf, qf+g) (same path, g in {1,2,4,8} or any g: it is
+// reduced to what fits) writing output slots [of, ...).  Returns the group size actually launched.
+// sel != nullptr: the g queries are sel[0..g) (any staged queries of this launch's range) and their answers go to
+// their own slots, of + (sel[j] - qf); such launches do not push records to peers (the caller does, afterwards).
+static int exact_launch(tfp_find_ctx* c, LaunchPlan& L, int qf, int of, int g, bool norm, int* launched, const int* sel = nullptr) {
+    tfp_store* s = c->st;
+    // pick the kernel flavour and the stage count that fits shared memory
+    bool use_tma = s->tmap_ok;
+    int n_stages = 0;
+    size_t smem = 0;
+    for (;;) {
+        if (use_tma) {
+            size_t fixed = scan_smem_bytes(0, g, L.dpad, L.cap) + 2 * kMaxStages * 8;
+            int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
+            n_stages = std::min(kMaxStages, room);
+            // A small shard (<= 32 tiles per CTA) scanned from a caller-made find context -- finds that are meant to
+            // overlap -- gets a 6-stage ring: two CTAs then share an SM, so one find's prologue / publish / merge
+            // runs under the other's streaming, and finds that run side by side read each tile from HBM once and
+            // from L2 after that.  Measured on 125k x 768 (profiles/r02_probe_small_stages.log): 58 -> 51 us per find
+            // with four finds in flight, 57 -> 40 with two; a lone scan pays 2-3 % (68.0 -> 69.3 us), so the
+            // store's own synchronous context and large stores keep the deep ring.
+            if (tuning().scan_stages >= 3) n_stages = std::min(n_stages, tuning().scan_stages);
+            else if (tuning().scan_stages == 0 && c != s->default_ctx && L.n_tiles <= 32u * (uint32_t)L.grid)
+                n_stages = std::min(n_stages, 6);
+            if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, L.dpad, L.cap); break; }
+            if (g > 1) { g >>= 1; continue; }
+            use_tma = false;
+        }
+        smem = scan_generic_smem_bytes(g, L.cap);
+        if (smem <= (size_t)s->max_smem) break;
+        if (g > 1) { g >>= 1; continue; }
+        return fail(-4, "internal: selection buffers do not fit shared memory (k=%d)", L.ksel);
+    }
+    L.p.n_stages = n_stages;
+    L.p.q_first = qf;
+    L.p.out_first = of;
+    L.p.use_qsel = sel ? 1 : 0;
+    for (int j = 0; j < kMaxNQ; j++) L.p.qsel[j] = sel ? sel[j < g ? j : g - 1] : 0;
+    L.p.xchg.raise = (of + g == L.count) ? 1 : 0;   // the launch that finishes the find raises the peers' words
+    int rc;
+    if (L.fused) rc = norm ? launch_scan_nq<false, false>(c, g, L.p, use_tma, L.grid, smem)
+                         : launch_scan_nq<true, false>(c, g, L.p, use_tma, L.grid, smem);
+    else       rc = norm ? launch_scan_nq<false, true>(c, 1, L.p, use_tma, L.grid, smem)
+                         : launch_scan_nq<true, true>(c, 1, L.p, use_tma, L.grid, smem);
+    if (rc) return rc;
+    if (!L.fused) {
+        // the spill kernels have no epilogue: re-arm the tile scheduler from the stream
+        CU_OK(cudaMemsetAsync(L.p.tile_counter, 0, sizeof(unsigned int), c->stream));
+        // big-k path: sort every row's candidate word (descending), keep the first k
+        size_t tmp = 0;
+        CU_OK(cub::DeviceRadixSort::SortKeysDescending(nullptr, tmp, c->all_cand.as<uint64_t>(),
+                                                       c->sorted_cand.as<uint64_t>(), (int64_t)L.n, 0, 64, c->stream));
+        if (c->cub_tmp.reserve(tmp)) return -1;
+        CU_OK(cub::DeviceRadixSort::SortKeysDescending(c->cub_tmp.p, tmp, c->all_cand.as<uint64_t>(),
+                                                       c->sorted_cand.as<uint64_t>(), (int64_t)L.n, 0, 64, c->stream));
+        decode_sorted_kernel<<<std::min(1024, (L.ksel + 255) / 256), 256, 0, c->stream>>>(
+            c->sorted_cand.as<uint64_t>(), (uint32_t)L.n, L.ksel, s->d_ids, of, L.p.out_cand, L.p.out_ids, L.p.out_sims,
+            L.p.out_slots, L.p.out_n, L.p.out_rec, L.p.rec_bytes, L.p.rec_topk);
+        CU_OK(cudaGetLastError());
+        c->launches += 2;
+    }
+    if (launched) *launched = g;
+    return 0;
 }
 
 // One tensor-core pass over the keys for g same-path staged queries named by index: h_qidx[j] is a staged query,
@@ -1331,31 +1419,70 @@ static int mma_pass_launch(tfp_find_ctx* c, const ScanParams& sp, const int* h_q
 // has to be good enough to leave few rows to re-score exactly; when it is not -- scores so close together that the
 // single-TF32 error band holds more rows than can be re-scored, or a candidate list that overflowed -- the flagged
 // queries go, TOGETHER, through one more pass with the 3xTF32 filter (error ~1e-6 instead of ~2e-3), and only what
-// that cannot settle either is re-run on the exact scan kernel, up to 8 queries per pass (`exact_some`).
-// The status words decide the escalation, so this is the one place a launch waits for the GPU.
-template <class ExactSome>
-static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o0, int g, bool norm, int grid,
-                            ExactSome&& exact_some) {
-    std::vector<int> idx((size_t)g);
-    for (int j = 0; j < g; j++) idx[(size_t)j] = q0 + j;
-    int terms = tuning().mma_terms;
+// that cannot settle either is re-run on the exact scan kernel, up to 8 queries per pass.
+// The status words decide the escalation, so somebody has to wait for the GPU before the answer is final:
+// mma_group_begin enqueues the first pass and the copy of its status words and returns; ctx_resolve_locked waits for
+// them and enqueues whatever else the group needs.  The synchronous callers run one after the other; a caller-made
+// context's tfp_find_ctx_launch leaves the second to the next call on the context (upload, launch, gather, download,
+// sync, device results / records -- each starts with ctx_resolve_locked), so that launch returns without waiting.
+struct MmaPending {
+    LaunchPlan L;
+    std::vector<int> idx;     // staged queries of the pass in flight, in status-word order
+    int q0 = 0, o0 = 0, terms = 1;
+    bool norm = false;
+};
+
+static int mma_group_begin(tfp_find_ctx* c, const LaunchPlan& L, int q0, int o0, int g, bool norm) {
+    MmaPending* m = new MmaPending();
+    m->L = L;
+    m->idx.resize((size_t)g);
+    for (int j = 0; j < g; j++) m->idx[(size_t)j] = q0 + j;
+    m->q0 = q0; m->o0 = o0; m->norm = norm;
+    m->terms = tuning().mma_terms;
+    int rc = mma_pass_launch(c, m->L.p, m->idx.data(), g, q0, o0, norm, L.grid, m->terms);
+    if (rc) { delete m; return rc; }
+    c->pend = m;
+    return 0;
+}
+
+static void ctx_drop_pending(tfp_find_ctx* c) {
+    delete c->pend;
+    c->pend = nullptr;
+}
+
+// Finish what mma_group_begin started on this context, if anything.  Caller holds the store's lock (shared or
+// exclusive) and has made the store's device current.  Waits for the context's stream.
+static int ctx_resolve_locked(tfp_find_ctx* c) {
+    if (!c->pend) return 0;
+    std::unique_ptr<MmaPending> m(c->pend);
+    c->pend = nullptr;
     for (;;) {
-        int rc = mma_pass_launch(c, sp, idx.data(), (int)idx.size(), q0, o0, norm, grid, terms);
-        if (rc) return rc;
         CU_OK(cudaStreamSynchronize(c->stream));
         if (tuning().mma_debug) return 0;   // (development timing runs skip the re-runs)
         const int* hs = c->h_status.as<int>();
         std::vector<int> flagged;
-        for (size_t j = 0; j < idx.size(); j++) if (hs[j] != 0) flagged.push_back(idx[j]);
+        for (size_t j = 0; j < m->idx.size(); j++) if (hs[j] != 0) flagged.push_back(m->idx[j]);
         if (flagged.empty()) return 0;
-        if (terms == 1 && flagged.size() >= 3) {   // (one or two queries: an exact scan each costs no more than another pass)
+        if (m->terms == 1 && flagged.size() >= 3) {   // (one or two queries: an exact scan each costs no more than another pass)
             c->mma_escalated += (int64_t)flagged.size();
-            idx.swap(flagged);
-            terms = 3;
+            m->idx.swap(flagged);
+            m->terms = 3;
+            int rc = mma_pass_launch(c, m->L.p, m->idx.data(), (int)m->idx.size(), m->q0, m->o0, m->norm, m->L.grid, 3);
+            if (rc) return rc;
             continue;
         }
+        // what neither filter settles is re-run on the exact kernel, up to 8 queries per pass over the keys
         c->mma_fallbacks += (int64_t)flagged.size();
-        return exact_some(flagged.data(), (int)flagged.size());
+        const int n_sel = (int)flagged.size();
+        int done = 0;
+        while (done < n_sel) {
+            const int left = n_sel - done;
+            int gg = left >= 8 ? 8 : (left >= 4 ? 4 : (left >= 2 ? 2 : 1)), launched = 0;
+            int rc = exact_launch(c, m->L, m->q0, m->o0, gg, m->norm, &launched, flagged.data() + done);
+            if (rc) return rc;
+            done += launched;
+        }
+        return 0;
     }
 }
 
@@ -1366,9 +1493,11 @@ static int mma_group_launch(tfp_find_ctx* c, const ScanParams& sp, int q0, int o
 // (c->keys_gathered), other paths leave them to gather_rows_kernel.
 // local_records: the find never leaves this shard (tfp_store_find[_batch]): size the packed records by
 // min(topk, rows) instead of the caller's topk -- only shards that exchange records need them equal.
+// may_defer: see mma_group_begin.
 static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, const XchgParams* xchg = nullptr,
-                             bool want_keys = false, bool local_records = false) {
+                             bool want_keys = false, bool local_records = false, bool may_defer = false) {
     tfp_store* s = c->st;
+    if (int rc0 = ctx_resolve_locked(c)) return rc0;   // the previous launch's answer is finished before its buffers are reused
     c->x_pushed = false;
     c->keys_gathered = false;
     if (c->dim != s->dim)                                                            // store.go:480-482
@@ -1415,8 +1544,11 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
     const uint32_t n_tiles = (uint32_t)((n + kRowsPerTile - 1) / kRowsPerTile);
     const int grid = (int)std::min<uint32_t>((uint32_t)std::min(s->sm_count, kMaxGrid), n_tiles);
 
-    ScanParams p;
+    LaunchPlan L;
+    ScanParams& p = L.p;
     memset(&p, 0, sizeof(p));
+    L.fused = fused; L.dpad = dpad; L.cap = cap; L.grid = grid; L.ksel = ksel; L.count = count; L.first = first;
+    L.n_tiles = n_tiles; L.n = n;
     p.keys = s->d_keys; p.ids = s->d_ids; p.knorm = s->d_knorm;
     p.n_rows = (uint32_t)n; p.dim = dim; p.n_chunks = n_chunks;
     p.topk = ksel; p.cap = cap;
@@ -1449,68 +1581,8 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
         p.all_cand = c->all_cand.as<uint64_t>();
     }
 
-    // Launch the exact scan for staged queries [qf, qf+g) (same path, g in {1,2,4,8} or any g: it is
-    // reduced to what fits) writing output slots [of, ...).  Returns the group size actually launched.
-    // sel != nullptr: the g queries are sel[0..g) (any staged queries of this launch's range) and their answers go to
-    // their own slots, of + (sel[j] - qf); such launches do not push records to peers (the caller does, afterwards).
     auto launch_exact = [&](int qf, int of, int g, bool norm, int* launched, const int* sel = nullptr) -> int {
-        // pick the kernel flavour and the stage count that fits shared memory
-        bool use_tma = s->tmap_ok;
-        int n_stages = 0;
-        size_t smem = 0;
-        for (;;) {
-            if (use_tma) {
-                size_t fixed = scan_smem_bytes(0, g, dpad, cap) + 2 * kMaxStages * 8;
-                int room = ((int)s->max_smem - (int)fixed) / kStageBytes;
-                n_stages = std::min(kMaxStages, room);
-                // A small shard (<= 32 tiles per CTA) scanned from a caller-made find context -- finds that are meant to
-                // overlap -- gets a 6-stage ring: two CTAs then share an SM, so one find's prologue / publish / merge
-                // runs under the other's streaming, and finds that run side by side read each tile from HBM once and
-                // from L2 after that.  Measured on 125k x 768 (profiles/r02_probe_small_stages.log): 58 -> 51 us per find
-                // with four finds in flight, 57 -> 40 with two; a lone scan pays 2-3 % (68.0 -> 69.3 us), so the
-                // store's own synchronous context and large stores keep the deep ring.
-                if (tuning().scan_stages >= 3) n_stages = std::min(n_stages, tuning().scan_stages);
-                else if (tuning().scan_stages == 0 && c != s->default_ctx && n_tiles <= 32u * (uint32_t)grid)
-                    n_stages = std::min(n_stages, 6);
-                if (n_stages >= 3) { smem = scan_smem_bytes(n_stages, g, dpad, cap); break; }
-                if (g > 1) { g >>= 1; continue; }
-                use_tma = false;
-            }
-            smem = scan_generic_smem_bytes(g, cap);
-            if (smem <= (size_t)s->max_smem) break;
-            if (g > 1) { g >>= 1; continue; }
-            return fail(-4, "internal: selection buffers do not fit shared memory (k=%d)", ksel);
-        }
-        p.n_stages = n_stages;
-        p.q_first = qf;
-        p.out_first = of;
-        p.use_qsel = sel ? 1 : 0;
-        for (int j = 0; j < kMaxNQ; j++) p.qsel[j] = sel ? sel[j < g ? j : g - 1] : 0;
-        p.xchg.raise = (of + g == count) ? 1 : 0;   // the launch that finishes the find raises the peers' words
-        int rc;
-        if (fused) rc = norm ? launch_scan_nq<false, false>(c, g, p, use_tma, grid, smem)
-                             : launch_scan_nq<true, false>(c, g, p, use_tma, grid, smem);
-        else       rc = norm ? launch_scan_nq<false, true>(c, 1, p, use_tma, grid, smem)
-                             : launch_scan_nq<true, true>(c, 1, p, use_tma, grid, smem);
-        if (rc) return rc;
-        if (!fused) {
-            // the spill kernels have no epilogue: re-arm the tile scheduler from the stream
-            CU_OK(cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), c->stream));
-            // big-k path: sort every row's candidate word (descending), keep the first k
-            size_t tmp = 0;
-            CU_OK(cub::DeviceRadixSort::SortKeysDescending(nullptr, tmp, c->all_cand.as<uint64_t>(),
-                                                           c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
-            if (c->cub_tmp.reserve(tmp)) return -1;
-            CU_OK(cub::DeviceRadixSort::SortKeysDescending(c->cub_tmp.p, tmp, c->all_cand.as<uint64_t>(),
-                                                           c->sorted_cand.as<uint64_t>(), (int64_t)n, 0, 64, c->stream));
-            decode_sorted_kernel<<<std::min(1024, (ksel + 255) / 256), 256, 0, c->stream>>>(
-                c->sorted_cand.as<uint64_t>(), (uint32_t)n, ksel, s->d_ids, of, p.out_cand, p.out_ids, p.out_sims,
-                p.out_slots, p.out_n, p.out_rec, p.rec_bytes, p.rec_topk);
-            CU_OK(cudaGetLastError());
-            c->launches += 2;
-        }
-        if (launched) *launched = g;
-        return 0;
+        return exact_launch(c, L, qf, of, g, norm, launched, sel);
     };
     auto path_of = [&](int qi) { return s->normalized && c->qinfo[(size_t)qi].normalized; };   // store.go:496
 
@@ -1535,20 +1607,13 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
         while (i + run < count && path_of(first + i + run) == norm) run++;
         if (mma_ok && run >= tuning().mma_min_queries) {
             const int g = std::min(run, kMmaMaxNQ);
-            // what neither filter settles is re-run on the exact kernel, up to 8 queries per pass over the keys
-            auto exact_some = [&](const int* sel, int n_sel) -> int {
-                int done = 0;
-                while (done < n_sel) {
-                    const int left = n_sel - done;
-                    int gg = left >= 8 ? 8 : (left >= 4 ? 4 : (left >= 2 ? 2 : 1)), launched = 0;
-                    int rc2 = launch_exact(first + i, i, gg, norm, &launched, sel + done);
-                    if (rc2) return rc2;
-                    done += launched;
-                }
-                return 0;
-            };
-            int rc = mma_group_launch(c, p, first + i, i, g, norm, grid, exact_some);
+            int rc = mma_group_begin(c, L, first + i, i, g, norm);
             if (rc) return rc;
+            // a launch that is this one group and nothing else may leave the status words to the context's next call
+            if (!(may_defer && i == 0 && g == count && tuning().mma_defer)) {
+                rc = ctx_resolve_locked(c);
+                if (rc) return rc;
+            }
             i += g;
             continue;
         }
@@ -1569,7 +1634,7 @@ extern "C" int tfp_find_ctx_launch(tfp_find_ctx* c, int first, int count, int to
     if (!c) return fail(2, "tfp_find_ctx_launch: ctx is NULL");
     std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
-    return ctx_launch_locked(c, first, count, topk);
+    return ctx_launch_locked(c, first, count, topk, nullptr, false, false, /*may_defer=*/true);
 }
 
 // Enqueue the gather of the winning rows of the last launch into c->out_keys.
@@ -1590,7 +1655,8 @@ extern "C" int tfp_find_ctx_gather_keys(tfp_find_ctx* c, float** d_keys) {
     if (c->last_count <= 0) return fail(2, "tfp_find_ctx_gather_keys: nothing was launched on this context");
     std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
-    int rc = ctx_gather_locked(c);
+    int rc = ctx_resolve_locked(c);
+    if (!rc) rc = ctx_gather_locked(c);
     if (rc) return rc;
     *d_keys = c->out_keys;
     return 0;
@@ -1600,6 +1666,7 @@ static int ctx_download_locked(tfp_find_ctx* c, int* out_n, int64_t* out_ids, fl
     tfp_store* s = c->st;
     const int count = c->last_count, topk = c->last_topk_host, ks = c->last_stride, dim = s->dim;
     if (count <= 0) return fail(2, "find download: nothing was launched on this context");
+    if (int rc = ctx_resolve_locked(c)) return rc;
     const size_t slots = (size_t)count * ks;
     // one D2H copy of the block's head: [n | ids | sims] and, when asked for, the key rows
     const size_t total = out_keys ? c->off_keys + slots * dim * 4 : c->off_sims + slots * 4;
@@ -1629,7 +1696,9 @@ extern "C" int tfp_find_ctx_download(tfp_find_ctx* c, int* out_n, int64_t* out_i
 }
 extern "C" int tfp_find_ctx_sync(tfp_find_ctx* c) {
     if (!c) return fail(2, "tfp_find_ctx_sync: ctx is NULL");
+    std::shared_lock<RwMutex> lk(c->st->rw);
     if (set_device(c->st)) return -1;
+    if (int rc = ctx_resolve_locked(c)) return rc;
     CU_OK(cudaStreamSynchronize(c->stream));
     if (c->dbg_grid > 0 && c->dbg_times.p) {   // development: timeline of the last scan
         std::vector<unsigned long long> t((size_t)c->dbg_grid * 4);
@@ -1669,6 +1738,10 @@ extern "C" int tfp_find_ctx_mma_counters(tfp_find_ctx* c, int64_t* passes, int64
 extern "C" int64_t tfp_find_ctx_mma_escalated(tfp_find_ctx* c) { return c ? c->mma_escalated : 0; }
 extern "C" int tfp_find_ctx_device_results(tfp_find_ctx* c, uint64_t** d_cand, int64_t** d_ids, float** d_sims, int** d_n) {
     if (!c) return fail(2, "tfp_find_ctx_device_results: ctx is NULL");
+    if (c->pend) {   // the arrays are final once the tensor-core batch in flight has been looked at
+        std::shared_lock<RwMutex> lk(c->st->rw);
+        if (set_device(c->st) || ctx_resolve_locked(c)) return -1;
+    }
     if (d_cand) *d_cand = c->out_cand;
     if (d_ids) *d_ids = c->out_ids;
     if (d_sims) *d_sims = c->out_sims;
@@ -1706,6 +1779,11 @@ extern "C" size_t tfp_record_bytes(int topk) { return record_bytes(topk < 0 ? 0 
 extern "C" int tfp_find_ctx_device_records(tfp_find_ctx* c, void** d_records, size_t* rec_bytes) {
     if (!c || !d_records || !rec_bytes) return fail(2, "tfp_find_ctx_device_records: NULL argument");
     if (c->last_count <= 0) return fail(2, "tfp_find_ctx_device_records: nothing was launched on this context");
+    if (c->pend) {
+        std::shared_lock<RwMutex> lk(c->st->rw);
+        if (set_device(c->st)) return -1;
+        if (int rc = ctx_resolve_locked(c)) return rc;
+    }
     *d_records = c->out_rec;
     *rec_bytes = record_bytes(c->last_topk);
     return 0;

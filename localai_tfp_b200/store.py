@@ -478,4 +478,6 @@ class FindContext:
         """(stride, cand_ptr, ids_ptr, sims_ptr, n_ptr): device addresses of the last launch's results."""
         a, b, c, d = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
         stride = self._L.tfp_find_ctx_device_results(self._h, C.byref(a), C.byref(b), C.byref(c), C.byref(d))
+        if stride < 0:
+            self.store._check(stride)
         return stride, a.value, b.value, c.value, d.value

@@ -113,3 +113,77 @@ def test_mma_path_tightly_clustered_keys_escalate_to_3xtf32(tfp, oracle, k, norm
         if k == 10 and normalized:
             assert reruns <= nq // 4      # (k = 100: ranks 100 and 148 of this cluster are 2e-5 apart, closer than the 3xTF32
                                           #  filter may call; those queries end on the exact kernel, 8 per pass)
+
+
+def clustered(n, nq, d, seed):
+    """Keys and queries inside one tight cluster: the first tensor-core pass flags most queries, so the answer needs
+    the passes that come after the status words (3xTF32, then exact re-runs)."""
+    rng = np.random.default_rng(seed)
+    centre = normalize_rows(rng.standard_normal((1, d)).astype(f32))[0]
+    K = normalize_rows(centre[None, :] + f32(0.05 / np.sqrt(d)) * rng.standard_normal((n, d)).astype(f32))
+    Q = normalize_rows(centre[None, :] + f32(0.05 / np.sqrt(d)) * rng.standard_normal((nq, d)).astype(f32))
+    return K, Q
+
+
+def check_all(oracle, K, Q, res, k):
+    for i in range(len(Q)):
+        check_find_against_scores(res[i][0], res[i][1], oracle.scores_block(K, Q[i], True), k)
+
+
+def test_launch_leaves_the_later_passes_to_the_next_call_on_the_context(tfp, oracle):
+    """tfp_find_ctx_launch of one tensor-core batch returns once the first pass is enqueued; the passes that depend on
+    its status words are enqueued by whichever call on the context comes next.  Every such call must see a finished,
+    bit-exact answer: download, sync + device arrays, a second launch (the first answer is then simply replaced), and
+    two contexts whose batches are in flight together."""
+    import torch
+    n, d, nq, k = 70000, 256, 24, 10
+    K, Q = clustered(n, nq, d, 3)
+    Q2 = make_keys(nq, d, seed=4, normalized=True)
+    s = tfp.Store()
+    s.StoresSet(K, [b""] * n)
+    a, b = s.find_context(), s.find_context()
+
+    a.upload(Q); b.upload(Q2)
+    a.launch(0, nq, k)                       # flagged queries pending ...
+    b.launch(0, nq, k)                       # ... while another context's batch goes in
+    check_all(oracle, K, Q, a.download(), k)
+    check_all(oracle, K, Q2, b.download(), k)
+    assert a.mma_escalated >= 1 or a.mma_counters()[1] >= 1, "the clustered batch was expected to need more than the first pass"
+
+    a.launch(0, nq, k)                       # read through the device arrays after a sync
+    a.sync()
+    stride, _, ids_p, sims_p, n_p = a.device_results()
+    assert stride == k
+    from localai_tfp_b200.sharded import _alias
+    ids = _alias(ids_p, (nq * k,), "<i8", "cuda:0").cpu().numpy()
+    sims = _alias(sims_p, (nq * k,), "<f4", "cuda:0").cpu().numpy()
+    cnt = _alias(n_p, (nq,), "<i4", "cuda:0").cpu().numpy()
+    res = [(ids[i * k:i * k + cnt[i]], sims[i * k:i * k + cnt[i]]) for i in range(nq)]
+    check_all(oracle, K, Q, res, k)
+
+    a.launch(0, nq, k)                       # never read: the next launch finishes it first, then replaces it
+    a.upload(Q2)
+    a.launch(0, nq, k)
+    check_all(oracle, K, Q2, a.download(), k)
+    a.close(); b.close(); s.close()
+
+
+def test_a_delete_between_launch_and_download_does_not_change_the_answer(tfp, oracle):
+    """A batch launched before a StoresDelete answers from the rows as they were at launch: the delete waits for the
+    finds in flight, and for a tensor-core batch that includes the passes that had not been enqueued yet."""
+    n, d, nq, k = 70000, 128, 16, 10
+    K, Q = clustered(n, nq, d, 8)
+    s = tfp.Store()
+    s.StoresSet(K, [b""] * n)
+    c = s.find_context()
+    c.upload(Q)
+    c.launch(0, nq, k)
+    s.StoresDelete(K[:5000])                 # compaction moves the tail of the store into the holes
+    check_all(oracle, K, Q, c.download(), k)              # the answer of the store as it was
+    c.launch(0, nq, k)
+    res = c.download()                                       # and now of the store as it is: ids of the survivors
+    K_now = K.copy(); K_now[:5000] = 0                       # deleted rows score 0 against unit queries near the centre: never in the top-k
+    for i in range(nq):
+        assert np.all(res[i][0] >= 5000)
+        check_find_against_scores(res[i][0], res[i][1], oracle.scores_block(K_now, Q[i], True), k)
+    c.close(); s.close()
