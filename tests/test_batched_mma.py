@@ -187,3 +187,26 @@ def test_a_delete_between_launch_and_download_does_not_change_the_answer(tfp, or
         assert np.all(res[i][0] >= 5000)
         check_find_against_scores(res[i][0], res[i][1], oracle.scores_block(K_now, Q[i], True), k)
     c.close(); s.close()
+
+
+def test_an_append_between_launch_and_download_is_not_in_the_answer(tfp, oracle):
+    """Appends do not wait for finds.  Rows that arrive after a batch was launched -- here the queries themselves, which
+    would be every query's best match -- must not show up in it, not even through the passes that are enqueued later
+    (they scan the row count the first pass saw); the next launch finds them."""
+    n, d, nq, k = 70000, 128, 16, 10
+    K, Q = clustered(n, nq, d, 21)
+    s = tfp.Store()
+    s.StoresSet(K, [b""] * n)
+    c = s.find_context()
+    c.upload(Q)
+    c.launch(0, nq, k)
+    s.StoresSet(Q, [b""] * nq)               # ids n .. n + nq - 1
+    res = c.download()
+    check_all(oracle, K, Q, res, k)
+    assert all(np.all(r[0] < n) for r in res)
+    c.launch(0, nq, k)
+    K2 = np.concatenate([K, Q])
+    res = c.download()
+    check_all(oracle, K2, Q, res, k)
+    assert all(int(res[i][0][0]) == n + i for i in range(nq))
+    c.close(); s.close()
