@@ -767,6 +767,63 @@ mma_finalize_kernel(const FinalizeParams p) {
         }
         return pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[slot] : 1.0), slot);
     };
+    // The walk as written above has lane l of a warp read 16 bytes of ITS row per load: 32 different lines per
+    // instruction, 256 L1 wavefronts per warp for every 128-byte step of the 32 rows (ncu, round 2: 83 % of this
+    // kernel's samples sit in the walk and the barrier behind it, at 1.3 TB/s).  A warp therefore fetches the step
+    // of its 32 rows TOGETHER -- 8 lanes per row, 4 whole 128-byte lines per instruction, 32 wavefronts per step --
+    // and hands every lane its own row's 128 bytes through a padded shared-memory tile (144-byte rows: both the
+    // 128-bit stores and the 128-bit loads are conflict-free).  Each lane still adds ITS row in index order: the
+    // arithmetic is unchanged.  The tile lives behind the staged query in the (dead) score-word array.
+    constexpr int kStgRow = 9;                           // float4 per staged row: 8 of data + 1 of padding
+    const size_t stg_off = (((size_t)p.dim * 4 + 15) & ~(size_t)15);
+    const bool coop = q_in_smem && stg_off + (size_t)kFinWarps * 32 * kStgRow * 16 <= kFinDynSmem;
+    if (coop) {
+        const int lane = tid & 31, wrp = tid >> 5;
+        const int lr = lane >> 3, lc = lane & 7;
+        float4* stg = reinterpret_cast<float4*>(reinterpret_cast<uint8_t*>(skey) + stg_off) + (size_t)wrp * 32 * kStgRow;
+        const float4* k4 = reinterpret_cast<const float4*>(p.keys);
+        const float4* qv4 = (const float4*)qs4;
+        const int n4 = p.dim >> 2;
+        const float4 zero4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (int t0 = wrp * 32; t0 < kMmaRescoreMax; t0 += kFinThreads) {
+            const int t = t0 + lane;
+            if (t0 >= C) { exact[t] = 0ull; continue; }  // (warp-uniform)
+            const bool valid = t < C;
+            const uint32_t my_slot = valid ? cand_slot(fbuf[t]) : 0u;
+            const unsigned vmask = __ballot_sync(0xFFFFFFFFu, valid);
+            uint32_t rslot[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) rslot[i] = __shfl_sync(0xFFFFFFFFu, my_slot, i * 4 + lr);
+            float4 nxt[8], cur[8];
+            auto fetch = [&](int base) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const bool on = ((vmask >> (i * 4 + lr)) & 1u) && base + lc < n4;
+                    nxt[i] = on ? __ldcs(k4 + (size_t)rslot[i] * n4 + base + lc) : zero4;
+                }
+            };
+            fetch(0);
+            Acc<F64> acc;
+            acc.zero();
+            for (int base = 0; base < n4; base += 8) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) stg[(i * 4 + lr) * kStgRow + lc] = nxt[i];
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 8; j++) cur[j] = stg[lane * kStgRow + j];
+                __syncwarp();
+                if (base + 8 < n4) fetch(base + 8);      // in flight while this step's 32 adds run
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    if (base + j < n4) {
+                        const float4 qq = qv4[base + j];
+                        acc.add(qq.x, cur[j].x); acc.add(qq.y, cur[j].y); acc.add(qq.z, cur[j].z); acc.add(qq.w, cur[j].w);
+                    }
+                }
+            }
+            exact[t] = valid ? pack_cand(finish_score<F64>(acc, mag1, F64 ? p.knorm[my_slot] : 1.0), my_slot) : 0ull;
+        }
+    } else {
     for (int t = tid; t < kMmaRescoreMax; t += blockDim.x) {
         uint64_t w = 0ull;
         if (t < C) {
@@ -775,6 +832,7 @@ mma_finalize_kernel(const FinalizeParams p) {
             else w = rescore(slot, reinterpret_cast<const float4*>(qv));
         }
         exact[t] = w;
+    }
     }
     __syncthreads();
     int PE = 2;

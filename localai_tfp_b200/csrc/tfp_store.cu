@@ -151,6 +151,8 @@ struct Tuning {
     int64_t mma_min_rows = 65536;
     int mma_terms = 1;             // 1 = single-TF32 filter + re-score of its error band (3xTF32 as the second pass), 3 = 3xTF32 split first
     bool mma_pair = true;          // single-TF32 filter on CTA pairs (cta_group::2: half the query bytes per SM)
+    int mma_serial = -1;           // tensor-core passes of different contexts are ordered one behind the other: 1 always, 0 never,
+                                   // -1 when the keys are 2 GiB or more (see mma_pass_launch)
     bool mma_defer = true;         // tfp_find_ctx_launch leaves a tensor-core batch's status words to the context's next call
     int mma_debug = 0;             // development timing only (results wrong): 1 no epilogue hits, 2 no MMAs
     bool mma_trace = false;        // print the tensor-core launch shape
@@ -169,6 +171,7 @@ static const Tuning& tuning() {
         if (const char* e = getenv("TFP_MMA_TERMS")) x.mma_terms = atoi(e) == 3 ? 3 : 1;
         if (const char* e = getenv("TFP_MMA_PAIR")) x.mma_pair = atoi(e) != 0;
         if (const char* e = getenv("TFP_MMA_DEFER")) x.mma_defer = atoi(e) != 0;
+        if (const char* e = getenv("TFP_MMA_SERIAL")) x.mma_serial = atoi(e);
         if (const char* e = getenv("TFP_MMA_DEBUG")) x.mma_debug = atoi(e);
         x.mma_trace = getenv("TFP_MMA_TRACE") != nullptr;
         x.scan_times = getenv("TFP_SCAN_TIMES") != nullptr;
@@ -324,6 +327,11 @@ struct tfp_store {
     std::vector<uint64_t> slot_hash;   // host mirror: slot -> row hash
     std::vector<int64_t> slot_id;      // host mirror: slot -> id
     cudaStream_t s_mut = nullptr;      // side stream for ingest / compaction
+    // Tensor-core passes of different find contexts run one after the other (each uses every SM); what overlaps with
+    // the next batch's passes is a batch's finalize.  mma_ev is recorded behind every full pass.
+    std::mutex mma_mu;
+    cudaEvent_t mma_ev = nullptr;
+    tfp_find_ctx* mma_last = nullptr;
     DevBuf st_rows, st_hash, st_knorm, st_isnorm, st_pair_row, st_pair_slot, st_pair_eq, st_src, st_dst, st_ids;
     std::vector<tfp_find_ctx*> ctxs;
     tfp_find_ctx* default_ctx = nullptr;
@@ -585,6 +593,7 @@ static void store_close(tfp_store* s) {
                       &s->st_pair_slot, &s->st_pair_eq, &s->st_src, &s->st_dst, &s->st_ids};
     for (DevBuf* b : bufs) b->release();
     if (s->s_mut) cudaStreamDestroy(s->s_mut);
+    if (s->mma_ev) cudaEventDestroy(s->mma_ev);
     delete s;
 }
 
@@ -1107,6 +1116,7 @@ static void ctx_destroy(tfp_find_ctx* c) {
     tfp_store* s = c->st;
     if (c->stream) cudaStreamSynchronize(c->stream);
     ctx_drop_pending(c);
+    if (s) { std::lock_guard<std::mutex> g(s->mma_mu); if (s->mma_last == c) s->mma_last = nullptr; }
     if (c->nccl_comm && c->comm_owned && g_nccl.CommDestroy) g_nccl.CommDestroy(c->nccl_comm);
     c->nccl_comm = nullptr;
     for (int r = 0; r < kXchgMaxWorld; r++)
@@ -1328,6 +1338,18 @@ static int mma_pass_launch(tfp_find_ctx* c, const ScanParams& sp, const int* h_q
     }
     for (int j = g; j < kMmaMaxNQ; j++) { he[j] = 0.0f; hq[j] = h_qidx[0]; }
     CU_OK(cudaMemcpyAsync(eps, he, (size_t)2 * kMmaMaxNQ * 4, cudaMemcpyHostToDevice, c->stream));
+    // Two contexts' passes interleaved CTA by CTA can settle into a bad schedule on a large store: each grid holds part
+    // of the SMs and both run at the pace of their late starters (1M x 768, 256 queries, two contexts in turn: 0.76 ms
+    // per batch in most runs, 1.1 - 1.2 ms in one run out of three; profiles/r02_probe_defer.log).  So on 2 GiB of keys
+    // or more this context's passes start behind the last full pass another context enqueued; what still overlaps is a
+    // batch's finalize with the next batch's passes (0.78 - 0.90 ms there, every run).  Smaller stores, whose passes
+    // do not fill the GPU for long, gain more from running freely (250k x 768, 64 queries: 0.167 ms against 0.197).
+    const bool serial = tuning().mma_serial > 0 || (tuning().mma_serial < 0 && (size_t)sp.n_rows * dim * 4 >= ((size_t)2 << 30));
+    if (serial) {
+        std::lock_guard<std::mutex> g(s->mma_mu);
+        if (!s->mma_ev) CU_OK(cudaEventCreateWithFlags(&s->mma_ev, cudaEventDisableTiming));
+        if (s->mma_last && s->mma_last != c) CU_OK(cudaStreamWaitEvent(c->stream, s->mma_ev, 0));
+    }
 
     qsplit_kernel<<<std::min(1024, (int)(((size_t)nqp * dim + 255) / 256)), 256, 0, c->stream>>>(sp.q, qmap, g, nqp, dim, qs);
     CU_OK(cudaGetLastError());
@@ -1391,6 +1413,11 @@ static int mma_pass_launch(tfp_find_ctx* c, const ScanParams& sp, const int* h_q
     CU_OK(cudaGetLastError());
     mp.mode = 1;
     if (launch_pass()) return -1;
+    if (serial) {
+        std::lock_guard<std::mutex> g(s->mma_mu);
+        CU_OK(cudaEventRecord(s->mma_ev, c->stream));
+        s->mma_last = c;
+    }
 
     FinalizeParams fp;
     memset(&fp, 0, sizeof(fp));
