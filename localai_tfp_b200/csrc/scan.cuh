@@ -702,8 +702,16 @@ scan_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 }
 
 // ---- the generic kernel: any dim (dim % 4 != 0, dim < 32, or a query too long
-// for shared memory).  Same arithmetic and selection; rows are read straight
-// from global memory, one thread per row, so it is correct but not tuned. -------
+// for shared memory).  Same arithmetic and selection, one thread per row.  A thread that reads its own row
+// straight from global memory makes every load instruction of its warp touch 32 lines (measured: 1.1 - 1.5 TB/s,
+// and two queries per pass slower than two passes; one CTA of four warps per SM has nothing in flight to hide the
+// latency either), so a warp fetches its 32 rows 32 columns at a time -- lane l copies column c0 + l of every row:
+// one or two lines per instruction -- into a padded shared-memory tile (144-byte rows: each lane's 128-bit loads of
+// its own row are conflict-free), with the same columns of the queries beside it.  The next step's loads (across
+// tile boundaries too) are issued before this step's adds, and kGenCtasPerSm CTAs share an SM. -------
+constexpr int kGenRowFloats = 36;              // staged row: 32 columns + 4 of padding
+constexpr int kGenCtasPerSm = 3;               // resident CTAs (of four warps) per SM: what keeps enough loads in flight
+__host__ __device__ inline size_t scan_generic_stage_floats(int nq) { return (size_t)32 * kGenRowFloats + (size_t)nq * 32; }
 template <int NQ, bool F64, bool SPILL>
 __global__ void __launch_bounds__(kSelThreads, 4)
 scan_generic_kernel(const __grid_constant__ ScanParams p) {
@@ -716,41 +724,102 @@ scan_generic_kernel(const __grid_constant__ ScanParams p) {
     sm.flag = sm.cnt + NQ;
     sm.pref = sm.flag + 1;
     sm.lmax = nullptr;   // the generic kernel publishes lbest at prunes only
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    constexpr uint32_t kStageFloats = (uint32_t)(32 * kGenRowFloats + NQ * 32);     // a warp's tile, then its query columns
+    float* ring = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(sm.pref + kMaxGrid + 1) + 15) & ~(uintptr_t)15) +
+                  (size_t)wrp * kStageFloats;
     SelState sel[NQ];
     sel_setup<NQ>(p, sm, sel, tid);
     named_bar_sync(kSelBarrier, kSelThreads);
     double mag1[NQ];
+    size_t qoff[NQ];
 #pragma unroll
-    for (int q = 0; q < NQ; q++) mag1[q] = F64 ? p.qinfo[scan_query_of(p, q)].mag1 : 0.0;
+    for (int q = 0; q < NQ; q++) {
+        mag1[q] = F64 ? p.qinfo[scan_query_of(p, q)].mag1 : 0.0;
+        qoff[q] = (size_t)scan_query_of(p, q) * p.dim;
+    }
     const uint32_t n_tiles = (p.n_rows + kRowsPerTile - 1) / kRowsPerTile;
+    const uint32_t n_chunks = ((uint32_t)p.dim + 31u) / 32u;
+    const uint32_t my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+    const uint32_t total = my_tiles * n_chunks;                                     // 32-column steps this warp walks, over all its tiles
+    // producer side: the NEXT step's loads are issued before this step's adds and wait in registers meanwhile (4-byte
+    // cp.async copies were measured at a third of this: ~19 cycles of the load/store unit each)
+    uint32_t i_tile = blockIdx.x, i_chunk = 0;
+    float nxt[32], nxq[NQ];
+    auto fetch = [&](uint32_t k) {
+        if (k < total) {
+            const int c0 = (int)i_chunk * 32;
+            const uint32_t row0 = i_tile * kRowsPerTile + (uint32_t)(wrp * 32);
+            const int nr = row0 < p.n_rows ? (int)(p.n_rows - row0 < 32u ? p.n_rows - row0 : 32u) : 0;
+            const bool on = c0 + lane < p.dim;
+            const float* src = p.keys + (size_t)row0 * p.dim + c0 + lane;
+#pragma unroll
+            for (int r = 0; r < 32; r++) {
+                const float* a = src + (size_t)r * p.dim;
+                nxt[r] = (on && r < nr) ? (p.evict_first ? __ldcs(a) : __ldcg(a)) : 0.0f;
+            }
+#pragma unroll
+            for (int q = 0; q < NQ; q++) nxq[q] = on ? __ldg(p.q + qoff[q] + c0 + lane) : 0.0f;
+            if (++i_chunk == n_chunks) { i_chunk = 0; i_tile += gridDim.x; }
+        }
+    };
+    fetch(0);
     unsigned long long last_pub = 0ull;
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
-        const bool valid = row < p.n_rows;
-        Acc<F64> acc[NQ];
+    uint32_t tile = blockIdx.x, chunk = 0;
+    Acc<F64> acc[NQ];
+    unsigned long long g_seen = 0ull;
+    for (uint32_t k = 0; k < total; k++) {
+        {
+            float* st = ring;
 #pragma unroll
-        for (int q = 0; q < NQ; q++) acc[q].zero();
-        unsigned long long g_seen = 0ull;
-        if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
-        if (valid) {
-            const float* kr = p.keys + (size_t)row * p.dim;
-            for (int i = 0; i < p.dim; i++) {
-                const float kv = kr[i];
+            for (int r = 0; r < 32; r++) st[r * kGenRowFloats + lane] = nxt[r];
 #pragma unroll
-                for (int q = 0; q < NQ; q++) acc[q].add(__ldg(p.q + (size_t)scan_query_of(p, q) * p.dim + i), kv);
+            for (int q = 0; q < NQ; q++) st[32 * kGenRowFloats + q * 32 + lane] = nxq[q];
+        }
+        __syncwarp();
+        fetch(k + 1);                                                               // in flight while this step's adds run
+        if (chunk == 0) {
+#pragma unroll
+            for (int q = 0; q < NQ; q++) acc[q].zero();
+            g_seen = 0ull;
+            if (!SPILL && tid < NQ) g_seen = *((volatile unsigned long long*)(p.gtau + tid));
+        }
+        const int w = p.dim - (int)chunk * 32 < 32 ? p.dim - (int)chunk * 32 : 32;
+        const float* st = ring;
+        const float4* kr4 = reinterpret_cast<const float4*>(st + lane * kGenRowFloats);
+        const float* sq = st + 32 * kGenRowFloats;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (4 * j < w) {                                                        // (warp-uniform); the adds stay in index order
+                const float4 kv = kr4[j];
+#pragma unroll
+                for (int q = 0; q < NQ; q++) {
+                    const float4 qq = reinterpret_cast<const float4*>(sq + q * 32)[j];
+                    acc[q].add(qq.x, kv.x);
+                    if (4 * j + 1 < w) acc[q].add(qq.y, kv.y);
+                    if (4 * j + 2 < w) acc[q].add(qq.z, kv.z);
+                    if (4 * j + 3 < w) acc[q].add(qq.w, kv.w);
+                }
             }
         }
-        float score[NQ];
-        const double kn = (F64 && valid) ? p.knorm[row] : 1.0;
+        __syncwarp();                                                               // the tile may be overwritten
+        if (++chunk == n_chunks) {
+            chunk = 0;
+            const uint32_t row = tile * kRowsPerTile + (uint32_t)tid;
+            const bool valid = row < p.n_rows;
+            float score[NQ];
+            const double kn = (F64 && valid) ? p.knorm[row] : 1.0;
 #pragma unroll
-        for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
-        tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen, last_pub);
+            for (int q = 0; q < NQ; q++) score[q] = finish_score<F64>(acc[q], mag1[q], kn);
+            tile_offer<NQ, SPILL>(p, sel, score, row, valid, tid, g_seen, last_pub);
+            tile += gridDim.x;
+        }
     }
     if constexpr (!SPILL) scan_epilogue<NQ>(p, sel, sm.flag, sm.pref, tid, nullptr, 0);
 }
 __host__ inline size_t scan_generic_smem_bytes(int nq, int cap) {
-    return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + (size_t)(kMaxGrid + 1) * 4 + 32;
+    return (size_t)nq * cap * 8 + (size_t)nq * 8 + (size_t)nq * 4 + 4 + (size_t)(kMaxGrid + 1) * 4 + 32 +
+           16 + (size_t)(kSelThreads / 32) * scan_generic_stage_floats(nq) * 4;
 }
 
 // ---- big-k path, pass 2: decode the first k of the (already sorted) spill -------

@@ -1569,7 +1569,9 @@ static int ctx_launch_locked(tfp_find_ctx* c, int first, int count, int topk, co
     const int dpad = n_chunks * kBoxCols;
     const int cap = fused ? std::max(512, next_pow2(ksel + std::max(ksel, 2 * kRowsPerTile))) : 2;
     const uint32_t n_tiles = (uint32_t)((n + kRowsPerTile - 1) / kRowsPerTile);
-    const int grid = (int)std::min<uint32_t>((uint32_t)std::min(s->sm_count, kMaxGrid), n_tiles);
+    // One persistent CTA per SM for the TMA scan (its stage ring keeps the loads in flight).  The generic kernel keeps
+    // them in flight with resident warps instead: kGenCtasPerSm CTAs of four warps per SM.
+    const int grid = (int)std::min<uint32_t>((uint32_t)std::min(s->sm_count * (s->tmap_ok ? 1 : kGenCtasPerSm), kMaxGrid), n_tiles);
 
     LaunchPlan L;
     ScanParams& p = L.p;
