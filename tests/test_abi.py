@@ -43,9 +43,25 @@ def test_product_never_touches_the_oracle():
     pkg = os.path.join(ROOT, "localai_tfp_b200")
     for dirpath, _, files in os.walk(pkg):
         for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h")):
+            if f.endswith((".py", ".cu", ".cuh", ".hpp", ".h", ".inl")):
                 src = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle" not in src.lower(), f"{f} mentions the oracle"
+
+
+@pytest.mark.parametrize("compiler,std,ext", [("gcc", "-std=c99", ".c"), ("g++", "-std=c++17", ".cpp")])
+def test_header_is_plain_c(tmp_path, compiler, std, ext):
+    """The boundary is a C ABI: the header must compile as strict C99 (what cgo's C compiler sees) and as C++,
+    with nothing but the standard headers."""
+    import shutil
+    import subprocess
+    if not shutil.which(compiler):
+        pytest.skip(compiler + " is not installed")
+    src = tmp_path / ("use_header" + ext)
+    src.write_text('#include "tfp_store.h"\n'
+                   "int main(void) { tfp_cfg cfg; tfp_stats st; (void)cfg; (void)st; return tfp_version() == 0; }\n")
+    r = subprocess.run([compiler, std, "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only",
+                        "-I", os.path.join(ROOT, "include"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
 
 
 def test_open_fails_loudly_without_a_gpu(tfp):
