@@ -485,9 +485,7 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
         // branch-free pass over the block; all its state is addressed as shared memory (no generic atomics).
         int* const my_hitn = hitn + ew;
         uint4* const my_hitq = hitq + ew * kMmaHitQueue;
-        auto on_hit = [&](int q, uint32_t row, float sc) {
-            if (q >= p.nq) return;
-            const unsigned int o = score_to_order(sc);
+        auto note_best = [&](int q, unsigned int o) {
             if (o > ((volatile unsigned int*)lb2)[q]) {
                 // keep the CTA's two best: the new best goes to lb, whichever of (old best, this score) is not
                 // the best any more is offered to lb2.  Every score but the largest ends up offered to lb2.
@@ -496,6 +494,11 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                 const unsigned int old2 = atomicMax(lb2 + q, lower);
                 ((volatile float*)lb_f)[q] = order_to_score(old2 > lower ? old2 : lower);
             }
+        };
+        auto on_hit = [&](int q, uint32_t row, float sc, bool note) {
+            if (q >= p.nq) return;
+            const unsigned int o = score_to_order(sc);
+            if (note) note_best(q, o);
             if (p.mode == 1 && o >= ((volatile unsigned int*)tau)[q]) {
                 // A global atomic per hit would stall the warp ~1 us each time (its result is needed for the
                 // store): stage the hit, the warp flushes all of them after the tile.
@@ -545,10 +548,30 @@ mma_scan_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constan
                     mask |= ((sj >= tj) | (sj > bj)) ? (1u << j) : 0u;      // both false for NaN
                 }
                 if (!valid || (p.debug & 1)) mask = 0u;
-                if (mask) {
+                // The first tile of a pass meets empty bests: every element is a "hit", and each costs a chain of
+                // dependent shared-memory atomics on its query's two bests (ncu: 60 % of the bound-only pass's samples
+                // sat in that code, another 26 % in warps waiting for it at the end).  While a block is that dense
+                // the warp finds each query's two best of its 32 rows with two redux steps -- independent across the
+                // 32 queries, so they pipeline -- lane j keeps those of query col0 + j, and ONE round of atomics, 32
+                // queries side by side, offers them (the CTA's two best are among the warps' two best).
+                if (__any_sync(0xFFFFFFFFu, __popc(mask) >= 12)) {
+                    unsigned int my_m1 = 0u, my_m2 = 0u;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const float sj = __uint_as_float(v[j]) * inv;
+                        const unsigned int o = (((mask >> j) & 1u) && col0 + j < p.nq) ? score_to_order(sj) : 0u;
+                        const unsigned int m1 = __reduce_max_sync(0xFFFFFFFFu, o);
+                        const int first = __ffs(__ballot_sync(0xFFFFFFFFu, o == m1)) - 1;
+                        const unsigned int m2 = __reduce_max_sync(0xFFFFFFFFu, lane == first ? 0u : o);
+                        if (lane == j) { my_m1 = m1; my_m2 = m2; }
+                        if (p.mode == 1 && o != 0u) on_hit(col0 + j, row, sj, false);
+                    }
+                    if (my_m1 != 0u) note_best(col0 + lane, my_m1);
+                    if (my_m2 != 0u) note_best(col0 + lane, my_m2);
+                } else if (mask) {
 #pragma unroll
                     for (int j = 0; j < 32; j++)
-                        if (mask & (1u << j)) on_hit(col0 + j, row, __uint_as_float(v[j]) * inv);
+                        if (mask & (1u << j)) on_hit(col0 + j, row, __uint_as_float(v[j]) * inv, true);
                 }
             }
             tc_fence_before();
